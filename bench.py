@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""bench.py — image-pairs/sec for raft_large 440x1024, 32 iterations (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+A step is one pass of the hot path inside the full forward over one batch of synthetic pairs
+(BASELINE config 2: batch 1 per GPU, 440x1024, 32 iterations; weak scaling over GPUs, no
+collective — pairs are independent).  Rank 0 prints ONE JSON line.
+
+* ``value``     pairs/s with inputs resident in HBM (CUDA-graph replay), max over ranks.
+* ``e2e``       pairs/s through ``model.apply``'s runner with HOST (pinned) inputs: H2D of both
+                frames and D2H of the final flow inside the timed region, every step.
+* ``roofline``  the window-lookup kernel (the kernel BASELINE's metric names): algorithmic bytes
+                per launch / mean launch duration from CUDA events recorded around every lookup
+                launch of an eager forward on the launching stream; peak from MEASURED_PEAKS.json.
+* ``cpu_baseline`` the CPU oracle (``oracle/raft_cpu.py``) timed on the host cores on a bounded
+                sample (N=1, rank 0 only).
+* ``--impl reference`` times that same CPU oracle as the reference arm (the reference itself needs
+                jax/flax, which this image lacks: BASELINE.md §3).
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "image-pairs/sec raft_large 440x1024 32 iters"
+UNIT = "pairs/s"
+H, W, ITERS = 440, 1024, 32
+FALLBACK_HBM_GBS = 6650.0  # B200_PROFILING.md fallback, used only if MEASURED_PEAKS.json is absent
+
+
+def synthetic_pairs(batch: int, seed: int):
+    """uniform [-1, 1] frames; frame 2 = frame 1 rolled by (3, -5) px + N(0, 0.02^2)."""
+    rng = np.random.default_rng(seed)
+    img1 = rng.uniform(-1, 1, (batch, H, W, 3)).astype(np.float32)
+    img2 = np.roll(img1, (3, -5), axis=(1, 2)) + rng.normal(0, 0.02, img1.shape).astype(np.float32)
+    return img1, np.clip(img2, -1, 1).astype(np.float32)
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", p
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)", {}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons for one GPU while the timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 8:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                smax.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------
+# CPU oracle arm (cpu_baseline and --impl reference)
+# ---------------------------------------------------------------------------------------
+def cpu_oracle_pairs_per_s(steps: int, warmup: int, budget_s: float):
+    """Times oracle/raft_cpu.py on the host cores.  Each step is a bounded sample of the workload
+    (one 440x1024 pair, ``sample_iters`` of the 32 iterations, per-iteration phases scaled to 32)."""
+    import torch
+
+    from oracle import raft_cpu
+
+    cores = torch.get_num_threads()
+    net = raft_cpu.build_modules("raft_large", seed=0)
+    img1, img2 = synthetic_pairs(1, seed=1)
+    # probe: 1 iteration, to size the sample so that (steps + warmup) samples fit the budget
+    t0 = time.perf_counter()
+    _, probe = raft_cpu.time_pair(net, img1, img2, 1, ITERS)
+    probe_s = time.perf_counter() - t0
+    fixed = probe["encoders"] + probe["build_pyramid"]
+    per_iter = max(probe_s - fixed, 1e-3)
+    per_step_budget = budget_s / max(steps + warmup, 1)
+    sample_iters = int(max(1, min(ITERS, (per_step_budget - fixed) / per_iter)))
+    for _ in range(warmup):
+        raft_cpu.time_pair(net, img1, img2, sample_iters, ITERS)
+    times, phases = [], {}
+    for _ in range(steps):
+        t, ph = raft_cpu.time_pair(net, img1, img2, sample_iters, ITERS)
+        times.append(t)
+        for k, v in ph.items():
+            phases[k] = phases.get(k, 0.0) + v / steps
+    per_pair = sum(times) / len(times)
+    sample = (f"1 pair 440x1024, {sample_iters} of {ITERS} iterations timed per step, per-iteration phases "
+              f"scaled to {ITERS}; {steps} steps after {warmup} warm-up; torch CPU convs + NumPy oracle hot path")
+    return 1.0 / per_pair, per_pair, cores, sample, phases
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # rank 0 alone runs the CPU arm
+    value, per_pair, cores, sample, phases = cpu_oracle_pairs_per_s(args.steps, args.warmup, budget_s=150.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_pair * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "raft_large 440x1024 batch 1, 32 iterations (BASELINE config 2)", "host": "cpu"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "phase_seconds_per_sample": phases},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "the reference (jax/flax) cannot be installed on this image; this is the CPU oracle port",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------
+class _TimedCorr:
+    """Wraps a corr block and records CUDA events around every lookup launch (eager pass only)."""
+
+    def __init__(self, inner, torch):
+        self.inner, self.torch = inner, torch
+        self.out_channels = inner.out_channels
+        self.lookup_events, self.build_events = [], []
+
+    def build_pyramid(self, f1, f2):
+        a, b = self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = self.inner.build_pyramid(f1, f2)
+        b.record()
+        self.build_events.append((a, b))
+        return out
+
+    def index_pyramid(self, pyr, coords):
+        a, b = self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = self.inner.index_pyramid(pyr, coords)
+        b.record()
+        self.lookup_events.append((a, b))
+        return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    import jax_raft_b200 as J
+    from jax_raft_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    B = args.batch
+
+    model, variables = J.raft_large(seed=0)
+    img1_np, img2_np = synthetic_pairs(B, seed=1 + rank)
+    pin1 = torch.from_numpy(img1_np).pin_memory()
+    pin2 = torch.from_numpy(img2_np).pin_memory()
+    out_pin = torch.empty((B, H, W, 2), dtype=torch.float32).pin_memory()
+
+    before = dict(_lib.LAUNCHES)
+    runner = model.runner(variables, B, H, W, ITERS, device=dev)  # 2 eager warm-ups + 1 capture
+    per_forward = (_lib.LAUNCHES["kernels"] - before["kernels"]) // 3
+    runner.image1.copy_(pin1)
+    runner.image2.copy_(pin2)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(step_fn, steps, warmup):
+        for _ in range(warmup):
+            step_fn()
+        barrier()
+        evs = []
+        for _ in range(steps):
+            flush.fill_(1)  # L2 flush between timed iterations, outside the timed events
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            step_fn()
+            b.record(stream)
+            evs.append((a, b))
+        barrier()
+        total_ms = sum(a.elapsed_time(b) for a, b in evs)
+        if world > 1:
+            t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total_ms = float(t.item())
+        return total_ms
+
+    def step_resident():
+        runner.graph.replay()
+
+    def step_e2e():
+        runner.image1.copy_(pin1, non_blocking=True)
+        runner.image2.copy_(pin2, non_blocking=True)
+        runner.graph.replay()
+        out_pin.copy_(runner.flows[-1], non_blocking=True)
+
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    total_ms = timed(step_resident, args.steps, args.warmup)
+    clocks = sampler.stop() if sampler else None
+    e2e_ms = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    torch.cuda.synchronize(dev)
+    assert torch.isfinite(out_pin).all(), "non-finite flow"
+
+    # ---- lookup-kernel roofline: events around every lookup launch of eager forwards ----
+    tcorr = _TimedCorr(model.corr_block, torch)
+    model_t = J.RAFT(model.config, corr_block=tcorr, precision=model.precision)
+    P = model.prepare(variables, dev)
+    with torch.no_grad():
+        for i in range(1 + args.roofline_passes):
+            if i == 1:
+                tcorr.lookup_events.clear()
+                tcorr.build_events.clear()
+            flush.fill_(1)
+            model_t.forward(P, runner.image1, runner.image2, ITERS)
+    torch.cuda.synchronize(dev)
+    lk_ms = [a.elapsed_time(b) for a, b in tcorr.lookup_events]
+    bd_ms = [a.elapsed_time(b) for a, b in tcorr.build_events]
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    hbm_gbs, peak_src, peaks = measured_peaks()
+    cfg = model.config
+    r, L = cfg.corr_block_radius, cfg.corr_block_num_levels
+    nq = B * (H // 8) * (W // 8)
+    lookup_bytes = nq * (L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4)  # 2904 B/query
+    lk_mean_ms = sum(lk_ms) / len(lk_ms)
+    achieved = lookup_bytes / (lk_mean_ms * 1e-3) / 1e9
+    N = (H // 8) * (W // 8)
+    P_l = sum((H // 8 >> l) * (W // 8 >> l) for l in range(L))
+    pyr_bytes = 4 * (2 * B * N * 256 + B * N * P_l)
+    pyr_ms = sum(bd_ms) / len(bd_ms)
+
+    pairs = world * B * args.steps
+    line = {
+        "metric": METRIC, "value": pairs / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {
+            "workload": f"raft_large {H}x{W} batch {B} per GPU, {ITERS} iterations (BASELINE config 2), random-init weights",
+            "global_batch": world * B, "parallelism": f"batch-sharded x{world}, no collective",
+            "conv_precision": model.precision + " (cuDNN library path, out of kernel scope)",
+            "l2": "flushed between timed steps (256 MiB write outside the events); step working set "
+                  "(261 MB pyramid + activations) also exceeds the 126 MB L2",
+            "timing": "per-step CUDA events on the launching stream, summed; barrier + synchronize both sides; max over ranks",
+        },
+        "e2e": {"value": pairs / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
+                "h2d_bytes_per_step": int(pin1.numel() * 4 * 2), "d2h_bytes_per_step": int(out_pin.numel() * 4)},
+        "gpu_launches": int(per_forward * args.steps),
+        "gpu_launches_per_step": int(per_forward),
+        "clocks": clocks,
+        "roofline": {
+            "kernel": "corr_lookup_kernel<4> (raftk_corr_lookup)", "bound": "hbm", "achieved": achieved,
+            "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": None,
+            "peak_source": peak_src, "algorithmic_bytes_per_launch": lookup_bytes,
+            "mean_launch_ms": lk_mean_ms, "launches_timed": len(lk_ms),
+            "how": "CUDA events around each lookup launch in eager forwards (event pair overhead included)",
+        },
+        "kernels": {
+            "corr_pyramid": {"mean_ms": pyr_ms, "algorithmic_bytes": pyr_bytes,
+                             "hbm_gbs": pyr_bytes / (pyr_ms * 1e-3) / 1e9,
+                             "tflops_algorithmic": 2.0 * B * N * N * 256 / (pyr_ms * 1e-3) / 1e12},
+        },
+    }
+    if world == 1 and not args.skip_cpu_baseline:
+        v, per_pair, cores, sample, phases = cpu_oracle_pairs_per_s(steps=1, warmup=0, budget_s=25.0)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                                "phase_seconds_per_sample": phases}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--batch", type=int, default=1, help="pairs per GPU (BASELINE config 2: 1)")
+    ap.add_argument("--roofline-passes", type=int, default=2)
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

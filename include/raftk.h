@@ -1,0 +1,124 @@
+/*
+ * raftk.h — C ABI of the B200 (sm_100a) RAFT correlation hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no framework types.  Every
+ * pointer named "device" is a CUDA device pointer owned by the caller; the library
+ * never allocates or frees caller-visible memory, never synchronises the host, and
+ * launches on the stream it is given (a cudaStream_t passed as void*).  All tensors
+ * are float32, dense, row-major, in the reference's layouts (NHWC, coords = (x, y)).
+ *
+ * Return value: 0 on success; a negative RAFTK_ERR_* for a rejected call (nothing was
+ * launched); a positive value is the cudaError_t of a failed launch.  Nothing throws
+ * across this boundary.  A jax.ffi handler maps non-zero to an XLA_FFI_Error
+ * (see INTEGRATION.md).
+ *
+ * Reference citations are into /root/reference/jax_raft/model.py.
+ *
+ * Terms: B = image pairs; (h, w) = 1/8-resolution feature-map size; D = feature
+ * channels; nq = query pixels per pair held by this GPU (h*w unless query rows are
+ * sharded); Q = B*nq; L = pyramid levels; r = lookup radius;
+ * level l has size (h>>l, w>>l).
+ */
+#ifndef RAFTK_H_
+#define RAFTK_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RAFTK_MAX_LEVELS 6
+
+enum {
+  RAFTK_OK = 0,
+  RAFTK_ERR_NULL = -1,        /* a required pointer is NULL */
+  RAFTK_ERR_SHAPE = -2,       /* a size is non-positive or inconsistent */
+  RAFTK_ERR_TOO_SMALL = -3,   /* h or w < 2 * 2^(L-1): model.py:431-436 */
+  RAFTK_ERR_UNSUPPORTED = -4, /* a valid request this build has no kernel for */
+  RAFTK_ERR_SCRATCH = -5,     /* scratch buffer missing or too small */
+  RAFTK_ERR_ALIGN = -6        /* a pointer is not aligned as documented */
+};
+
+/* ABI version (major*1000 + minor) and a static description of an error code. */
+int raftk_version(void);
+const char* raftk_error_string(int code);
+
+/* ------------------------------------------------------------------------------------
+ * Kernel family 1 — all-pairs correlation volume + avg-pool pyramid.
+ * Replaces CorrBlock.build_pyramid, model.py:418-446 (volume: 472-481, pooling: 443-445).
+ *
+ *   fmap1   device, (B, nq, D)       query-pixel features (fmap1 rows held by this GPU)
+ *   fmap2   device, (B, h, w, D)     all target-pixel features
+ *   levels  HOST array of L device pointers; levels[l] is (B*nq, h>>l, w>>l):
+ *             levels[0][q, y, x] = sum_d fmap1[q, d] * fmap2[b(q), y, x, d] / sqrt(D)
+ *             levels[l+1][q, y, x] = mean of the 2x2 block of levels[l] (VALID: odd
+ *             trailing rows/columns dropped), as the reference pools level by level.
+ *   scratch device, raftk_corr_pyramid_scratch_bytes(...) bytes, 256-byte aligned; holds
+ *           the bf16 hi/mid split of both feature maps for the tensor-core kernel.
+ *
+ * The product kernel is a tcgen05/TMEM GEMM with the pooling fused in its epilogue.
+ * Products are formed from a two-term bf16 split of each float32 operand (hi*hi +
+ * mid*hi + hi*mid, fp32 accumulate): relative error ~2e-5, inside the 1e-3 the
+ * north-star allows.  Pooling bounds are exact.
+ * ---------------------------------------------------------------------------------- */
+size_t raftk_corr_pyramid_scratch_bytes(int B, int nq, int h, int w, int D);
+int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float* const* levels,
+                       int num_levels, int B, int nq, int h, int w, int D,
+                       void* scratch, size_t scratch_bytes, void* stream);
+
+/* Same contract, plain fp32 FMA kernels (no tensor cores, no scratch).  Diagnostic:
+ * used by the tests to separate indexing errors from split-precision error. */
+int raftk_corr_pyramid_simt(const float* fmap1, const float* fmap2, float* const* levels,
+                            int num_levels, int B, int nq, int h, int w, int D, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Kernel family 2 — radius-r bilinear window lookup.
+ * Replaces CorrBlock.index_pyramid, model.py:448-470, and its inner grid_sample,
+ * model.py:24-34.
+ *
+ *   levels  HOST array of L device pointers, as written by raftk_corr_pyramid
+ *   coords  device, (Q, 2)  centroid (x, y) in level-0 pixels
+ *   out     device, (Q, L*(2r+1)^2); channel l*(2r+1)^2 + i*(2r+1) + j samples level l
+ *           at (x/2^l + i - r, y/2^l + j - r): the x offset is the slow index
+ *           (model.py:452-455, 463).  Bilinear, each corner zero outside the level
+ *           (jax map_coordinates order=1 mode='constant'), float32 operations in the
+ *           reference's order so results are bit-identical to a float32 CPU evaluation.
+ * ---------------------------------------------------------------------------------- */
+int raftk_corr_lookup(const float* const* levels, int num_levels, const float* coords,
+                      float* out, int Q, int h, int w, int radius, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Kernel family 2b — "alt_corr": the same lookup computed on the fly from the feature
+ * maps, never materialising the volume (no reference counterpart; equals
+ * index_pyramid(build_pyramid(f1, f2), coords) by linearity of the average pool).
+ *
+ *   raftk_altcorr_pool_fmap2: f2_levels[0] = fmap2 (B,h,w,D) is an INPUT;
+ *     f2_levels[l>=1] (B, h>>l, w>>l, D) are written: 2x2 VALID average of level l-1
+ *     (the pooling rule of model.py:443-445 applied to fmap2).
+ *   raftk_altcorr_lookup: fmap1 (B, nq, D), coords (B*nq, 2), out (B*nq, L*(2r+1)^2),
+ *     same channel order and border rule as raftk_corr_lookup.
+ * ---------------------------------------------------------------------------------- */
+int raftk_altcorr_pool_fmap2(float* const* f2_levels, int num_levels, int B, int h, int w,
+                             int D, void* stream);
+int raftk_altcorr_lookup(const float* fmap1, const float* const* f2_levels, int num_levels,
+                         const float* coords, float* out, int B, int nq, int h, int w,
+                         int D, int radius, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Kernel family 3 — convex 8x flow upsampling.
+ * Replaces the up_mask branch of upsample_flow, model.py:85-98.
+ *
+ *   flow  device, (B, h, w, 2)
+ *   mask  device, (B, h, w, 576); channel k*64 + fy*8 + fx, k = (dy+1)*3 + (dx+1)
+ *   out   device, (B, 8h, 8w, 2):
+ *         out[b, 8y+fy, 8x+fx, c] = sum_k softmax_k(mask[b,y,x,:,fy,fx]) * 8*flow[b,y+dy,x+dx,c]
+ *         with zero flow outside the image.
+ * ---------------------------------------------------------------------------------- */
+int raftk_convex_upsample(const float* flow, const float* mask, float* out, int B, int h,
+                          int w, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAFTK_H_ */

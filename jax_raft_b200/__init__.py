@@ -1,0 +1,17 @@
+"""jax_raft_b200 — B200 (sm_100a) implementation of RAFT's correlation hot path behind the
+API of alebeck/jax-raft (``jax_raft/__init__.py:1-7``: ``RAFT``, ``raft_large``, ``raft_small``).
+
+Importing the package does not need a GPU; calling any correlation / upsampling op does, and
+raises if ``lib/libraftk.so`` has not been built (there is no CPU or eager fallback).
+"""
+
+from .corr import AltCorrBlock, CorrBlock
+from .functional import make_coords_grid, upsample_flow
+from .model import (RAFT, RAFT_LARGE, RAFT_SMALL, RaftConfig, init_variables, raft_large, raft_small,
+                    torch_state_dict_from_variables, variables_from_torch_state_dict)
+
+__all__ = [
+    "RAFT", "raft_large", "raft_small", "CorrBlock", "AltCorrBlock", "upsample_flow", "make_coords_grid",
+    "RaftConfig", "RAFT_LARGE", "RAFT_SMALL", "init_variables", "variables_from_torch_state_dict",
+    "torch_state_dict_from_variables",
+]

@@ -1,0 +1,172 @@
+"""Host-side mirror of the reference's correlation block, backed by libraftk (sm_100a).
+
+``CorrBlock`` keeps the reference's duck-typed contract (``/root/reference/jax_raft/model.py:403-481``,
+plug point ``:643-644``, contract ``:530-539``): ``out_channels``,
+``build_pyramid(fmap1, fmap2) -> pyramid`` and ``index_pyramid(pyramid, coords)``.  Arrays are
+torch CUDA float32 tensors in the reference's NHWC layouts; errors are ``AssertionError`` with the
+reference's messages, raised before any launch.
+"""
+
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+
+
+def _check_cuda_f32(name: str, t: torch.Tensor) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a torch.Tensor on a CUDA device, got {type(t)}")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} is on {t.device}: the correlation path runs on sm_100a only; there is no CPU fallback")
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name} must be float32, got {t.dtype}")
+    return t.contiguous()
+
+
+def _check_fmaps(fmap1, fmap2, num_levels, query_rows):
+    """The reference's build_pyramid assertions (model.py:426, 431-436), raised before any launch.
+
+    With ``query_rows=(y0, y1)`` fmap1 may be the full map (it is sliced) or already the band
+    of rows [y0, y1) (row-sharded callers); fmap2 is always the full map.
+    """
+    h = fmap2.shape[-3]
+    presliced = False
+    if query_rows is not None:
+        y0, y1 = query_rows
+        assert 0 <= y0 <= y1 <= h, f"query_rows {query_rows} outside [0, {h}]"
+        presliced = fmap1.shape[-3] == y1 - y0 and fmap1.shape[-3] != h
+    if presliced:
+        assert fmap1.shape[0] == fmap2.shape[0] and fmap1.shape[2:] == fmap2.shape[2:], \
+            "Input feature maps should have the same shapes"
+    else:
+        assert fmap1.shape == fmap2.shape, "Input feature maps should have the same shapes"
+    min_fmap_size = 2 * (2 ** (num_levels - 1))
+    assert not any(s < min_fmap_size for s in fmap2.shape[-3:-1]), (
+        "Feature maps are too small to be down-sampled by the correlation pyramid. "
+        f"H and W of feature maps should be at least {min_fmap_size}; got: {tuple(fmap2.shape[-3:-1])}. "
+        "Remember that input images to the model are downsampled by 8, so that means their "
+        f"dimensions should be at least 8 * {min_fmap_size} = {8 * min_fmap_size}."
+    )
+    fmap1 = _check_cuda_f32("fmap1", fmap1)
+    fmap2 = _check_cuda_f32("fmap2", fmap2)
+    if query_rows is not None and not presliced:
+        fmap1 = fmap1[:, query_rows[0]:query_rows[1]].contiguous()
+    return fmap1, fmap2
+
+
+class CorrBlock:
+    """All-pairs correlation pyramid + radius-r window lookup (model.py:403-481)."""
+
+    def __init__(self, num_levels: int = 4, radius: int = 4, kernel: str = "tc"):
+        assert 1 <= num_levels <= _lib.MAX_LEVELS
+        assert kernel in ("tc", "simt")
+        self.num_levels = num_levels
+        self.radius = radius
+        self.out_channels = num_levels * (2 * radius + 1) ** 2  # model.py:416
+        self.kernel = kernel
+
+    # -- model.py:418-446 ---------------------------------------------------------------
+    def build_pyramid(self, fmap1: torch.Tensor, fmap2: torch.Tensor,
+                      query_rows: Optional[Tuple[int, int]] = None) -> List[torch.Tensor]:
+        """Returns ``num_levels`` tensors (B*nq, h>>l, w>>l, 1).
+
+        ``query_rows=(y0, y1)`` builds only the volume rows of fmap1 rows [y0, y1): the
+        row-sharded mode of SURVEY.md §8e (fmap2 must be the full, all-gathered map).
+        """
+        fmap1, fmap2 = _check_fmaps(fmap1, fmap2, self.num_levels, query_rows)
+        b, h, w, d = fmap2.shape
+        nq = fmap1.shape[1] * w
+        lib = _lib.load()
+        levels = [
+            torch.empty((b * nq, h >> l, w >> l, 1), dtype=torch.float32, device=fmap1.device)
+            for l in range(self.num_levels)
+        ]
+        stream = _lib.current_stream_ptr(fmap1.device)
+        with torch.cuda.device(fmap1.device):
+            if self.kernel == "simt":
+                rc = lib.raftk_corr_pyramid_simt(fmap1.data_ptr(), fmap2.data_ptr(), _lib.ptr_array(levels),
+                                                 self.num_levels, b, nq, h, w, d, stream)
+                _lib.check("raftk_corr_pyramid_simt", rc)
+                _lib.count_launch(self.num_levels)  # volume + (L-1) pooling kernels
+            else:
+                nbytes = lib.raftk_corr_pyramid_scratch_bytes(b, nq, h, w, d)
+                scratch = torch.empty((max(nbytes, 1),), dtype=torch.uint8, device=fmap1.device)
+                rc = lib.raftk_corr_pyramid(fmap1.data_ptr(), fmap2.data_ptr(), _lib.ptr_array(levels),
+                                            self.num_levels, b, nq, h, w, d, scratch.data_ptr(), nbytes, stream)
+                _lib.check("raftk_corr_pyramid", rc)
+                _lib.count_launch(self.num_levels)  # interim: forwards to the simt kernels
+                # scratch was allocated on the launching stream, so the caching allocator
+                # cannot hand it to anyone before the kernel has consumed it.
+        return levels
+
+    # -- model.py:448-470 ---------------------------------------------------------------
+    def index_pyramid(self, corr_pyramid: Sequence[torch.Tensor], centroids_coords: torch.Tensor) -> torch.Tensor:
+        assert centroids_coords.shape[-1] == 2
+        coords = _check_cuda_f32("centroids_coords", centroids_coords)
+        b, hq, wq, _ = coords.shape
+        q = b * hq * wq
+        assert len(corr_pyramid) == self.num_levels
+        lv0 = corr_pyramid[0]
+        assert lv0.shape[0] == q, "pyramid and coords disagree on the number of query pixels"
+        h, w = int(lv0.shape[1]), int(lv0.shape[2])
+        levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(corr_pyramid)]
+        out = torch.empty((b, hq, wq, self.out_channels), dtype=torch.float32, device=coords.device)
+        lib = _lib.load()
+        with torch.cuda.device(coords.device):
+            rc = lib.raftk_corr_lookup(_lib.ptr_array(levels), self.num_levels, coords.data_ptr(), out.data_ptr(),
+                                       q, h, w, self.radius, _lib.current_stream_ptr(coords.device))
+        _lib.check("raftk_corr_lookup", rc)
+        _lib.count_launch(1)
+        assert out.shape == (b, hq, wq, self.out_channels)
+        return out
+
+
+class AltCorrBlock:
+    """On-the-fly lookup that never materialises the volume ("alt_corr").
+
+    Same contract as :class:`CorrBlock`; the opaque "pyramid" is ``(fmap1_rows, [fmap2 pooled
+    l times])``.  Not in the reference; equal to the volume path by linearity
+    of the average pool.
+    """
+
+    def __init__(self, num_levels: int = 4, radius: int = 4):
+        assert 1 <= num_levels <= _lib.MAX_LEVELS
+        self.num_levels = num_levels
+        self.radius = radius
+        self.out_channels = num_levels * (2 * radius + 1) ** 2
+
+    def build_pyramid(self, fmap1: torch.Tensor, fmap2: torch.Tensor,
+                      query_rows: Optional[Tuple[int, int]] = None):
+        fmap1, fmap2 = _check_fmaps(fmap1, fmap2, self.num_levels, query_rows)
+        b, h, w, d = fmap2.shape
+        f2_levels = [fmap2] + [
+            torch.empty((b, h >> l, w >> l, d), dtype=torch.float32, device=fmap2.device)
+            for l in range(1, self.num_levels)
+        ]
+        lib = _lib.load()
+        with torch.cuda.device(fmap2.device):
+            rc = lib.raftk_altcorr_pool_fmap2(_lib.ptr_array(f2_levels), self.num_levels, b, h, w, d,
+                                              _lib.current_stream_ptr(fmap2.device))
+        _lib.check("raftk_altcorr_pool_fmap2", rc)
+        _lib.count_launch(self.num_levels - 1)
+        return (fmap1, f2_levels)
+
+    def index_pyramid(self, corr_pyramid, centroids_coords: torch.Tensor) -> torch.Tensor:
+        fmap1, f2_levels = corr_pyramid
+        assert centroids_coords.shape[-1] == 2
+        coords = _check_cuda_f32("centroids_coords", centroids_coords)
+        b, hq, wq, _ = coords.shape
+        assert fmap1.shape[:3] == (b, hq, wq), "fmap1 rows and coords disagree"
+        _, h, w, d = f2_levels[0].shape
+        out = torch.empty((b, hq, wq, self.out_channels), dtype=torch.float32, device=coords.device)
+        lib = _lib.load()
+        with torch.cuda.device(coords.device):
+            rc = lib.raftk_altcorr_lookup(fmap1.data_ptr(), _lib.ptr_array(f2_levels), self.num_levels,
+                                          coords.data_ptr(), out.data_ptr(), b, hq * wq, h, w, d, self.radius,
+                                          _lib.current_stream_ptr(coords.device))
+        _lib.check("raftk_altcorr_lookup", rc)
+        _lib.count_launch(1)
+        return out

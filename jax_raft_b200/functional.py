@@ -1,0 +1,52 @@
+"""Functional helpers of the reference (``/root/reference/jax_raft/model.py:24-98``), NHWC.
+
+``upsample_flow`` with a mask runs the hand-written sm_100a kernel through the C ABI; the
+mask-less bilinear branch (raft_small, model.py:79-83) is out of kernel scope
+and stays on the host framework's library path.
+"""
+
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from .corr import _check_cuda_f32
+
+
+def make_coords_grid(batch_size: int, h: int, w: int, device="cuda") -> torch.Tensor:
+    """``coords[b, y, x] = (x, y)`` float32 (model.py:37-40)."""
+    ys, xs = torch.meshgrid(torch.arange(h, device=device), torch.arange(w, device=device), indexing="ij")
+    coords = torch.stack([xs, ys], dim=-1).to(torch.float32)
+    return coords[None].repeat(batch_size, 1, 1, 1)
+
+
+def upsample_flow(flow: torch.Tensor, up_mask: Optional[torch.Tensor] = None, factor: int = 8) -> torch.Tensor:
+    """Upsample flow (B, h, w, C) by ``factor`` (model.py:69-98).
+
+    With ``up_mask`` (B, h, w, 9*factor*factor): convex combination of the 3x3 neighbours with
+    softmax weights (model.py:85-98) — the CUDA kernel, which implements factor 8 and C = 2 (the
+    only configuration the reference's models use).  Without: ``factor *`` align-corners bilinear
+    resize (model.py:79-83).
+    """
+    batch_size, h, w, num_channels = flow.shape
+    if up_mask is None:
+        x = flow.permute(0, 3, 1, 2)
+        up = F.interpolate(x, size=(h * factor, w * factor), mode="bilinear", align_corners=True)
+        return (factor * up).permute(0, 2, 3, 1).contiguous()
+
+    assert up_mask.shape == (batch_size, h, w, 9 * factor * factor)
+    if factor != 8 or num_channels != 2:
+        raise NotImplementedError("the convex upsampling kernel implements factor=8, 2 flow channels")
+    flow = _check_cuda_f32("flow", flow)
+    up_mask = _check_cuda_f32("up_mask", up_mask)
+    out = torch.empty((batch_size, 8 * h, 8 * w, 2), dtype=torch.float32, device=flow.device)
+    lib = _lib.load()
+    with torch.cuda.device(flow.device):
+        rc = lib.raftk_convex_upsample(flow.data_ptr(), up_mask.data_ptr(), out.data_ptr(), batch_size, h, w,
+                                       _lib.current_stream_ptr(flow.device))
+    _lib.check("raftk_convex_upsample", rc)
+    _lib.count_launch(1)
+    return out

@@ -1,0 +1,518 @@
+"""RAFT host model with the reference's Flax-shaped API, hot path on libraftk (sm_100a).
+
+Mirrors ``/root/reference/jax_raft/model.py``:
+
+* ``raft_large(*, pretrained=False, **kwargs) -> (model, variables)`` (``:694``), ``raft_small`` (``:732``);
+  ``corr_block=`` is the injection point (``:643-644``).
+* ``model.apply(variables, image1, image2, train=False, num_flow_updates=12) -> (N, B, H, W, 2)``
+  (``:557``, ``:605``); images NHWC float32 in [-1, 1] (``examples/demo.py:9-10``).
+* ``variables = {"params": ..., "batch_stats": ...}`` with the Flax tree names and layouts
+  (conv ``kernel`` HWIO, norm ``scale``/``bias``, ``batch_stats`` ``mean``/``var``), i.e. exactly
+  what ``scripts/convert_checkpoint.py:11-56`` produces from a torchvision ``state_dict``.
+
+Scope: the correlation block and the convex upsampler are the hand-written
+CUDA kernels; encoders, the conv-GRU update block and the mask predictor are dense convolutions
+and deliberately stay on the host framework's library path (cuDNN through torch).  Inference only
+(``train=True`` raises): there is no VJP for the kernels.
+"""
+
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Any, Dict, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from .corr import CorrBlock
+from .functional import make_coords_grid, upsample_flow
+
+Tree = Dict[str, Any]
+
+
+# ---------------------------------------------------------------------------------------
+# Architecture description (the keyword arguments of _raft, model.py:608-635)
+# ---------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class RaftConfig:
+    name: str
+    feature_encoder_layers: Tuple[int, ...]
+    feature_encoder_block: str  # "residual" | "bottleneck"
+    feature_encoder_norm: Optional[str]  # "instance" | "batch" | None
+    context_encoder_layers: Tuple[int, ...]
+    context_encoder_block: str
+    context_encoder_norm: Optional[str]
+    corr_block_num_levels: int
+    corr_block_radius: int
+    motion_encoder_corr_layers: Tuple[int, ...]
+    motion_encoder_flow_layers: Tuple[int, ...]
+    motion_encoder_out_channels: int
+    recurrent_block_hidden_state_size: int
+    recurrent_block_kernel_size: Tuple[Tuple[int, int], ...]
+    recurrent_block_padding: Tuple[Tuple[int, int], ...]
+    flow_head_hidden_size: int
+    use_mask_predictor: bool
+    encoder_strides: Tuple[int, ...] = (2, 1, 2, 2)  # FeatureEncoder.strides, model.py:227
+
+
+RAFT_LARGE = RaftConfig(  # model.py:702-729
+    name="raft_large",
+    feature_encoder_layers=(64, 64, 96, 128, 256), feature_encoder_block="residual", feature_encoder_norm="instance",
+    context_encoder_layers=(64, 64, 96, 128, 256), context_encoder_block="residual", context_encoder_norm="batch",
+    corr_block_num_levels=4, corr_block_radius=4,
+    motion_encoder_corr_layers=(256, 192), motion_encoder_flow_layers=(128, 64), motion_encoder_out_channels=128,
+    recurrent_block_hidden_state_size=128, recurrent_block_kernel_size=((1, 5), (5, 1)),
+    recurrent_block_padding=((0, 2), (2, 0)), flow_head_hidden_size=256, use_mask_predictor=True,
+)
+
+RAFT_SMALL = RaftConfig(  # model.py:740-767
+    name="raft_small",
+    feature_encoder_layers=(32, 32, 64, 96, 128), feature_encoder_block="bottleneck", feature_encoder_norm="instance",
+    context_encoder_layers=(32, 32, 64, 96, 160), context_encoder_block="bottleneck", context_encoder_norm=None,
+    corr_block_num_levels=4, corr_block_radius=3,
+    motion_encoder_corr_layers=(96,), motion_encoder_flow_layers=(64, 32), motion_encoder_out_channels=82,
+    recurrent_block_hidden_state_size=96, recurrent_block_kernel_size=((3, 3),),
+    recurrent_block_padding=((1, 1),), flow_head_hidden_size=128, use_mask_predictor=False,
+)
+
+
+# ---------------------------------------------------------------------------------------
+# Variable tree: shapes, initialisers, conversion to/from torchvision state_dict keys
+# ---------------------------------------------------------------------------------------
+def _conv_specs(cfg: RaftConfig):
+    """Yield (path, kh, kw, cin, cout, init, norm) for every conv; path is the Flax tree path.
+
+    ``init`` is "kaiming" for the reference's ``Conv()`` helper (variance_scaling(2, fan_out,
+    truncated_normal), model.py:101-104) and "lecun" for bare ``nn.Conv`` (flax default).
+    ``norm`` is the norm layer that follows inside a ConvNormActivation ("batch" owns params).
+    """
+    def encoder(prefix, layers, block, norm):
+        yield (f"{prefix}/convnormrelu/layers_0", 7, 7, 3, layers[0], "kaiming", norm)
+        cin = layers[0]
+        for li, (cout, stride) in enumerate(zip(layers[1:4], cfg.encoder_strides[1:]), start=1):
+            for bi in range(2):
+                s = stride if bi == 0 else 1
+                base = f"{prefix}/layer{li}/layers_{bi}"
+                if block == "residual":
+                    yield (f"{base}/convnormrelu1/layers_0", 3, 3, cin, cout, "kaiming", norm)
+                    yield (f"{base}/convnormrelu2/layers_0", 3, 3, cout, cout, "kaiming", norm)
+                else:
+                    yield (f"{base}/convnormrelu1/layers_0", 1, 1, cin, cout // 4, "kaiming", norm)
+                    yield (f"{base}/convnormrelu2/layers_0", 3, 3, cout // 4, cout // 4, "kaiming", norm)
+                    yield (f"{base}/convnormrelu3/layers_0", 1, 1, cout // 4, cout, "kaiming", norm)
+                if s != 1:
+                    yield (f"{base}/downsample/layers_0", 1, 1, cin, cout, "kaiming", norm)
+                cin = cout
+        yield (f"{prefix}/conv", 1, 1, cin, layers[4], "kaiming", None)
+
+    yield from encoder("feature_encoder", cfg.feature_encoder_layers, cfg.feature_encoder_block, cfg.feature_encoder_norm)
+    yield from encoder("context_encoder", cfg.context_encoder_layers, cfg.context_encoder_block, cfg.context_encoder_norm)
+
+    corr_ch = cfg.corr_block_num_levels * (2 * cfg.corr_block_radius + 1) ** 2
+    me = "update_block/motion_encoder"
+    cl, fl = cfg.motion_encoder_corr_layers, cfg.motion_encoder_flow_layers
+    yield (f"{me}/convcorr1/layers_0", 1, 1, corr_ch, cl[0], "kaiming", None)
+    if len(cl) == 2:
+        yield (f"{me}/convcorr2/layers_0", 3, 3, cl[0], cl[1], "kaiming", None)
+    yield (f"{me}/convflow1/layers_0", 7, 7, 2, fl[0], "kaiming", None)
+    yield (f"{me}/convflow2/layers_0", 3, 3, fl[0], fl[1], "kaiming", None)
+    yield (f"{me}/conv/layers_0", 3, 3, cl[-1] + fl[1], cfg.motion_encoder_out_channels - 2, "kaiming", None)
+
+    hid = cfg.recurrent_block_hidden_state_size
+    ctx = cfg.context_encoder_layers[4] - hid
+    gru_in = hid + ctx + cfg.motion_encoder_out_channels
+    for gi, (kh, kw) in enumerate(cfg.recurrent_block_kernel_size, start=1):
+        for g in ("convz", "convr", "convq"):
+            yield (f"update_block/recurrent_block/convgru{gi}/{g}", kh, kw, gru_in, hid, "lecun", None)
+    yield ("update_block/flow_head/conv1", 3, 3, hid, cfg.flow_head_hidden_size, "lecun", None)
+    yield ("update_block/flow_head/conv2", 3, 3, cfg.flow_head_hidden_size, 2, "lecun", None)
+    if cfg.use_mask_predictor:
+        yield ("mask_predictor/convrelu/layers_0", 3, 3, hid, 256, "kaiming", None)
+        yield ("mask_predictor/conv", 1, 1, 256, 8 * 8 * 9, "lecun", None)
+
+
+def _tree_set(tree: Tree, path: str, value) -> None:
+    parts = path.split("/")
+    for p in parts[:-1]:
+        tree = tree.setdefault(p, {})
+    tree[parts[-1]] = value
+
+
+def _tree_get(tree: Tree, path: str):
+    for p in path.split("/"):
+        tree = tree[p]
+    return tree
+
+
+def _tree_items(tree: Tree, prefix: str = ""):
+    for k, v in tree.items():
+        path = f"{prefix}/{k}" if prefix else k
+        if isinstance(v, dict):
+            yield from _tree_items(v, path)
+        else:
+            yield path, v
+
+
+def init_variables(cfg: RaftConfig, seed: int = 0) -> Tree:
+    """Random-init ``{"params", "batch_stats"}`` with the reference's initialisers (host numpy).
+
+    The reference draws from ``jax.random.PRNGKey(0)`` (model.py:681-682); JAX's generator is not
+    available here, so the values differ while the distributions match.
+    """
+    g = torch.Generator().manual_seed(seed)
+    params: Tree = {}
+    stats: Tree = {}
+    for path, kh, kw, cin, cout, init, norm in _conv_specs(cfg):
+        fan = kh * kw * (cout if init == "kaiming" else cin)
+        scale = 2.0 if init == "kaiming" else 1.0
+        std = math.sqrt(scale / fan) / 0.87962566103423978
+        kernel = torch.empty((kh, kw, cin, cout))
+        torch.nn.init.trunc_normal_(kernel, mean=0.0, std=std, a=-2 * std, b=2 * std, generator=g)
+        _tree_set(params, f"{path}/kernel", kernel.numpy())
+        _tree_set(params, f"{path}/bias", np.zeros((cout,), np.float32))
+        if norm == "batch":
+            npath = path.rsplit("/", 1)[0] + "/layers_1"
+            _tree_set(params, f"{npath}/scale", np.ones((cout,), np.float32))
+            _tree_set(params, f"{npath}/bias", np.zeros((cout,), np.float32))
+            _tree_set(stats, f"{npath}/mean", np.zeros((cout,), np.float32))
+            _tree_set(stats, f"{npath}/var", np.ones((cout,), np.float32))
+    return {"params": params, "batch_stats": stats}
+
+
+def variables_from_torch_state_dict(state_dict) -> Tree:
+    """torchvision RAFT ``state_dict`` -> Flax-layout variables; the rules of
+    ``scripts/convert_checkpoint.py``: conv OIHW -> HWIO ``kernel`` (``:20``), 1-D ``weight`` ->
+    ``scale`` (``:23``), numeric path parts ``N`` -> ``layers_N`` (``:28``), ``running_mean/var`` ->
+    ``batch_stats`` ``mean/var`` (``:41-44``), ``num_batches_tracked`` dropped (``:45-46``)."""
+    params: Tree = {}
+    stats: Tree = {}
+    for key, value in state_dict.items():
+        if key.endswith(".num_batches_tracked"):
+            continue
+        v = np.asarray(value.detach().cpu().numpy() if hasattr(value, "detach") else value, dtype=np.float32)
+        parts = [("layers_" + p) if p.isdigit() else p for p in key.split(".")]
+        leaf = parts[-1]
+        tree = params
+        if leaf == "running_mean":
+            tree, leaf = stats, "mean"
+        elif leaf == "running_var":
+            tree, leaf = stats, "var"
+        elif leaf == "weight" and v.ndim == 4:
+            leaf, v = "kernel", v.transpose(2, 3, 1, 0)
+        elif leaf == "weight" and v.ndim == 1:
+            leaf = "scale"
+        _tree_set(tree, "/".join(parts[:-1] + [leaf]), np.ascontiguousarray(v))
+    return {"params": params, "batch_stats": stats}
+
+
+def torch_state_dict_from_variables(variables: Tree) -> Dict[str, torch.Tensor]:
+    """Inverse of :func:`variables_from_torch_state_dict` (without ``num_batches_tracked``)."""
+    out: Dict[str, torch.Tensor] = {}
+
+    def key_of(path_parts):
+        return ".".join(p[len("layers_"):] if p.startswith("layers_") else p for p in path_parts)
+
+    for path, v in _tree_items(variables["params"]):
+        parts = path.split("/")
+        v = np.asarray(v)
+        if parts[-1] == "kernel":
+            out[key_of(parts[:-1] + ["weight"])] = torch.from_numpy(np.ascontiguousarray(v.transpose(3, 2, 0, 1)))
+        elif parts[-1] == "scale":
+            out[key_of(parts[:-1] + ["weight"])] = torch.from_numpy(v.copy())
+        else:
+            out[key_of(parts)] = torch.from_numpy(v.copy())
+    for path, v in _tree_items(variables.get("batch_stats", {})):
+        parts = path.split("/")
+        leaf = {"mean": "running_mean", "var": "running_var"}[parts[-1]]
+        out[key_of(parts[:-1] + [leaf])] = torch.from_numpy(np.asarray(v).copy())
+    return out
+
+
+# ---------------------------------------------------------------------------------------
+# Prepared (device, library-layout) parameters
+# ---------------------------------------------------------------------------------------
+@dataclass
+class _ConvP:
+    w: torch.Tensor  # OIHW, channels_last
+    b: torch.Tensor
+
+
+def _prepare(cfg: RaftConfig, variables: Tree, device) -> Dict[str, _ConvP]:
+    """HWIO kernels -> OIHW channels_last on ``device``; inference BatchNorm (flax epsilon 1e-5,
+    use_running_average) folded into the preceding conv; MaskPredictor's 0.25 multiplier
+    (model.py:400, a power of two, so exact) folded into its last conv."""
+    params, stats = variables["params"], variables.get("batch_stats", {})
+    out: Dict[str, _ConvP] = {}
+    for path, kh, kw, cin, cout, _init, norm in _conv_specs(cfg):
+        k = torch.as_tensor(np.asarray(_tree_get(params, f"{path}/kernel")), dtype=torch.float32)
+        assert tuple(k.shape) == (kh, kw, cin, cout), f"{path}/kernel: expected {(kh, kw, cin, cout)}, got {tuple(k.shape)}"
+        b = torch.as_tensor(np.asarray(_tree_get(params, f"{path}/bias")), dtype=torch.float32)
+        w = k.permute(3, 2, 0, 1).contiguous().to(torch.float64)
+        b = b.to(torch.float64)
+        if norm == "batch":
+            npath = path.rsplit("/", 1)[0] + "/layers_1"
+            scale = torch.as_tensor(np.asarray(_tree_get(params, f"{npath}/scale")), dtype=torch.float64)
+            nbias = torch.as_tensor(np.asarray(_tree_get(params, f"{npath}/bias")), dtype=torch.float64)
+            mean = torch.as_tensor(np.asarray(_tree_get(stats, f"{npath}/mean")), dtype=torch.float64)
+            var = torch.as_tensor(np.asarray(_tree_get(stats, f"{npath}/var")), dtype=torch.float64)
+            g = scale / torch.sqrt(var + 1e-5)
+            w = w * g[:, None, None, None]
+            b = (b - mean) * g + nbias
+        if path == "mask_predictor/conv":
+            w, b = w * 0.25, b * 0.25
+        out[path] = _ConvP(
+            w.to(torch.float32).to(device).contiguous(memory_format=torch.channels_last),
+            b.to(torch.float32).to(device),
+        )
+    return out
+
+
+# ---------------------------------------------------------------------------------------
+# Forward pieces (NCHW-shaped channels_last tensors == NHWC memory)
+# ---------------------------------------------------------------------------------------
+def _conv(x, p: _ConvP, stride=1, padding=0):
+    return F.conv2d(x, p.w, p.b, stride=stride, padding=padding)
+
+
+def _cna(P, path, x, norm, stride=1, padding=None, act=True):
+    """ConvNormActivation (model.py:120-159): conv (+bias), norm, relu."""
+    p = P[f"{path}/layers_0"]
+    if padding is None:
+        padding = ((p.w.shape[2] - 1) // 2, (p.w.shape[3] - 1) // 2)
+    x = _conv(x, p, stride, padding)
+    if norm == "instance":  # nn.InstanceNorm(epsilon=1e-5, no scale/bias), model.py:706-707
+        x = F.instance_norm(x, eps=1e-5)
+    return F.relu(x) if act else x
+
+
+def _encoder(P, prefix, x, layers, block, norm, strides):
+    x = _cna(P, f"{prefix}/convnormrelu", x, norm, stride=strides[0])
+    for li, stride in enumerate(strides[1:], start=1):
+        for bi in range(2):
+            s = stride if bi == 0 else 1
+            base = f"{prefix}/layer{li}/layers_{bi}"
+            if block == "residual":  # model.py:162-184
+                y = _cna(P, f"{base}/convnormrelu1", x, norm, stride=s)
+                y = _cna(P, f"{base}/convnormrelu2", y, norm)
+            else:  # model.py:187-216
+                y = _cna(P, f"{base}/convnormrelu1", x, norm)
+                y = _cna(P, f"{base}/convnormrelu2", y, norm, stride=s)
+                y = _cna(P, f"{base}/convnormrelu3", y, norm)
+            if s != 1:
+                x = _cna(P, f"{base}/downsample", x, norm, stride=s, act=False)
+            x = F.relu(x + y)
+    return _conv(x, P[f"{prefix}/conv"])
+
+
+def _motion_encoder(P, cfg, flow, corr_features):
+    """model.py:260-290."""
+    me = "update_block/motion_encoder"
+    corr = _cna(P, f"{me}/convcorr1", corr_features, None)
+    if len(cfg.motion_encoder_corr_layers) == 2:
+        corr = _cna(P, f"{me}/convcorr2", corr, None)
+    fl = _cna(P, f"{me}/convflow1", flow, None)
+    fl = _cna(P, f"{me}/convflow2", fl, None)
+    cf = _cna(P, f"{me}/conv", torch.cat([corr, fl], dim=1), None)
+    return torch.cat([cf, flow], dim=1)
+
+
+def _conv_gru(P, path, h, x, padding):
+    """model.py:293-312."""
+    hx = torch.cat([h, x], dim=1)
+    z = torch.sigmoid(_conv(hx, P[f"{path}/convz"], padding=padding))
+    r = torch.sigmoid(_conv(hx, P[f"{path}/convr"], padding=padding))
+    q = torch.tanh(_conv(torch.cat([r * h, x], dim=1), P[f"{path}/convq"], padding=padding))
+    return (1 - z) * h + z * q
+
+
+class RAFT:
+    """Counterpart of the reference's ``RAFT`` module (model.py:513-605) + ``UpdateCell`` (484-510)."""
+
+    def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32"):
+        assert precision in ("tf32", "fp32")
+        self.config = config
+        self.corr_block = corr_block or CorrBlock(config.corr_block_num_levels, config.corr_block_radius)
+        expected = config.corr_block_num_levels * (2 * config.corr_block_radius + 1) ** 2
+        assert self.corr_block.out_channels == expected, (
+            f"corr_block.out_channels={self.corr_block.out_channels} does not match the motion encoder ({expected})")
+        # "tf32": cuDNN may use TF32 for the float32 convolutions — what XLA's GPU backend does
+        # by default for the reference.  "fp32": full-precision library convolutions.
+        self.precision = precision
+        self._prepared: Dict[Tuple[int, str], Any] = {}
+        self._graphs: Dict[Any, "_GraphRunner"] = {}
+
+    # Flax-style init: returns fresh variables (model.py:681-682)
+    def init(self, seed: int = 0) -> Tree:
+        return init_variables(self.config, seed)
+
+    def prepare(self, variables: Tree, device) -> Dict[str, _ConvP]:
+        key = (id(variables), str(device))
+        if key not in self._prepared:
+            # hold a reference to `variables` so its id cannot be reused while cached
+            self._prepared[key] = (variables, _prepare(self.config, variables, device))
+        return self._prepared[key][1]
+
+    # -- model.py:557-605 ---------------------------------------------------------------
+    def forward(self, P, image1: torch.Tensor, image2: torch.Tensor, num_flow_updates: int) -> torch.Tensor:
+        cfg = self.config
+        batch_size, h, w, _ = image1.shape
+        assert (h, w) == tuple(image2.shape[-3:-1]), "input images should have the same shape"
+        assert (h % 8 == 0) and (w % 8 == 0), "input image H and W should be divisible by 8"
+        prev = torch.backends.cudnn.allow_tf32
+        torch.backends.cudnn.allow_tf32 = self.precision == "tf32"
+        try:
+            x = torch.cat([image1, image2], dim=0).permute(0, 3, 1, 2)  # NHWC memory, NCHW view
+            fmaps = _encoder(P, "feature_encoder", x, cfg.feature_encoder_layers, cfg.feature_encoder_block,
+                             cfg.feature_encoder_norm, cfg.encoder_strides)
+            fmaps = fmaps.permute(0, 2, 3, 1).contiguous()  # (2B, h/8, w/8, D) NHWC
+            fmap1, fmap2 = fmaps[:batch_size], fmaps[batch_size:]
+            assert tuple(fmap1.shape[-3:-1]) == (h // 8, w // 8), "The feature encoder should downsample H and W by 8"
+
+            corr_pyramid = self.corr_block.build_pyramid(fmap1, fmap2)  # model.py:567
+
+            context_out = _encoder(P, "context_encoder", image1.permute(0, 3, 1, 2), cfg.context_encoder_layers,
+                                   cfg.context_encoder_block, cfg.context_encoder_norm, cfg.encoder_strides)
+            hid = cfg.recurrent_block_hidden_state_size
+            assert context_out.shape[1] - hid > 0
+            hidden_state = torch.tanh(context_out[:, :hid])
+            context = F.relu(context_out[:, hid:])
+
+            coords0 = make_coords_grid(batch_size, h // 8, w // 8, device=image1.device)
+            coords1 = coords0.clone()
+
+            flows = []
+            for _ in range(num_flow_updates):  # nn.scan(UpdateCell), model.py:589-603
+                coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context)
+                flows.append(up)
+            return torch.stack(flows, dim=0)
+        finally:
+            torch.backends.cudnn.allow_tf32 = prev
+
+    # -- model.py:494-510 ---------------------------------------------------------------
+    def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context):
+        cfg = self.config
+        corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
+        flow = (coords1 - coords0).permute(0, 3, 1, 2)
+        motion = _motion_encoder(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
+        x = torch.cat([context, motion], dim=1)
+        for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
+            hidden_state = _conv_gru(P, f"update_block/recurrent_block/convgru{gi}", hidden_state, x, pad)
+        d = F.relu(_conv(hidden_state, P["update_block/flow_head/conv1"], padding=1))
+        delta_flow = _conv(d, P["update_block/flow_head/conv2"], padding=1)
+        coords1 = coords1 + delta_flow.permute(0, 2, 3, 1)
+        up_mask = None
+        if cfg.use_mask_predictor:  # model.py:377-400
+            m = _cna(P, "mask_predictor/convrelu", hidden_state, None)
+            up_mask = _conv(m, P["mask_predictor/conv"]).permute(0, 2, 3, 1).contiguous()
+        upsampled = upsample_flow(flow=(coords1 - coords0).contiguous(), up_mask=up_mask)
+        return coords1, hidden_state, upsampled
+
+    # -- public entry, mirrors flax Module.apply -------------------------------------------
+    def apply(self, variables: Tree, image1, image2, train: bool = False, num_flow_updates: int = 12,
+              device=None, use_cuda_graph: bool = True) -> torch.Tensor:
+        """Returns the ``num_flow_updates`` upsampled flows, shape (N, B, H, W, 2), on the GPU.
+
+        ``image1`` / ``image2``: NHWC float32 in [-1, 1]; torch CUDA tensors, or host arrays
+        (numpy / CPU tensors), which are copied to ``device`` (default: current CUDA device).
+        With ``use_cuda_graph`` the whole forward is captured once per (shape, N) and replayed.
+        """
+        if train:
+            raise NotImplementedError("inference only: the sm_100a kernels define no VJP (train=True unsupported)")
+        dev = torch.device(device) if device is not None else None
+        img1 = _to_device(image1, dev)
+        img2 = _to_device(image2, img1.device)
+        assert img1.ndim == 4 and img1.shape[-1] == 3, "images must be (B, H, W, 3)"
+        P = self.prepare(variables, img1.device)
+        if not use_cuda_graph:
+            with torch.no_grad():
+                return self.forward(P, img1, img2, num_flow_updates)
+        key = (id(variables), str(img1.device), tuple(img1.shape), num_flow_updates)
+        runner = self._graphs.get(key)
+        if runner is None:
+            runner = _GraphRunner(self, P, tuple(img1.shape), img1.device, num_flow_updates)
+            self._graphs[key] = runner
+        return runner(img1, img2).clone()
+
+    def runner(self, variables: Tree, batch_size: int, height: int, width: int, num_flow_updates: int,
+               device=None) -> "_GraphRunner":
+        """The captured forward for one shape, with static input/output buffers (no clone)."""
+        dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        P = self.prepare(variables, dev)
+        shape = (batch_size, height, width, 3)
+        key = (id(variables), str(dev), shape, num_flow_updates)
+        if key not in self._graphs:
+            self._graphs[key] = _GraphRunner(self, P, shape, dev, num_flow_updates)
+        return self._graphs[key]
+
+
+def _to_device(x, device) -> torch.Tensor:
+    if isinstance(x, torch.Tensor):
+        t = x
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float32)))
+    if t.dtype != torch.float32:
+        t = t.to(torch.float32)
+    if t.is_cuda and (device is None or t.device == device):
+        return t.contiguous()
+    if device is None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("jax_raft_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        device = torch.device("cuda", torch.cuda.current_device())
+    return t.to(device, non_blocking=True).contiguous()
+
+
+class _GraphRunner:
+    """One CUDA graph of the whole forward for a fixed (B, H, W, N): static buffers, replay."""
+
+    def __init__(self, model: RAFT, P, shape, device, num_flow_updates: int):
+        self.device = device
+        self.image1 = torch.zeros(shape, dtype=torch.float32, device=device)
+        self.image2 = torch.zeros(shape, dtype=torch.float32, device=device)
+        with torch.cuda.device(device), torch.no_grad():
+            side = torch.cuda.Stream(device=device)
+            side.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(side):
+                for _ in range(2):  # warm-up: cuDNN autotune, lazy module loading
+                    model.forward(P, self.image1, self.image2, num_flow_updates)
+            torch.cuda.current_stream(device).wait_stream(side)
+            torch.cuda.synchronize(device)
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self.flows = model.forward(P, self.image1, self.image2, num_flow_updates)
+
+    def __call__(self, image1: torch.Tensor, image2: torch.Tensor) -> torch.Tensor:
+        self.image1.copy_(image1, non_blocking=True)
+        self.image2.copy_(image2, non_blocking=True)
+        self.graph.replay()
+        return self.flows
+
+
+# ---------------------------------------------------------------------------------------
+# Factories (model.py:608-767)
+# ---------------------------------------------------------------------------------------
+def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs):
+    corr_block = kwargs.pop("corr_block", None)
+    precision = kwargs.pop("precision", "tf32")
+    if kwargs:
+        raise TypeError(
+            f"unsupported keyword(s) {sorted(kwargs)}: this build replaces the correlation block "
+            "(corr_block=) only; encoders, update block and mask predictor are fixed by the architecture")
+    if pretrained:
+        # model.py:684-689 downloads a msgpack from GitHub; this environment has no network.
+        raise RuntimeError(
+            "pretrained=True needs network access (model.py:17-21, 684-689); load a converted checkpoint with "
+            "variables_from_torch_state_dict(torch.load(path)) instead")
+    model = RAFT(cfg, corr_block=corr_block, precision=precision)
+    return model, model.init(seed)
+
+
+def raft_large(*, pretrained: bool = False, **kwargs):
+    """RAFT (large).  Returns ``(model, variables)`` like model.py:694-729."""
+    return _raft(RAFT_LARGE, pretrained=pretrained, **kwargs)
+
+
+def raft_small(*, pretrained: bool = False, **kwargs):
+    """RAFT (small).  Returns ``(model, variables)`` like model.py:732-767."""
+    return _raft(RAFT_SMALL, pretrained=pretrained, **kwargs)

@@ -1,0 +1,57 @@
+"""alt_corr (family 2b): pooled-fmap2 levels and the on-the-fly lookup against the oracle and
+against the materialised-volume path.  Index work is shared with the volume lookup (bit-exact
+there); values differ by the float32 summation order of the dot products: tolerance 1e-4 of the
+correlation scale (north-star: 1e-3 relative)."""
+
+import numpy as np
+import pytest
+import torch
+
+import jax_raft_b200 as J
+from oracle import corr_oracle as O
+
+pytestmark = pytest.mark.gpu
+F32 = np.float32
+
+
+def _scale_close(got, ref, tol=1e-4):
+    rms = float(np.sqrt(np.mean(ref.astype(np.float64) ** 2))) or 1.0
+    assert float(np.abs(got - ref).max()) <= tol * max(rms, 1.0), float(np.abs(got - ref).max())
+
+
+@pytest.mark.parametrize("shape,r", [((1, 16, 16, 128), 4), ((2, 19, 21, 128), 3), ((1, 23, 31, 256), 4)])
+def test_against_oracle(cuda, lib, shape, r):
+    b, h, w, d = shape
+    rng = np.random.default_rng(h)
+    f1 = (rng.standard_normal((b, h, w, d)) * 1.45).astype(F32)
+    f2 = (rng.standard_normal((b, h, w, d)) * 1.45).astype(F32)
+    coords = O.make_coords_grid(b, h, w) + rng.uniform(-8, 8, (b, h, w, 2)).astype(F32)
+    alt = J.AltCorrBlock(4, r)
+    pyr = alt.build_pyramid(torch.from_numpy(f1).to(cuda), torch.from_numpy(f2).to(cuda))
+    ref_levels = O.pool_fmap2(f2)
+    for l in range(1, 4):  # pooled fmap2: same ((a+b)+(c+d))/4 order as the oracle -> exact
+        np.testing.assert_array_equal(pyr[1][l].cpu().numpy(), ref_levels[l])
+    out = alt.index_pyramid(pyr, torch.from_numpy(coords).to(cuda)).cpu().numpy()
+    ref = O.index_pyramid(O.build_pyramid(f1, f2), coords, r)
+    _scale_close(out, ref)
+    # and against the volume path on the GPU
+    cb = J.CorrBlock(4, r, kernel="simt")
+    vol = cb.index_pyramid(cb.build_pyramid(torch.from_numpy(f1).to(cuda), torch.from_numpy(f2).to(cuda)),
+                           torch.from_numpy(coords).to(cuda)).cpu().numpy()
+    _scale_close(out, vol)
+
+
+def test_query_row_band(cuda, lib):
+    rng = np.random.default_rng(8)
+    b, h, w, d = 1, 20, 24, 128
+    f1 = rng.standard_normal((b, h, w, d)).astype(F32)
+    f2 = rng.standard_normal((b, h, w, d)).astype(F32)
+    coords = O.make_coords_grid(b, h, w) + rng.uniform(-6, 6, (b, h, w, 2)).astype(F32)
+    alt = J.AltCorrBlock(4, 4)
+    t1, t2, tc = (torch.from_numpy(x).to(cuda) for x in (f1, f2, coords))
+    full = alt.index_pyramid(alt.build_pyramid(t1, t2), tc)
+    band = alt.index_pyramid(alt.build_pyramid(t1, t2, query_rows=(7, 15)), tc[:, 7:15].contiguous())
+    assert torch.equal(band, full[:, 7:15])
+    # already-sliced fmap1 (what a row-sharded rank holds)
+    band2 = alt.index_pyramid(alt.build_pyramid(t1[:, 7:15].contiguous(), t2, query_rows=(7, 15)), tc[:, 7:15].contiguous())
+    assert torch.equal(band2, band)

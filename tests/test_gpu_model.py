@@ -1,0 +1,69 @@
+"""End-to-end: model.apply against torchvision's RAFT on the CPU (fp32) with shared random-init
+weights (torch.manual_seed(0)) — the implementation the reference was validated against
+(validate_sintel.py:257-263).  Bar: mean EPE <= 0.01 px."""
+
+import numpy as np
+import pytest
+import torch
+
+import jax_raft_b200 as J
+
+pytestmark = pytest.mark.gpu
+
+
+def _epe(a, b):
+    return float(np.sqrt(((a - b) ** 2).sum(-1)).mean())
+
+
+def _torchvision_cpu(name, img1, img2, iters):
+    import torchvision.models.optical_flow as tvof
+
+    torch.manual_seed(0)
+    net = getattr(tvof, name)(weights=None).eval()
+    with torch.no_grad():
+        flows = net(torch.from_numpy(img1).permute(0, 3, 1, 2), torch.from_numpy(img2).permute(0, 3, 1, 2),
+                    num_flow_updates=iters)
+    return net, [f.permute(0, 2, 3, 1).numpy() for f in flows]
+
+
+@pytest.mark.parametrize("name", ["raft_small", "raft_large"])
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_flow_matches_cpu_reference(cuda, lib, golden, name, precision):
+    g = golden(f"e2e_{name}")
+    img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
+    net, ref_flows = _torchvision_cpu(name, img1, img2, iters)
+    # the live CPU run reproduces the committed golden flow (same seed, same torch build)
+    assert _epe(ref_flows[-1], g["flow"]) < 1e-3
+    variables = J.variables_from_torch_state_dict(net.state_dict())
+    model, _ = getattr(J, name)(precision=precision)
+    flows = model.apply(variables, img1, img2, train=False, num_flow_updates=iters, use_cuda_graph=False)
+    assert flows.shape == (iters, 1, 128, 160, 2)
+    got = flows.cpu().numpy()
+    for i in (0, iters - 1):
+        assert _epe(got[i], ref_flows[i]) <= 0.01, (name, precision, i, _epe(got[i], ref_flows[i]))
+    assert _epe(got[-1], g["flow"]) <= 0.01
+    # CUDA-graph replay gives the same result as eager, twice in a row
+    a = model.apply(variables, img1, img2, num_flow_updates=iters)
+    b = model.apply(variables, img1, img2, num_flow_updates=iters)
+    assert torch.equal(a, b)
+    assert _epe(a.cpu().numpy()[-1], got[-1]) <= 1e-3
+
+
+def test_alt_corr_block_drops_in(cuda, lib, golden):
+    g = golden("e2e_raft_large")
+    img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
+    net, ref_flows = _torchvision_cpu("raft_large", img1, img2, iters)
+    variables = J.variables_from_torch_state_dict(net.state_dict())
+    model, _ = J.raft_large(corr_block=J.AltCorrBlock(4, 4), precision="fp32")
+    flows = model.apply(variables, img1, img2, num_flow_updates=iters, use_cuda_graph=False)
+    assert _epe(flows.cpu().numpy()[-1], ref_flows[-1]) <= 0.01
+
+
+def test_apply_checks_inputs(cuda, lib):
+    model, variables = J.raft_small()
+    x = np.zeros((1, 100, 128, 3), np.float32)
+    with pytest.raises(AssertionError, match="divisible by 8"):
+        model.apply(variables, x, x, use_cuda_graph=False)
+    with pytest.raises(AssertionError, match="same shape"):
+        model.apply(variables, np.zeros((1, 128, 128, 3), np.float32), np.zeros((1, 128, 136, 3), np.float32),
+                    use_cuda_graph=False)

@@ -1,0 +1,90 @@
+"""Host-side mirror of the reference API: variable tree, converter rules, argument checks.  No GPU."""
+
+import numpy as np
+import pytest
+import torch
+
+import jax_raft_b200 as J
+from jax_raft_b200.model import _tree_items
+
+
+@pytest.mark.parametrize("name", ["raft_large", "raft_small"])
+def test_variable_tree_matches_converted_torchvision_checkpoint(name):
+    import torchvision.models.optical_flow as tvof
+
+    model, variables = getattr(J, name)()
+    assert set(variables) == {"params", "batch_stats"}
+    tv = getattr(tvof, name)(weights=None)
+    conv = J.variables_from_torch_state_dict(tv.state_dict())  # convert_checkpoint.py rules
+    mine = dict(_tree_items(variables))
+    ref = dict(_tree_items(conv))
+    assert set(mine) == set(ref)
+    for k in mine:
+        assert np.asarray(mine[k]).shape == np.asarray(ref[k]).shape, k
+    # e.g. SURVEY.md §8c: (256,324,1,1) -> params/update_block/motion_encoder/convcorr1/layers_0/kernel (1,1,324,256)
+    if name == "raft_large":
+        k = variables["params"]["update_block"]["motion_encoder"]["convcorr1"]["layers_0"]["kernel"]
+        assert k.shape == (1, 1, 324, 256)
+        assert "mean" in variables["batch_stats"]["context_encoder"]["convnormrelu"]["layers_1"]
+    # round trip
+    sd = {k: v for k, v in tv.state_dict().items() if not k.endswith("num_batches_tracked")}
+    back = J.torch_state_dict_from_variables(conv)
+    assert set(back) == set(sd)
+    assert all(torch.equal(back[k], sd[k]) for k in sd)
+
+
+def test_factories_keep_reference_signature():
+    model, variables = J.raft_large(pretrained=False)
+    assert model.corr_block.out_channels == 4 * 81 and model.corr_block.radius == 4
+    small, _ = J.raft_small()
+    assert small.corr_block.out_channels == 4 * 49 and small.config.use_mask_predictor is False
+    with pytest.raises(RuntimeError, match="network"):
+        J.raft_large(pretrained=True)
+    with pytest.raises(TypeError):
+        J.raft_large(not_a_kwarg=1)
+    alt = J.AltCorrBlock(4, 4)
+    m2, _ = J.raft_large(corr_block=alt)  # the reference's injection point, model.py:643-644
+    assert m2.corr_block is alt
+    with pytest.raises(AssertionError):
+        J.raft_large(corr_block=J.CorrBlock(4, 3))  # out_channels must match the motion encoder
+    with pytest.raises(NotImplementedError):
+        model.apply(variables, np.zeros((1, 64, 64, 3), np.float32), np.zeros((1, 64, 64, 3), np.float32), train=True)
+
+
+def test_corr_block_asserts_like_reference_and_has_no_cpu_fallback():
+    cb = J.CorrBlock(4, 4)
+    assert cb.out_channels == 324
+    with pytest.raises(AssertionError, match="same shapes"):
+        cb.build_pyramid(torch.zeros(1, 16, 16, 8), torch.zeros(1, 16, 17, 8))
+    with pytest.raises(AssertionError, match="too small"):
+        cb.build_pyramid(torch.zeros(1, 15, 16, 8), torch.zeros(1, 15, 16, 8))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        cb.build_pyramid(torch.zeros(1, 16, 16, 8), torch.zeros(1, 16, 16, 8))
+    with pytest.raises(AssertionError):
+        cb.index_pyramid([torch.zeros(4, 16, 16, 1)] * 4, torch.zeros(1, 2, 2, 3))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        J.upsample_flow(torch.zeros(1, 4, 4, 2), torch.zeros(1, 4, 4, 576))
+    with pytest.raises(AssertionError):
+        J.upsample_flow(torch.zeros(1, 4, 4, 2), torch.zeros(1, 4, 4, 575))
+
+
+def test_bilinear_branch_and_coords_grid_on_cpu():
+    from oracle import corr_oracle as O
+
+    flow = torch.randn(2, 5, 7, 2)
+    up = J.upsample_flow(flow)  # raft_small path: host-framework code (model.py:79-83)
+    np.testing.assert_allclose(up.numpy(), O.upsample_flow(flow.numpy()), rtol=1e-4, atol=1e-4)
+    g = J.make_coords_grid(2, 3, 4, device="cpu")
+    np.testing.assert_array_equal(g.numpy(), O.make_coords_grid(2, 3, 4))
+
+
+def test_product_package_does_not_import_the_oracle():
+    import os
+    import re
+
+    pkg = os.path.dirname(J.__file__)
+    for root, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")):
+                text = open(os.path.join(root, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
