@@ -97,7 +97,7 @@ class CorrBlock:
                 rc = lib.raftk_corr_pyramid(fmap1.data_ptr(), fmap2.data_ptr(), _lib.ptr_array(levels),
                                             self.num_levels, b, nq, h, w, d, scratch.data_ptr(), nbytes, stream)
                 _lib.check("raftk_corr_pyramid", rc)
-                _lib.count_launch(self.num_levels)  # interim: forwards to the simt kernels
+                _lib.count_launch(2 + max(0, self.num_levels - 4))  # bf16 split + tcgen05 GEMM (+ pools past level 3)
                 # scratch was allocated on the launching stream, so the caching allocator
                 # cannot hand it to anyone before the kernel has consumed it.
         return levels

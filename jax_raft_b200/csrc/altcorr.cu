@@ -124,11 +124,12 @@ __global__ void __launch_bounds__(kAltWarps * 32) altcorr_lookup_kernel(const Al
 extern "C" int raftk_altcorr_pool_fmap2(float* const* f2_levels, int num_levels, int B, int h, int w,
                                         int D, void* stream) {
   using namespace raftk;
-  if (!f2_levels) return RAFTK_ERR_NULL;
   if (num_levels < 1 || num_levels > RAFTK_MAX_LEVELS || B < 0 || h <= 0 || w <= 0 || D <= 0)
     return RAFTK_ERR_SHAPE;
   if (!levels_fit(h, w, num_levels)) return RAFTK_ERR_TOO_SMALL;
   if (D % 4) return RAFTK_ERR_UNSUPPORTED;
+  if (B == 0) return RAFTK_OK;  // empty batch: pointers may be NULL
+  if (!f2_levels) return RAFTK_ERR_NULL;
   for (int l = 0; l < num_levels; ++l) {
     if (!f2_levels[l]) return RAFTK_ERR_NULL;
     if ((uintptr_t)f2_levels[l] & 15) return RAFTK_ERR_ALIGN;
@@ -149,12 +150,13 @@ extern "C" int raftk_altcorr_lookup(const float* fmap1, const float* const* f2_l
                                     const float* coords, float* out, int B, int nq, int h, int w,
                                     int D, int radius, void* stream) {
   using namespace raftk;
-  if (!fmap1 || !f2_levels || !coords || !out) return RAFTK_ERR_NULL;
   if (num_levels < 1 || num_levels > RAFTK_MAX_LEVELS || B < 0 || nq < 0 || h <= 0 || w <= 0 ||
       D <= 0 || radius < 0)
     return RAFTK_ERR_SHAPE;
   if ((h >> (num_levels - 1)) < 1 || (w >> (num_levels - 1)) < 1) return RAFTK_ERR_TOO_SMALL;
   if (D % 128 || D > 128 * kAltMaxD4 || radius > 7) return RAFTK_ERR_UNSUPPORTED;
+  if ((long long)B * nq == 0) return RAFTK_OK;  // empty batch: pointers may be NULL
+  if (!fmap1 || !f2_levels || !coords || !out) return RAFTK_ERR_NULL;
   if ((uintptr_t)fmap1 & 15) return RAFTK_ERR_ALIGN;
   AltParams p{};
   for (int l = 0; l < num_levels; ++l) {

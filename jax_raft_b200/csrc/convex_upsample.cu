@@ -80,8 +80,9 @@ convex_upsample_kernel(const float* __restrict__ flow, const float* __restrict__
 extern "C" int raftk_convex_upsample(const float* flow, const float* mask, float* out, int B,
                                      int h, int w, void* stream) {
   using namespace raftk;
-  if (!flow || !mask || !out) return RAFTK_ERR_NULL;
   if (B < 0 || h <= 0 || w <= 0) return RAFTK_ERR_SHAPE;
+  if (B == 0) return RAFTK_OK;  // empty batch: pointers may be NULL
+  if (!flow || !mask || !out) return RAFTK_ERR_NULL;
   if (((uintptr_t)flow & 7) || ((uintptr_t)mask & 7) || ((uintptr_t)out & 15)) return RAFTK_ERR_ALIGN;
   const long long npix = (long long)B * h * w;
   if (npix == 0) return RAFTK_OK;

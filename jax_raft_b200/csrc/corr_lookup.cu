@@ -78,12 +78,12 @@ __global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const Lo
 extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, const float* coords,
                                  float* out, int Q, int h, int w, int radius, void* stream) {
   using namespace raftk;
-  if (!levels || !coords || !out) return RAFTK_ERR_NULL;
   if (Q < 0 || h <= 0 || w <= 0 || radius < 0 || num_levels < 1 || num_levels > RAFTK_MAX_LEVELS)
     return RAFTK_ERR_SHAPE;
   if ((h >> (num_levels - 1)) < 1 || (w >> (num_levels - 1)) < 1) return RAFTK_ERR_TOO_SMALL;
   if (radius > 7) return RAFTK_ERR_UNSUPPORTED;
-  if (Q == 0) return RAFTK_OK;
+  if (Q == 0) return RAFTK_OK;  // empty batch: nothing to read, pointers may be NULL
+  if (!levels || !coords || !out) return RAFTK_ERR_NULL;
   LookupParams p{};
   for (int l = 0; l < num_levels; ++l) {
     if (!levels[l]) return RAFTK_ERR_NULL;

@@ -77,10 +77,11 @@ pool2x2_kernel(const float* __restrict__ in, float* __restrict__ out, long long 
 
 int check_pyramid_args(const float* fmap1, const float* fmap2, float* const* levels, int num_levels,
                        int B, int nq, int h, int w, int D) {
-  if (!fmap1 || !fmap2 || !levels) return RAFTK_ERR_NULL;
   if (num_levels < 1 || num_levels > RAFTK_MAX_LEVELS || B < 0 || nq < 0 || h <= 0 || w <= 0 || D <= 0)
     return RAFTK_ERR_SHAPE;
   if (!levels_fit(h, w, num_levels)) return RAFTK_ERR_TOO_SMALL;
+  if (B == 0 || nq == 0) return RAFTK_OK;  // empty batch: pointers may be NULL
+  if (!fmap1 || !fmap2 || !levels) return RAFTK_ERR_NULL;
   for (int l = 0; l < num_levels; ++l)
     if (!levels[l]) return RAFTK_ERR_NULL;
   return RAFTK_OK;
