@@ -49,9 +49,10 @@ constexpr int BN = PW * PH;       // 256 accumulator columns
 constexpr int KBLK = 64;          // bf16 per 128-byte swizzle row
 constexpr int A_BLOCK_BYTES = BM * 128;  // 16 KB: 128 rows x 64 bf16
 constexpr int B_STAGE_BYTES = BN * 128;  // 32 KB: 256 rows x 64 bf16
-constexpr int STAGING_PER_WARP = 4096 + 2048 + 1024 + 512;  // level 0..3 row blocks
+constexpr int NUM_EPI_WARPS = 8;         // two per TMEM lane quarter: patch rows 0-3 and 4-7
+constexpr int STAGING_PER_WARP = 4096;   // one 32-query x 32-float row block, reused by every level
 constexpr int MAX_STAGES = 6;
-constexpr int NUM_THREADS = 256;
+constexpr int NUM_THREADS = 128 + 32 * NUM_EPI_WARPS;
 constexpr int SMEM_LIMIT = 232448;  // 227 KB
 
 struct Params {
@@ -184,34 +185,65 @@ split_bf16_kernel(const float* __restrict__ f1, const float* __restrict__ f2, __
 }
 
 // ---- epilogue helpers ---------------------------------------------------------------------
-// Store one staged row block (32 queries x WIDTH floats) to level memory: lanes sweep the
-// block row-major so every warp store covers whole 4*WIDTH-byte row segments.
+// Store one staged row block (32 queries x WIDTH floats) to level memory.  `row` points at
+// (first query of the block, row Y, column X0) of the level; `slab` = floats per query slab;
+// `cols` = level columns left from X0.  Lanes sweep the block row-major, so every warp store
+// covers whole 4*WIDTH-byte row segments (4 queries x 128 B for level 0).
 template <int WIDTH, bool SWIZZLED>
-__device__ __forceinline__ void store_row_block(const float* S, float* lvl, int lh, int lw, bool vec_ok,
-                                                long long q_first, int q_valid, int Y, int X0, int lane) {
-  constexpr int CH = WIDTH / 4;  // 16-byte chunks per query row
+__device__ __forceinline__ void store_row_block(const float* S, float* row, long long slab, int cols, bool vec_ok,
+                                                int q_valid, int lane) {
+  constexpr int CH = WIDTH / 4;   // 16-byte chunks per query row
+  constexpr int QPI = 32 / CH;    // queries covered by one warp store
   if (vec_ok) {
+    const int qq0 = lane / CH, c = lane % CH;
+    if (4 * c >= cols) return;
+    // all shared-memory reads first, then all global stores: the two never alias, and batching
+    // keeps CH independent loads in flight instead of a load->store->load chain
+    float4 v[CH];
 #pragma unroll
-    for (int i = 0; i < 32 * CH / 32; ++i) {
-      const int idx = i * 32 + lane;
-      const int qq = idx / CH, c = idx % CH;
-      const int X = X0 + 4 * c;
-      if (qq < q_valid && X < lw) {
-        const int pc = SWIZZLED ? (c ^ (qq & 7)) : c;
-        const float4 v = *reinterpret_cast<const float4*>(S + qq * WIDTH + pc * 4);
-        st_na_f4(lvl + ((q_first + qq) * lh + Y) * (long long)lw + X, v);
-      }
+    for (int i = 0; i < CH; ++i) {
+      const int qq = qq0 + i * QPI;
+      const int pc = SWIZZLED ? (c ^ (qq & 7)) : c;
+      v[i] = *reinterpret_cast<const float4*>(S + qq * WIDTH + pc * 4);
+    }
+    float* ptr = row + qq0 * slab + 4 * c;
+#pragma unroll
+    for (int i = 0; i < CH; ++i) {
+      if (qq0 + i * QPI < q_valid) st_na_f4(ptr, v[i]);
+      ptr += QPI * slab;
     }
   } else {
     for (int idx = lane; idx < 32 * WIDTH; idx += 32) {
       const int qq = idx / WIDTH, x = idx % WIDTH;
-      if (qq < q_valid && X0 + x < lw) {
+      if (qq < q_valid && x < cols) {
         const int c = x >> 2;
         const int pc = SWIZZLED ? (c ^ (qq & 7)) : c;
-        lvl[((q_first + qq) * lh + Y) * (long long)lw + X0 + x] = S[qq * WIDTH + pc * 4 + (x & 3)];
+        row[qq * slab + x] = S[qq * WIDTH + pc * 4 + (x & 3)];
       }
     }
   }
+}
+
+// Stage WIDTH floats per lane (plain row-major [lane][WIDTH]) and store them as level-l row Y.
+template <int WIDTH>
+__device__ __forceinline__ void stage_and_store(float* S, const float* v, float* lvl, int lh, int lw, bool vec_ok,
+                                                long long q_first, int q_valid, int Y, int X0, int lane) {
+#pragma unroll
+  for (int c = 0; c < WIDTH / 4; ++c)
+    *reinterpret_cast<float4*>(S + lane * WIDTH + c * 4) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+  __syncwarp();
+  if (Y < lh && q_valid > 0) {
+    const long long slab = (long long)lh * lw;
+    store_row_block<WIDTH, false>(S, lvl + q_first * slab + (long long)Y * lw + X0, slab, lw - X0, vec_ok, q_valid, lane);
+  }
+  __syncwarp();
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int threads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
 // out[i] = ((a[2i] + a[2i+1]) + (b[2i] + b[2i+1])) / 4 — the reference's pooling of the level below
@@ -226,13 +258,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const Params p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment for the 128B-swizzle tiles; plain offset arithmetic keeps the pointers
+  // in the shared address space (LDS/STS instead of generic LD/ST)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int kblocks = p.D / KBLK;            // k-blocks per plane
   const int a_blocks = 2 * kblocks;          // hi blocks then mid blocks
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + a_blocks * A_BLOCK_BYTES;
   uint8_t* smem_stage = smem_b + p.num_stages * B_STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + 4 * STAGING_PER_WARP);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + NUM_EPI_WARPS * STAGING_PER_WARP);
   uint64_t* b_full = bars;                    // [MAX_STAGES]
   uint64_t* b_empty = bars + MAX_STAGES;      // [MAX_STAGES]
   uint64_t* a_full = bars + 2 * MAX_STAGES;   // [1]
@@ -252,7 +286,7 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     mbar_init(a_empty, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[i], NUM_EPI_WARPS);  // one arrival per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -364,11 +398,17 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
-    const int quarter = warp - 4;  // TMEM lanes [32*quarter, 32*quarter + 32)
-    float* S0 = reinterpret_cast<float*>(smem_stage + quarter * STAGING_PER_WARP);
-    float* S1 = S0 + 1024;
-    float* S2 = S1 + 512;
-    float* S3 = S2 + 256;
+    // Eight warps: quarter = TMEM lane quarter this warp may read (hardware: warp id % 4),
+    // half = which four patch rows (two level-1 rows, one level-2 row) it owns.
+    const int quarter = warp & 3;
+    const int half = (warp - 4) >> 2;
+    float* S = reinterpret_cast<float*>(smem_stage + (warp - 4) * STAGING_PER_WARP);
+    // The level-2 row of the upper half (rows 0-3) travels to the lower-half warp through the
+    // last 1 KB of the LOWER warp's staging tile, which that warp only touches while staging
+    // level-0 rows.  bar_free: "lower warp is past its level-0 rows, write now";
+    // bar_ready: "upper row written".
+    float* X = reinterpret_cast<float*>(smem_stage + (4 + quarter) * STAGING_PER_WARP) + 768;
+    const int bar_ready = 1 + quarter, bar_free = 5 + quarter;
     int buf = 0;
     uint32_t acc_phase = 0;
     for (long long t = t_begin; t < t_end; ++t) {
@@ -382,87 +422,75 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
       mbar_wait(&acc_full[buf], acc_phase);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN;
+      const uint32_t taddr =
+          tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 4 * PW);
 
-      float l1_prev[16], l2_prev[8];
+      float l1[2][16];
 #pragma unroll
-      for (int rp = 0; rp < PH / 2; ++rp) {
-        float r0[32], r1[32];
-        tmem_ld_32x32(taddr + (2 * rp) * PW, r0);
-        tmem_ld_32x32(taddr + (2 * rp + 1) * PW, r1);
+      for (int rp = 0; rp < 2; ++rp) {
+        float r[2][32];
+        tmem_ld_32x32(taddr + (2 * rp) * PW, r[0]);
+        tmem_ld_32x32(taddr + (2 * rp + 1) * PW, r[1]);
         tmem_ld_wait();
-        if (rp == PH / 2 - 1) {
-          // the accumulator is now entirely in registers: hand it back to the MMA warp
+        if (rp == 1) {
+          // this warp's share of the accumulator is in registers: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&acc_empty[buf]);
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          r0[i] *= p.scale;
-          r1[i] *= p.scale;
+          r[0][i] *= p.scale;
+          r[1][i] *= p.scale;
         }
-        // ---- level 0, two rows ----
+        // ---- level 0: two rows through the swizzled staging tile ----
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          const float* r = half ? r1 : r0;
-          const int Y = y0 + 2 * rp + half;
+        for (int hrow = 0; hrow < 2; ++hrow) {
+          const int Y = y0 + 4 * half + 2 * rp + hrow;
 #pragma unroll
           for (int c = 0; c < 8; ++c)
-            *reinterpret_cast<float4*>(S0 + lane * 32 + ((c ^ (lane & 7)) * 4)) =
-                make_float4(r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
+            *reinterpret_cast<float4*>(S + lane * 32 + ((c ^ (lane & 7)) * 4)) =
+                make_float4(r[hrow][4 * c], r[hrow][4 * c + 1], r[hrow][4 * c + 2], r[hrow][4 * c + 3]);
           __syncwarp();
-          if (Y < p.lh[0] && q_valid > 0)
-            store_row_block<32, true>(S0, p.level[0], p.lh[0], p.lw[0], p.vec_ok[0], q_first, q_valid, Y, x0, lane);
+          if (Y < p.lh[0] && q_valid > 0) {
+            const long long slab = (long long)p.lh[0] * p.lw[0];
+            store_row_block<32, true>(S, p.level[0] + q_first * slab + (long long)Y * p.lw[0] + x0, slab,
+                                      p.lw[0] - x0, p.vec_ok[0], q_valid, lane);
+          }
           __syncwarp();
         }
+        // ---- level 1 row ----
         if (p.L > 1) {
-          // ---- level 1 row rp ----
-          float l1[16];
-          pool_rows<16>(r0, r1, l1);
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-            *reinterpret_cast<float4*>(S1 + lane * 16 + c * 4) =
-                make_float4(l1[4 * c], l1[4 * c + 1], l1[4 * c + 2], l1[4 * c + 3]);
-          __syncwarp();
-          const int Y1 = (y0 >> 1) + rp;
-          if (Y1 < p.lh[1] && q_valid > 0)
-            store_row_block<16, false>(S1, p.level[1], p.lh[1], p.lw[1], p.vec_ok[1], q_first, q_valid, Y1, x0 >> 1, lane);
-          __syncwarp();
-          if (p.L > 2) {
-            if (rp & 1) {
-              // ---- level 2 row rp/2 ----
-              float l2[8];
-              pool_rows<8>(l1_prev, l1, l2);
-#pragma unroll
-              for (int c = 0; c < 2; ++c)
-                *reinterpret_cast<float4*>(S2 + lane * 8 + c * 4) =
-                    make_float4(l2[4 * c], l2[4 * c + 1], l2[4 * c + 2], l2[4 * c + 3]);
-              __syncwarp();
-              const int Y2 = (y0 >> 2) + (rp >> 1);
-              if (Y2 < p.lh[2] && q_valid > 0)
-                store_row_block<8, false>(S2, p.level[2], p.lh[2], p.lw[2], p.vec_ok[2], q_first, q_valid, Y2, x0 >> 2, lane);
-              __syncwarp();
-              if (p.L > 3) {
-                if (rp == 3) {
-                  // ---- level 3 row ----
-                  float l3[4];
-                  pool_rows<4>(l2_prev, l2, l3);
-                  *reinterpret_cast<float4*>(S3 + lane * 4) = make_float4(l3[0], l3[1], l3[2], l3[3]);
-                  __syncwarp();
-                  const int Y3 = y0 >> 3;
-                  if (Y3 < p.lh[3] && q_valid > 0)
-                    store_row_block<4, false>(S3, p.level[3], p.lh[3], p.lw[3], p.vec_ok[3], q_first, q_valid, Y3, x0 >> 3, lane);
-                  __syncwarp();
-                } else {
-#pragma unroll
-                  for (int i = 0; i < 8; ++i) l2_prev[i] = l2[i];
-                }
-              }
-            } else {
-#pragma unroll
-              for (int i = 0; i < 16; ++i) l1_prev[i] = l1[i];
-            }
+          pool_rows<16>(r[0], r[1], l1[rp]);
+          stage_and_store<16>(S, l1[rp], p.level[1], p.lh[1], p.lw[1], p.vec_ok[1], q_first, q_valid,
+                              (y0 >> 1) + 2 * half + rp, x0 >> 1, lane);
+        }
+      }
+      if (p.L > 2) {
+        // ---- level 2 row ----
+        float l2[8];
+        pool_rows<8>(l1[0], l1[1], l2);
+        stage_and_store<8>(S, l2, p.level[2], p.lh[2], p.lw[2], p.vec_ok[2], q_first, q_valid, (y0 >> 2) + half,
+                           x0 >> 2, lane);
+        if (p.L > 3) {
+          // ---- level 3 row: needs the level-2 rows of both halves ----
+          if (half == 0) {
+            named_bar_sync(bar_free, 64);
+            *reinterpret_cast<float4*>(X + lane * 8) = make_float4(l2[0], l2[1], l2[2], l2[3]);
+            *reinterpret_cast<float4*>(X + lane * 8 + 4) = make_float4(l2[4], l2[5], l2[6], l2[7]);
+            named_bar_arrive(bar_ready, 64);
+          } else {
+            named_bar_arrive(bar_free, 64);
+            named_bar_sync(bar_ready, 64);
+            float up[8], l3[4];
+            const float4 u0 = *reinterpret_cast<const float4*>(X + lane * 8);
+            const float4 u1 = *reinterpret_cast<const float4*>(X + lane * 8 + 4);
+            up[0] = u0.x; up[1] = u0.y; up[2] = u0.z; up[3] = u0.w;
+            up[4] = u1.x; up[5] = u1.y; up[6] = u1.z; up[7] = u1.w;
+            __syncwarp();
+            pool_rows<4>(up, l2, l3);
+            stage_and_store<4>(S, l3, p.level[3], p.lh[3], p.lw[3], p.vec_ok[3], q_first, q_valid, y0 >> 3, x0 >> 3,
+                               lane);
           }
         }
       }
@@ -587,7 +615,7 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   p.total_tiles = (long long)B * p.m_tiles * p.n_tiles;
   p.scale = 1.0f / (float)sqrt((double)D);
   const int a_bytes = 2 * (D / KBLK) * A_BLOCK_BYTES;
-  const int fixed = 1024 + a_bytes + 4 * STAGING_PER_WARP + 256;
+  const int fixed = 1024 + a_bytes + NUM_EPI_WARPS * STAGING_PER_WARP + 256;
   int stages = (SMEM_LIMIT - fixed) / B_STAGE_BYTES;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages < 2) return RAFTK_ERR_UNSUPPORTED;
