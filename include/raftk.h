@@ -37,7 +37,8 @@ enum {
   RAFTK_ERR_TOO_SMALL = -3,   /* h or w < 2 * 2^(L-1): model.py:431-436 */
   RAFTK_ERR_UNSUPPORTED = -4, /* a valid request this build has no kernel for */
   RAFTK_ERR_SCRATCH = -5,     /* scratch buffer missing or too small */
-  RAFTK_ERR_ALIGN = -6        /* a pointer is not aligned as documented */
+  RAFTK_ERR_ALIGN = -6,       /* a pointer is not aligned as documented */
+  RAFTK_ERR_STATIC_LIMIT = -7 /* problem needs more than RAFTK_STATIC_SCRATCH_BYTES of scratch */
 };
 
 /* ABI version (major*1000 + minor) and a static description of an error code. */
@@ -66,6 +67,28 @@ size_t raftk_corr_pyramid_scratch_bytes(int B, int nq, int h, int w, int D);
 int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float* const* levels,
                        int num_levels, int B, int nq, int h, int w, int D,
                        void* scratch, size_t scratch_bytes, void* stream);
+
+/* Allocation-free variant of raftk_corr_pyramid.  It has no counterpart in the reference.
+ *
+ * For hosts that cannot hand over a scratch buffer at the call site and must not allocate one —
+ * e.g. a custom-call handler inside an XLA program compiled without a scratch operand, or a
+ * process whose framework pool already owns the GPU's memory, where a cudaMalloc from this
+ * library would stall the device or fail.  The scratch is a fixed RAFTK_STATIC_SCRATCH_BYTES
+ * array inside the library's device image: every GPU that loads the library holds those 16 MiB
+ * until the process exits.  The call itself allocates nothing.
+ *
+ *   - Same arguments and results as raftk_corr_pyramid, minus scratch / scratch_bytes.
+ *   - Limit: raftk_corr_pyramid_scratch_bytes(B, nq, h, w, D) <= RAFTK_STATIC_SCRATCH_BYTES
+ *     (one 440x1024 pair at D = 256 needs 14.4 MB); larger problems return
+ *     RAFTK_ERR_STATIC_LIMIT and launch nothing.
+ *   - The first call on each device looks up the array's device address (and may load the
+ *     module): issue it before any stream capture starts.
+ *   - All calls on a device share the array, which keeps the previous call's contents.  Nothing
+ *     in it needs to be zero on entry (each call rewrites everything it later reads), but calls
+ *     that overlap on the same GPU race on it: order them on one stream or with events. */
+#define RAFTK_STATIC_SCRATCH_BYTES (16u << 20)
+int raftk_corr_pyramid_static(const float* fmap1, const float* fmap2, float* const* levels,
+                              int num_levels, int B, int nq, int h, int w, int D, void* stream);
 
 /* Same contract, plain fp32 FMA kernels (no tensor cores, no scratch).  Diagnostic:
  * used by the tests to separate indexing errors from split-precision error. */

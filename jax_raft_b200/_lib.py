@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libraftk.so")
 
 MAX_LEVELS = 6
+STATIC_SCRATCH_BYTES = 16 << 20  # RAFTK_STATIC_SCRATCH_BYTES
 
 # name -> (restype, argtypes); must list every symbol include/raftk.h declares.
 _FloatPtrArray = POINTER(c_void_p)
@@ -26,6 +27,10 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_void_p, _FloatPtrArray, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
          c_size_t, c_void_p],
+    ),
+    "raftk_corr_pyramid_static": (
+        c_int,
+        [c_void_p, c_void_p, _FloatPtrArray, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
     ),
     "raftk_corr_pyramid_simt": (
         c_int,

@@ -13,6 +13,9 @@ extern "C" const char* raftk_error_string(int code) {
     case RAFTK_ERR_UNSUPPORTED: return "raftk: no kernel in this build for the requested configuration";
     case RAFTK_ERR_SCRATCH: return "raftk: scratch buffer missing or too small";
     case RAFTK_ERR_ALIGN: return "raftk: a pointer is not aligned as documented";
+    case RAFTK_ERR_STATIC_LIMIT:
+      return "raftk: problem exceeds the built-in scratch (RAFTK_STATIC_SCRATCH_BYTES = 16 MiB); "
+             "use raftk_corr_pyramid with a caller-provided scratch buffer";
     default:
       if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));
       return "raftk: unknown error code";

@@ -633,3 +633,69 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   if (num_levels > 4) return launch_pool_levels(levels, 4, num_levels, (long long)B * nq, h, w, s);
   return RAFTK_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of raftk_corr_pyramid (no counterpart in the reference).
+//
+// raftk_corr_pyramid needs a caller-provided scratch buffer for the bf16 hi/mid split of the two
+// feature maps.  Some hosts of this library have no way to provide one at the point of the call:
+// a custom-call handler running inside an XLA program that was compiled without a scratch
+// operand for it, or a process whose framework pool (XLA's preallocating allocator, torch's
+// caching allocator) already owns the device memory, so that a raw cudaMalloc from here would
+// stall the device or simply fail.  For them the scratch lives in the library image itself: a
+// fixed array in device memory that every GPU loading the library carries until the process
+// exits.  Its size bounds the problem: RAFTK_STATIC_SCRATCH_BYTES (16 MiB) holds one 440x1024
+// pair at D = 256 (14.4 MB); anything larger is refused with RAFTK_ERR_STATIC_LIMIT.
+//
+// Host code cannot use the array's name as a pointer — on the host that symbol is only a handle
+// — so the device address is looked up with cudaGetSymbolAddress once per device, with that
+// device current, the first time the entry point runs there, and kept.  That first call can load
+// the module; make it before any stream capture begins.
+//
+// Every call on a device uses the same array and leaves its split operands behind.  Nothing in it
+// has to start at zero: the split kernel of a call rewrites every byte that call's GEMM reads
+// (rows past the end of a tile are zero-filled by TMA, never fetched), so stale contents are
+// harmless.  Two calls that overlap on one GPU (different streams) would overwrite each other's
+// operands: callers must order them.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_raftk_static_scratch[RAFTK_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_static_scratch_addr[kMaxDevices] = {};
+std::mutex g_static_scratch_mutex;
+
+// Device address of the static scratch on the current device (looked up once per device).
+int static_scratch_address(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= kMaxDevices) return RAFTK_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (!g_static_scratch_addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_raftk_static_scratch);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    g_static_scratch_addr[dev] = p;
+  }
+  *out = g_static_scratch_addr[dev];
+  return RAFTK_OK;
+}
+}  // namespace
+
+extern "C" int raftk_corr_pyramid_static(const float* fmap1, const float* fmap2, float* const* levels,
+                                         int num_levels, int B, int nq, int h, int w, int D, void* stream) {
+  using namespace raftk;
+  int rc = check_pyramid_args(fmap1, fmap2, levels, num_levels, B, nq, h, w, D);
+  if (rc != RAFTK_OK) return rc;
+  if (B == 0 || nq == 0) return RAFTK_OK;
+  const size_t need = raftk_corr_pyramid_scratch_bytes(B, nq, h, w, D);
+  if (need > (size_t)RAFTK_STATIC_SCRATCH_BYTES) return RAFTK_ERR_STATIC_LIMIT;
+  void* scratch = nullptr;
+  rc = static_scratch_address(&scratch);
+  if (rc != RAFTK_OK) return rc;
+  return raftk_corr_pyramid(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, scratch,
+                            (size_t)RAFTK_STATIC_SCRATCH_BYTES, stream);
+}
