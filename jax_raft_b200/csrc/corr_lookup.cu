@@ -32,24 +32,10 @@ struct LookupParams {
   int r;
 };
 
-constexpr int kLookupWarps = 8;
-
-// R > 0: compile-time radius; R == 0: radius from params (generic, slower).
-template <int R>
-__global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const LookupParams p) {
-  extern __shared__ float smem[];
-  const int r = R > 0 ? R : p.r;
-  const int S = 2 * r + 1;   // taps per side
-  const int FP = 2 * r + 2;  // footprint side
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * kLookupWarps + warp;
-  if (q >= p.Q) return;
-  float* F = smem + warp * (p.L * FP * FP);
-
-  const float cx = __ldg(p.coords + 2 * (size_t)q);
-  const float cy = __ldg(p.coords + 2 * (size_t)q + 1);
-
-  // ---- phase 1: footprints -> shared memory ----
+// Generic staging: per level the (2r+2)^2 footprint as [l][2r+2][2r+2], zeros outside the level.
+__device__ __forceinline__ void stage_footprints_generic(const LookupParams& p, int q, float cx, float cy, int r,
+                                                         float* F, int lane) {
+  const int FP = 2 * r + 2;
   float sc = 1.0f;
 #pragma unroll 1
   for (int l = 0; l < p.L; ++l, sc *= 0.5f) {
@@ -67,10 +53,151 @@ __global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const Lo
       Fl[e] = v;
     }
   }
+}
+
+constexpr int kLookupWarps = 8;
+
+// R > 0: compile-time radius; R == 0: radius from params (generic, slower).
+template <int R>
+__global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const LookupParams p) {
+  extern __shared__ float smem[];
+  const int r = R > 0 ? R : p.r;
+  const int S = 2 * r + 1;   // taps per side
+  const int FP = 2 * r + 2;  // footprint side
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * kLookupWarps + warp;
+  if (q >= p.Q) return;
+  float* F = smem + warp * (p.L * FP * FP);
+
+  const float cx = __ldg(p.coords + 2 * (size_t)q);
+  const float cy = __ldg(p.coords + 2 * (size_t)q + 1);
+
+  stage_footprints_generic(p, q, cx, cy, r, F, lane);
   __syncwarp();
 
   // ---- phase 2: taps ----
   lookup_taps<R>(F, cx, cy, p.L, r, p.out + (size_t)q * (p.L * S * S), lane);
+}
+
+// ------------------------------------------------------------------------------------------
+// Fast path: every level has a row pitch that is a multiple of 4 floats and a 16-byte aligned
+// base (true for 440x1024 and most 32-aligned frame widths), L = 4, r in {3, 4}.
+//
+// Persistent warps, one query at a time.  Phase 1 fetches each footprint row as the aligned
+// 16-byte chunks that cover it (3 or 4 per row) — 5 LDG.128 per lane per query instead of 13
+// scalar loads, touching the same 32-byte sectors — into a [2r+3][16] tile per level whose
+// column origin is floor4(x0): chunks outside the level or past the footprint are written as
+// zeros, and a guard row below the footprint stays zero, so phase 2 needs no bounds checks.
+// Phase 2 evaluates taps lane, lane+32, lane+64 of each level with per-lane tap constants
+// hoisted out of the query loop; arithmetic is the same per-tap float32 sequence as
+// lookup_taps (bit-identical results).  Coordinates beyond +-1e6 or non-finite take the generic
+// per-query routine (warp-uniform branch).
+// ------------------------------------------------------------------------------------------
+constexpr int kFastWarps = 8;
+
+template <int R>
+__global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const LookupParams p) {
+  constexpr int S = 2 * R + 1, FP = 2 * R + 2, ROWS = FP + 1, PITCH = 16, TILE = ROWS * PITCH;
+  constexpr int NTAP = (S * S + 31) / 32;
+  extern __shared__ float smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* F = smem + warp * (4 * TILE);
+  // guard row of each level tile (never written again); all other cells are rewritten per query
+  for (int e = lane; e < 4 * PITCH; e += 32) F[(e / PITCH) * TILE + FP * PITCH + (e % PITCH)] = 0.0f;
+  __syncwarp();
+
+  // tap constants (independent of the query)
+  // (a lane whose third tap does not exist evaluates tap 0 again and skips the store)
+  float di[NTAP], dj[NTAP];
+#pragma unroll
+  for (int k = 0; k < NTAP; ++k) {
+    const int t = lane + 32 * k < S * S ? lane + 32 * k : 0;
+    const int i = t / S, j = t - i * S;
+    di[k] = (float)(i - R);
+    dj[k] = (float)(j - R);
+  }
+  const bool last_tap_valid = lane + 32 * (NTAP - 1) < S * S;
+  // load-task constants: rows 0..7 of level k in iteration k; for r = 4 the last two rows of
+  // all four levels share a fifth iteration (8 lanes per level)
+  const int row_u = lane >> 2, chunk = lane & 3;
+  const int lvx = lane >> 3, rowx = 8 + ((lane >> 2) & 1);
+  // this lane's level for that fifth iteration, selected once (no dynamic indexing of params)
+  const float* levelx = lvx == 0 ? p.level[0] : lvx == 1 ? p.level[1] : lvx == 2 ? p.level[2] : p.level[3];
+  const int lhx = lvx == 0 ? p.lh[0] : lvx == 1 ? p.lh[1] : lvx == 2 ? p.lh[2] : p.lh[3];
+  const int lwx = lvx == 0 ? p.lw[0] : lvx == 1 ? p.lw[1] : lvx == 2 ? p.lw[2] : p.lw[3];
+  constexpr int C = 4 * S * S;  // the fast path is instantiated for L = 4 only
+  const int nwarps = gridDim.x * kFastWarps;
+
+  for (int q = blockIdx.x * kFastWarps + warp; q < p.Q; q += nwarps) {
+    const float cx = __ldg(p.coords + 2 * (size_t)q);
+    const float cy = __ldg(p.coords + 2 * (size_t)q + 1);
+    if (!(fabsf(cx) <= 1.0e6f && fabsf(cy) <= 1.0e6f)) {
+      // far outside or non-finite: generic staging (its own layout), then restore the zero tile
+      stage_footprints_generic(p, q, cx, cy, R, F, lane);
+      __syncwarp();
+      lookup_taps<R>(F, cx, cy, p.L, R, p.out + (size_t)q * C, lane);
+      __syncwarp();
+      for (int e = lane; e < 4 * TILE; e += 32) F[e] = 0.0f;  // generic layout overwrote the guard rows
+      __syncwarp();
+      continue;
+    }
+
+    // ---- phase 1: aligned 16-byte chunks -> registers -> shared memory ----
+    float4 v[5];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      v[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      {
+        const float sc = __int_as_float((127 - k) << 23);
+        const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
+        const int lh = p.lh[k], lw = p.lw[k];
+        const int gy = by + row_u, gx = (bx & ~3) + 4 * chunk;
+        if (row_u < FP && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw && gx <= bx + FP - 1)
+          v[k] = __ldg(reinterpret_cast<const float4*>(p.level[k] + ((size_t)q * lh + gy) * lw + gx));
+      }
+    }
+    if (FP > 8) {
+      v[4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      {
+        const float sc = __int_as_float((127 - lvx) << 23);
+        const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
+        const int gy = by + rowx, gx = (bx & ~3) + 4 * chunk;
+        if ((unsigned)gy < (unsigned)lhx && (unsigned)gx < (unsigned)lwx && gx <= bx + FP - 1)
+          v[4] = __ldg(reinterpret_cast<const float4*>(levelx + ((size_t)q * lhx + gy) * lwx + gx));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (row_u < FP) *reinterpret_cast<float4*>(F + k * TILE + row_u * PITCH + chunk * 4) = v[k];
+    if (FP > 8) *reinterpret_cast<float4*>(F + lvx * TILE + rowx * PITCH + chunk * 4) = v[4];
+    __syncwarp();
+
+    // ---- phase 2: taps ----
+    float* obase = p.out + (size_t)q * C + lane;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+      const float sc = __int_as_float((127 - l) << 23);
+      const float cxl = cx * sc, cyl = cy * sc;
+      const float fbxa = (float)(((int)floorf(cxl) - R) & ~3);  // tile column origin
+      const float fby = floorf(cyl) - (float)R;                 // tile row origin
+      const float* Fl = F + l * TILE;
+#pragma unroll
+      for (int k = 0; k < NTAP; ++k) {
+        const float sx = __fadd_rn(cxl, di[k]), sy = __fadd_rn(cyl, dj[k]);
+        const float fx0 = floorf(sx), fy0 = floorf(sy);
+        const float wx1 = __fadd_rn(sx, -fx0), wy1 = __fadd_rn(sy, -fy0);
+        const float wx0 = __fadd_rn(1.0f, -wx1), wy0 = __fadd_rn(1.0f, -wy1);
+        const int off = __float2int_rn(fmaf(fy0 - fby, (float)PITCH, fx0 - fbxa));
+        const float* f = Fl + off;
+        float acc = __fmul_rn(__fmul_rn(wy0, wx0), f[0]);
+        acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy0, wx1), f[1]));
+        acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx0), f[PITCH]));
+        acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx1), f[PITCH + 1]));
+        if (k < NTAP - 1 || last_tap_valid) obase[l * S * S + 32 * k] = acc;
+      }
+    }
+    __syncwarp();
+  }
 }
 
 }  // namespace raftk
@@ -96,10 +223,24 @@ extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, con
   p.Q = Q;
   p.L = num_levels;
   p.r = radius;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  bool fast = (radius == 3 || radius == 4) && num_levels == 4;
+  for (int l = 0; l < num_levels && fast; ++l)
+    fast = (p.lw[l] % 4 == 0) && (((uintptr_t)p.level[l] & 15) == 0);
+  if (fast) {
+    const int tile = (2 * radius + 3) * 16;
+    const size_t smem = (size_t)kFastWarps * 4 * tile * sizeof(float);
+    int blocks = (Q + kFastWarps - 1) / kFastWarps;
+    if (blocks > RAFTK_SM_COUNT * 8) blocks = RAFTK_SM_COUNT * 8;  // persistent grid
+    if (radius == 4)
+      corr_lookup_fast_kernel<4><<<blocks, kFastWarps * 32, smem, s>>>(p);
+    else
+      corr_lookup_fast_kernel<3><<<blocks, kFastWarps * 32, smem, s>>>(p);
+    return launch_status();
+  }
   const int FP = 2 * radius + 2;
   const size_t smem = (size_t)kLookupWarps * num_levels * FP * FP * sizeof(float);
   const int blocks = (Q + kLookupWarps - 1) / kLookupWarps;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (radius == 4)
     corr_lookup_kernel<4><<<blocks, kLookupWarps * 32, smem, s>>>(p);
   else if (radius == 3)

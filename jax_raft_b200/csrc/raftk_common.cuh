@@ -38,4 +38,12 @@ __device__ __forceinline__ float2 ldg_nc_f2(const float* p) {
   return r;
 }
 
+__device__ __forceinline__ float4 ldg_nc_f4(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+
 }  // namespace raftk
