@@ -237,6 +237,60 @@ def time_hot_path_kernels(torch, J, model, variables, runner, flush, dev, passes
         return lk, bd, f"CUDA events around each launch in eager forwards behind a GPU backlog ({type(exc).__name__})"
 
 
+def kernel_microbench(torch, J, dev, flush, hbm_gbs, batch, iters=10):
+    """The three kernel families alone, at the Sintel 1/8 shape and `batch` pairs: CUDA events around
+    each launch, L2 flushed before every launch.  Gives the roofline fractions at a size that
+    fills the machine (the batch-1 step is launch/latency-bound: 20 MB per launch)."""
+    h, w, d, r, L = H // 8, W // 8, 256, 4, 4
+    g = torch.Generator(device=dev).manual_seed(0)
+    f1 = torch.randn((batch, h, w, d), device=dev, generator=g) * 1.45
+    f2 = torch.randn((batch, h, w, d), device=dev, generator=g) * 1.45
+    coords = J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
+    flow = torch.randn((batch, h, w, 2), device=dev, generator=g)
+    mask = torch.randn((batch, h, w, 576), device=dev, generator=g)
+    cb = J.CorrBlock(L, r)
+
+    def timed(fn):
+        ts = []
+        out = None
+        for i in range(iters + 2):
+            flush.fill_(i)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            out = fn()
+            b.record()
+            torch.cuda.synchronize(dev)
+            if i >= 2:
+                ts.append(a.elapsed_time(b))
+        return sum(ts) / len(ts), out
+
+    nq = batch * h * w
+    P_l = sum((h >> l) * (w >> l) for l in range(L))
+    pyr_ms, pyr = timed(lambda: cb.build_pyramid(f1, f2))
+    lk_ms, _ = timed(lambda: cb.index_pyramid(pyr, coords))
+    up_ms, _ = timed(lambda: J.upsample_flow(flow, mask))
+    pyr_bytes = 4 * (2 * nq * d + nq * P_l)
+    lk_bytes = nq * (L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4)
+    up_bytes = nq * (2304 + 8 + 512)
+    flops = 2.0 * batch * (h * w) ** 2 * d
+
+    def entry(ms, nbytes, extra=None):
+        e = {"mean_ms": ms, "algorithmic_bytes": nbytes, "hbm_gbs": nbytes / (ms * 1e-3) / 1e9,
+             "frac_of_hbm_peak": nbytes / (ms * 1e-3) / 1e9 / hbm_gbs}
+        if extra:
+            e.update(extra)
+        return e
+
+    return {
+        "batch": batch,
+        "how": "events around each call (split + GEMM for the pyramid), L2 flushed before each, host launch overhead included",
+        "corr_pyramid": entry(pyr_ms, pyr_bytes, {"tflops_algorithmic": flops / (pyr_ms * 1e-3) / 1e12,
+                                                  "tflops_issued_bf16": 3 * flops / (pyr_ms * 1e-3) / 1e12}),
+        "corr_lookup": entry(lk_ms, lk_bytes),
+        "convex_upsample": entry(up_ms, up_bytes),
+    }
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -356,12 +410,14 @@ def run_b200(args):
             "mean_launch_ms": lk_mean_ms, "launches_timed": len(lk_ms),
             "how": how,
         },
-        "kernels": {
+        "kernels_in_step": {
             "corr_pyramid": {"mean_ms": pyr_ms, "algorithmic_bytes": pyr_bytes,
                              "hbm_gbs": pyr_bytes / (pyr_ms * 1e-3) / 1e9,
                              "tflops_algorithmic": 2.0 * B * N * N * 256 / (pyr_ms * 1e-3) / 1e12},
         },
     }
+    if world == 1 and args.micro_batch > 0:
+        line["kernels_saturating"] = kernel_microbench(torch, J, dev, flush, hbm_gbs, args.micro_batch)
     if world == 1 and not args.skip_cpu_baseline:
         v, per_pair, cores, sample, phases = cpu_oracle_pairs_per_s(steps=1, warmup=0, budget_s=25.0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
@@ -380,6 +436,8 @@ def main():
     ap.add_argument("--batch", type=int, default=1, help="pairs per GPU (BASELINE config 2: 1)")
     ap.add_argument("--roofline-passes", type=int, default=2)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--micro-batch", type=int, default=16,
+                    help="pairs for the kernel-only roofline lines (0 = skip); extra info, not the headline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

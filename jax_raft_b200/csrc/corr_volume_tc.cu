@@ -19,19 +19,28 @@
 //             in shared memory while target patches stream through a TMA ring (A-stationary:
 //             halves L2->smem operand traffic, which at K = 256 is the second bottleneck after
 //             the HBM stores).
-//   CTAs    persistent, one per SM; the linearised tile list is cut into equal contiguous ranges.
+//   CTAs    persistent, one per SM, launched as clusters of two (tcgen05 cta_group::2): a pair
+//           owns a 256-query tile; each CTA keeps its own 128 query rows of A and loads HALF of
+//           every target patch, the leader CTA issues M = 256 MMAs that read both halves.  That
+//           halves per-CTA operand traffic and doubles the k-block stages in flight (4 x 16 KB).
+//           The linearised tile list is cut into equal contiguous ranges, one per pair.
 //
-// Warp roles (256 threads): warp 0 TMA producer, warp 1 MMA issuer (one elected lane each),
-// warp 2 TMEM allocator, warps 4-7 epilogue (TMEM lane quarter = warp - 4).  Accumulators are
-// double-buffered in TMEM (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of
-// tile i+1.  The epilogue transposes each 32-query x 32-column row block through a swizzled
-// shared-memory tile so that global stores are 128-byte row segments (4 queries per warp store).
+// Warp roles (384 threads): warp 0 TMA producer, warp 1 MMA issuer (one elected lane each; leader
+// CTA only), warp 2 TMEM allocator, warps 4-11 epilogue (TMEM lane quarter = warp % 4, patch rows
+// 0-3 / 4-7).  Accumulators are double-buffered in TMEM (2 x 256 columns) so the epilogue of tile
+// i overlaps the MMAs of tile i+1.  Each 32-query x 32-float row block is staged in a swizzled
+// shared-memory tile and leaves as ONE bulk tensor (TMA) store, which also clips rows, columns and
+// queries at the level's edges; levels whose pitch TMA cannot address (w>>l not a multiple of 4)
+// are written with plain stores from the same staging tile.  1/sqrt(D) rides on fmap1 in the split
+// pre-pass, so the epilogue has no multiply.
 //
 // Roofline (B = 1, 55x128, D = 256): 25.4 GFLOP algorithmic (76 GFLOP issued), 275.7 MB
-// (261.3 MB of stores): HBM-store-bound at ~42 us; the three-product MMA work is ~46 us of
-// bf16 pipe, so the two are balanced by design.
+// (261.3 MB of stores): HBM-store floor ~42 us, three-product MMA floor ~46 us of bf16 pipe.
+// Measured (ncu, B200): 77 us, tensor pipe 59 % active; mainloop alone (epilogue stubbed) runs at
+// 85 %, so the register-resident pooling epilogue is the limiter (profiles/).
 
 #include <cuda.h>
+#include <cstring>
 #include <cuda_bf16.h>
 
 #include "raftk_common.cuh"
@@ -64,7 +73,6 @@ struct Params {
   int m_tiles, px_tiles, n_tiles;
   long long total_tiles;
   int num_stages;
-  float scale;
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------
@@ -141,6 +149,64 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, float* v) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- cluster / CTA-pair (cta_group::2) variants ----------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  // default .release.cta: ordering of the TMEM reads is carried by tcgen05.fence, and a cluster-scope
+  // release would make the warp wait for all of its outstanding global stores
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA loads of a CTA pair: data lands in the issuing CTA, completion bytes go to `bar_cluster`
+// (the leader CTA's barrier).
+__device__ __forceinline__ void tma_load_3d_pair(const CUtensorMap* tm, uint32_t bar_cluster, void* dst, int c0,
+                                                 int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, "
+      "%5}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_pair(const CUtensorMap* tm, uint32_t bar_cluster, void* dst, int c0,
+                                                 int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, "
+      "%5, %6}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+// commit of the pair's MMAs: one arrival on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart.
 // start address >> 4 | LBO (unused for swizzled K-major, canonical 1) | SBO = 1024 B | version 1
 // (Blackwell) | layout type 2 (SWIZZLE_128B).  Advancing K by 16 bf16 = +32 B on the start address.
@@ -149,12 +215,14 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
          (2ull << 61);
 }
 // kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major, N = 256, M = 128.
-constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc(int m) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
 
 // ---- split kernel: float32 rows -> [hi | mid] bf16 rows ---------------------------------
 __global__ void __launch_bounds__(256)
 split_bf16_kernel(const float* __restrict__ f1, const float* __restrict__ f2, __nv_bfloat16* __restrict__ a_split,
-                  __nv_bfloat16* __restrict__ b_split, long long rows1, long long rows2, int D) {
+                  __nv_bfloat16* __restrict__ b_split, long long rows1, long long rows2, int D, float scale1) {
   const int d4 = D >> 2;
   const long long total = (rows1 + rows2) * d4;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
@@ -163,7 +231,8 @@ split_bf16_kernel(const float* __restrict__ f1, const float* __restrict__ f2, __
     const int c = (int)(t - row * d4) * 4;
     const float* src;
     __nv_bfloat16* dst;
-    if (row < rows1) {
+    const bool first = row < rows1;
+    if (first) {
       src = f1 + row * D + c;
       dst = a_split + row * 2 * D + c;
     } else {
@@ -172,7 +241,8 @@ split_bf16_kernel(const float* __restrict__ f1, const float* __restrict__ f2, __
       dst = b_split + row * 2 * D + c;
     }
     const float4 x = __ldg(reinterpret_cast<const float4*>(src));
-    const float xs[4] = {x.x, x.y, x.z, x.w};
+    const float sc = first ? scale1 : 1.0f;  // 1/sqrt(D) rides on fmap1, so the epilogue has no multiply
+    const float xs[4] = {x.x * sc, x.y * sc, x.z * sc, x.w * sc};
     __nv_bfloat16 hi[4], mid[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -185,58 +255,77 @@ split_bf16_kernel(const float* __restrict__ f1, const float* __restrict__ f2, __
 }
 
 // ---- epilogue helpers ---------------------------------------------------------------------
-// Store one staged row block (32 queries x WIDTH floats) to level memory.  `row` points at
-// (first query of the block, row Y, column X0) of the level; `slab` = floats per query slab;
-// `cols` = level columns left from X0.  Lanes sweep the block row-major, so every warp store
-// covers whole 4*WIDTH-byte row segments (4 queries x 128 B for level 0).
+// Plain-store fallback for a staged row block (32 queries x WIDTH floats) whose level TMA cannot
+// address: `row` points at (first query of the block, row Y, column X0); `slab` = floats per
+// query slab; `cols` = level columns left from X0.  Lanes sweep the block row-major, so a warp
+// store covers whole row segments.
 template <int WIDTH, bool SWIZZLED>
-__device__ __forceinline__ void store_row_block(const float* S, float* row, long long slab, int cols, bool vec_ok,
-                                                int q_valid, int lane) {
-  constexpr int CH = WIDTH / 4;   // 16-byte chunks per query row
-  constexpr int QPI = 32 / CH;    // queries covered by one warp store
-  if (vec_ok) {
-    const int qq0 = lane / CH, c = lane % CH;
-    if (4 * c >= cols) return;
-    // all shared-memory reads first, then all global stores: the two never alias, and batching
-    // keeps CH independent loads in flight instead of a load->store->load chain
-    float4 v[CH];
-#pragma unroll
-    for (int i = 0; i < CH; ++i) {
-      const int qq = qq0 + i * QPI;
+__device__ __forceinline__ void store_row_block(const float* S, float* row, long long slab, int cols, int q_valid,
+                                                int lane) {
+  for (int idx = lane; idx < 32 * WIDTH; idx += 32) {
+    const int qq = idx / WIDTH, x = idx % WIDTH;
+    if (qq < q_valid && x < cols) {
+      const int c = x >> 2;
       const int pc = SWIZZLED ? (c ^ (qq & 7)) : c;
-      v[i] = *reinterpret_cast<const float4*>(S + qq * WIDTH + pc * 4);
-    }
-    float* ptr = row + qq0 * slab + 4 * c;
-#pragma unroll
-    for (int i = 0; i < CH; ++i) {
-      if (qq0 + i * QPI < q_valid) st_na_f4(ptr, v[i]);
-      ptr += QPI * slab;
-    }
-  } else {
-    for (int idx = lane; idx < 32 * WIDTH; idx += 32) {
-      const int qq = idx / WIDTH, x = idx % WIDTH;
-      if (qq < q_valid && x < cols) {
-        const int c = x >> 2;
-        const int pc = SWIZZLED ? (c ^ (qq & 7)) : c;
-        row[qq * slab + x] = S[qq * WIDTH + pc * 4 + (x & 3)];
-      }
+      row[qq * slab + x] = S[qq * WIDTH + pc * 4 + (x & 3)];
     }
   }
 }
 
-// Stage WIDTH floats per lane (plain row-major [lane][WIDTH]) and store them as level-l row Y.
-template <int WIDTH>
-__device__ __forceinline__ void stage_and_store(float* S, const float* v, float* lvl, int lh, int lw, bool vec_ok,
-                                                long long q_first, int q_valid, int Y, int X0, int lane) {
+// TMA (bulk tensor) store plumbing for the epilogue.
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, const void* src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Where one pyramid level goes.
+struct LevelDst {
+  const CUtensorMap* tm;  // (x, y, query, pair) tensor map, box (WIDTH, 1, 32, 1)
+  float* base;
+  int lh, lw;
+  bool tma;     // pitch and base allow TMA / 16-byte stores
+};
+
+// Stage one row block (lane = query, WIDTH floats each) in the warp's shared-memory tile and send
+// it to level memory as row Y, columns X0.., of queries [m_first, m_first + 32) of pair b.
+// Aligned levels go out as ONE bulk tensor store per row block: the TMA engine clips columns,
+// rows and queries past the level / past nq, and keeps many stores in flight per SM — the LSU
+// path (a few hundred outstanding 16-byte stores per SM) cannot sustain the 27 B/clk/SM that the
+// HBM write roofline asks of this epilogue.  Unaligned levels fall back to LDS + STG.
+template <int WIDTH, bool SWIZZLED>
+__device__ __forceinline__ void emit_row(float* S, const float* v, const LevelDst& d, int nq, int b, int m_first, int Y,
+                                         int X0, int lane) {
+  // the previous row block may still be being read out of S by the TMA engine
+  if (lane == 0) bulk_wait_read_all();
+  __syncwarp();
 #pragma unroll
-  for (int c = 0; c < WIDTH / 4; ++c)
-    *reinterpret_cast<float4*>(S + lane * WIDTH + c * 4) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
-  __syncwarp();
-  if (Y < lh && q_valid > 0) {
-    const long long slab = (long long)lh * lw;
-    store_row_block<WIDTH, false>(S, lvl + q_first * slab + (long long)Y * lw + X0, slab, lw - X0, vec_ok, q_valid, lane);
+  for (int c = 0; c < WIDTH / 4; ++c) {
+    const int pc = SWIZZLED ? (c ^ (lane & 7)) : c;
+    *reinterpret_cast<float4*>(S + lane * WIDTH + pc * 4) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
   }
-  __syncwarp();
+  const int q_valid = min(32, nq - m_first);
+  if (d.tma) {
+    fence_async_smem();  // make the generic-proxy writes visible to the async proxy
+    __syncwarp();
+    if (lane == 0 && Y < d.lh && q_valid > 0) {
+      tma_store_4d(d.tm, S, X0, Y, m_first, b);
+      bulk_commit();
+    }
+  } else {
+    __syncwarp();
+    if (Y < d.lh && q_valid > 0) {
+      const long long slab = (long long)d.lh * d.lw;
+      store_row_block<WIDTH, SWIZZLED>(S, d.base + ((long long)b * nq + m_first) * slab + (long long)Y * d.lw + X0, slab,
+                                       d.lw - X0, q_valid, lane);
+    }
+    __syncwarp();
+  }
 }
 
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
@@ -254,9 +343,20 @@ __device__ __forceinline__ void pool_rows(const float* a, const float* b, float*
     out[i] = __fadd_rn(__fadd_rn(a[2 * i], a[2 * i + 1]), __fadd_rn(b[2 * i], b[2 * i + 1])) * 0.25f;
 }
 
+// CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per
+// 256-query tile: each CTA keeps its own 128 query rows of A and loads HALF of every target
+// patch (4 of its 8 rows); the leader CTA issues M = 256 MMAs that read both halves and write
+// each CTA's 128 accumulator lanes.  Per-CTA operand traffic and shared memory per stage halve,
+// which doubles the number of k-block stages in flight.
+template <int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
+                       const __grid_constant__ CUtensorMap tmO2, const __grid_constant__ CUtensorMap tmO3,
                        const Params p) {
+  constexpr int kBStage = B_STAGE_BYTES / CG;  // bytes of one B stage held by this CTA
+  const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment for the 128B-swizzle tiles; plain offset arithmetic keeps the pointers
   // in the shared address space (LDS/STS instead of generic LD/ST)
@@ -265,7 +365,7 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const int a_blocks = 2 * kblocks;          // hi blocks then mid blocks
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + a_blocks * A_BLOCK_BYTES;
-  uint8_t* smem_stage = smem_b + p.num_stages * B_STAGE_BYTES;
+  uint8_t* smem_stage = smem_b + p.num_stages * kBStage;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + NUM_EPI_WARPS * STAGING_PER_WARP);
   uint64_t* b_full = bars;                    // [MAX_STAGES]
   uint64_t* b_empty = bars + MAX_STAGES;      // [MAX_STAGES]
@@ -286,23 +386,33 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     mbar_init(a_empty, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], NUM_EPI_WARPS);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[i], NUM_EPI_WARPS * CG);  // one arrival per epilogue warp (of both CTAs)
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(512));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (CG == 1) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(512));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(512));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // contiguous, balanced range of the linearised tile list (pair, m tile, n tile)
-  const long long t_begin = p.total_tiles * blockIdx.x / gridDim.x;
-  const long long t_end = p.total_tiles * (blockIdx.x + 1) / gridDim.x;
+  // contiguous, balanced range of the linearised tile list (pair, m tile, n tile); with CG = 2
+  // both CTAs of a pair walk the same range
+  const long long unit = blockIdx.x / CG, units = gridDim.x / CG;
+  const long long t_begin = p.total_tiles * unit / units;
+  const long long t_end = p.total_tiles * (unit + 1) / units;
+  // barriers the pair shares live in the leader CTA
+  const uint32_t a_full_lead = CG == 2 ? mapa_shared(smem_u32(a_full), 0) : 0u;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -316,11 +426,15 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const int b = (int)(bm / p.m_tiles);
         if (bm != cur_bm) {
           cur_bm = bm;
-          const int m0 = (int)(bm - (long long)b * p.m_tiles) * BM;
+          const int m0 = (int)(bm - (long long)b * p.m_tiles) * (BM * CG) + (int)rank * BM;
           mbar_wait(a_empty, a_phase ^ 1);  // MMAs of the previous A tile have drained
-          mbar_expect_tx(a_full, a_blocks * A_BLOCK_BYTES);
-          for (int j = 0; j < a_blocks; ++j)
-            tma_load_3d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * KBLK, m0, b);
+          if (leader) mbar_expect_tx(a_full, CG * a_blocks * A_BLOCK_BYTES);
+          for (int j = 0; j < a_blocks; ++j) {
+            if (CG == 1)
+              tma_load_3d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * KBLK, m0, b);
+            else
+              tma_load_3d_pair(&tmA, a_full_lead, smem_a + j * A_BLOCK_BYTES, j * KBLK, m0, b);
+          }
           a_phase ^= 1;
         }
         const int x0 = (nt % p.px_tiles) * PW, y0 = (nt / p.px_tiles) * PH;
@@ -329,8 +443,12 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           const int kb = j >> 1;
           const int kcoord = (j & 1) ? p.D + kb * KBLK : kb * KBLK;
           mbar_wait(&b_empty[stage], phase ^ 1);
-          mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);
-          tma_load_4d(&tmB, &b_full[stage], smem_b + stage * B_STAGE_BYTES, kcoord, x0, y0, b);
+          if (leader) mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);  // both CTAs' halves
+          if (CG == 1)
+            tma_load_4d(&tmB, &b_full[stage], smem_b + stage * kBStage, kcoord, x0, y0, b);
+          else  // this CTA's 4 of the patch's 8 rows
+            tma_load_4d_pair(&tmB, mapa_shared(smem_u32(&b_full[stage]), 0), smem_b + stage * kBStage, kcoord, x0,
+                             y0 + (int)rank * (PH / 2), b);
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1;
@@ -339,8 +457,15 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (lane == 0 && leader) {
+      constexpr uint32_t kIdesc = make_idesc(BM * CG);
+      auto commit = [](uint64_t* bar) {
+        if (CG == 1) tc_commit(bar); else tc_commit_pair(bar);
+      };
+      auto mma = [](uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+        if (CG == 1) tc_mma_bf16(d, da, db, idesc, acc); else tc_mma_bf16_pair(d, da, db, idesc, acc);
+      };
       int stage = 0, buf = 0;
       uint32_t phase = 0, a_phase = 0, acc_phase = 0;
       long long cur_bm = -1;
@@ -348,7 +473,7 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       for (long long t = t_begin; t < t_end; ++t) {
         const long long bm = t / p.n_tiles;
         if (bm != cur_bm) {
-          if (have_a) tc_commit(a_empty);  // everything issued so far has finished reading A
+          if (have_a) commit(a_empty);  // everything issued so far has finished reading A
           cur_bm = bm;
           have_a = true;
           mbar_wait(a_full, a_phase);
@@ -364,14 +489,14 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           // stage holding B_hi[kb]: hi*hi and mid*hi
           mbar_wait(&b_full[stage], phase);
           tc_fence_after();
-          uint32_t bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
+          uint32_t bs = smem_u32(smem_b + stage * kBStage);
 #pragma unroll
           for (int k4 = 0; k4 < KBLK / 16; ++k4)
-            tc_mma_bf16(tmem_d, umma_desc(a_hi + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, (kb | k4) != 0);
+            mma(tmem_d, umma_desc(a_hi + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, (kb | k4) != 0);
 #pragma unroll
           for (int k4 = 0; k4 < KBLK / 16; ++k4)
-            tc_mma_bf16(tmem_d, umma_desc(a_mid + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, 1);
-          tc_commit(&b_empty[stage]);
+            mma(tmem_d, umma_desc(a_mid + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, 1);
+          commit(&b_empty[stage]);
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1;
@@ -379,17 +504,17 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           // stage holding B_mid[kb]: hi*mid
           mbar_wait(&b_full[stage], phase);
           tc_fence_after();
-          bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
+          bs = smem_u32(smem_b + stage * kBStage);
 #pragma unroll
           for (int k4 = 0; k4 < KBLK / 16; ++k4)
-            tc_mma_bf16(tmem_d, umma_desc(a_hi + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, 1);
-          tc_commit(&b_empty[stage]);
+            mma(tmem_d, umma_desc(a_hi + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, 1);
+          commit(&b_empty[stage]);
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tc_commit(&acc_full[buf]);
+        commit(&acc_full[buf]);
         if (++buf == 2) {
           buf = 0;
           acc_phase ^= 1;
@@ -409,16 +534,18 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     // bar_ready: "upper row written".
     float* X = reinterpret_cast<float*>(smem_stage + (4 + quarter) * STAGING_PER_WARP) + 768;
     const int bar_ready = 1 + quarter, bar_free = 5 + quarter;
+    const LevelDst dst[4] = {{&tmO0, p.level[0], p.lh[0], p.lw[0], p.vec_ok[0] != 0},
+                             {&tmO1, p.level[1], p.lh[1], p.lw[1], p.vec_ok[1] != 0},
+                             {&tmO2, p.level[2], p.lh[2], p.lw[2], p.vec_ok[2] != 0},
+                             {&tmO3, p.level[3], p.lh[3], p.lw[3], p.vec_ok[3] != 0}};
     int buf = 0;
     uint32_t acc_phase = 0;
     for (long long t = t_begin; t < t_end; ++t) {
       const long long bm = t / p.n_tiles;
       const int nt = (int)(t - bm * p.n_tiles);
       const int b = (int)(bm / p.m_tiles);
-      const int m0 = (int)(bm - (long long)b * p.m_tiles) * BM + quarter * 32;  // first query of this warp
+      const int m0 = (int)(bm - (long long)b * p.m_tiles) * (BM * CG) + (int)rank * BM + quarter * 32;  // first query of this warp
       const int x0 = (nt % p.px_tiles) * PW, y0 = (nt / p.px_tiles) * PH;
-      const long long q_first = (long long)b * p.nq + m0;
-      const int q_valid = min(32, p.nq - m0);  // <= 0: this warp's queries are all past the end
 
       mbar_wait(&acc_full[buf], acc_phase);
       tc_fence_after();
@@ -436,42 +563,25 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           // this warp's share of the accumulator is in registers: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&acc_empty[buf]);
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          r[0][i] *= p.scale;
-          r[1][i] *= p.scale;
-        }
-        // ---- level 0: two rows through the swizzled staging tile ----
-#pragma unroll
-        for (int hrow = 0; hrow < 2; ++hrow) {
-          const int Y = y0 + 4 * half + 2 * rp + hrow;
-#pragma unroll
-          for (int c = 0; c < 8; ++c)
-            *reinterpret_cast<float4*>(S + lane * 32 + ((c ^ (lane & 7)) * 4)) =
-                make_float4(r[hrow][4 * c], r[hrow][4 * c + 1], r[hrow][4 * c + 2], r[hrow][4 * c + 3]);
-          __syncwarp();
-          if (Y < p.lh[0] && q_valid > 0) {
-            const long long slab = (long long)p.lh[0] * p.lw[0];
-            store_row_block<32, true>(S, p.level[0] + q_first * slab + (long long)Y * p.lw[0] + x0, slab,
-                                      p.lw[0] - x0, p.vec_ok[0], q_valid, lane);
+          if (lane == 0) {
+            if (CG == 1) mbar_arrive(&acc_empty[buf]);
+            else mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[buf]), 0));  // the leader's barrier
           }
-          __syncwarp();
         }
+        // ---- level 0: two rows ----
+        emit_row<32, true>(S, r[0], dst[0], p.nq, b, m0, y0 + 4 * half + 2 * rp, x0, lane);
+        emit_row<32, true>(S, r[1], dst[0], p.nq, b, m0, y0 + 4 * half + 2 * rp + 1, x0, lane);
         // ---- level 1 row ----
         if (p.L > 1) {
           pool_rows<16>(r[0], r[1], l1[rp]);
-          stage_and_store<16>(S, l1[rp], p.level[1], p.lh[1], p.lw[1], p.vec_ok[1], q_first, q_valid,
-                              (y0 >> 1) + 2 * half + rp, x0 >> 1, lane);
+          emit_row<16, false>(S, l1[rp], dst[1], p.nq, b, m0, (y0 >> 1) + 2 * half + rp, x0 >> 1, lane);
         }
       }
       if (p.L > 2) {
         // ---- level 2 row ----
         float l2[8];
         pool_rows<8>(l1[0], l1[1], l2);
-        stage_and_store<8>(S, l2, p.level[2], p.lh[2], p.lw[2], p.vec_ok[2], q_first, q_valid, (y0 >> 2) + half,
-                           x0 >> 2, lane);
+        emit_row<8, false>(S, l2, dst[2], p.nq, b, m0, (y0 >> 2) + half, x0 >> 2, lane);
         if (p.L > 3) {
           // ---- level 3 row: needs the level-2 rows of both halves ----
           if (half == 0) {
@@ -489,8 +599,7 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             up[4] = u1.x; up[5] = u1.y; up[6] = u1.z; up[7] = u1.w;
             __syncwarp();
             pool_rows<4>(up, l2, l3);
-            stage_and_store<4>(S, l3, p.level[3], p.lh[3], p.lw[3], p.vec_ok[3], q_first, q_valid, y0 >> 3, x0 >> 3,
-                               lane);
+            emit_row<4, false>(S, l3, dst[3], p.nq, b, m0, y0 >> 3, x0 >> 3, lane);
           }
         }
       }
@@ -499,13 +608,17 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         acc_phase ^= 1;
       }
     }
+    if (lane == 0) bulk_wait_all();  // every bulk store has left shared memory and is globally performed
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();  // the peer may still signal our barriers until here
   if (warp == 2) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    if (CG == 1)
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    else
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
   }
 }
 
@@ -569,11 +682,14 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
     const long long total = (rows1 + rows2) * (D / 4);
     long long blocks = (total + 255) / 256;
     if (blocks > (long long)RAFTK_SM_COUNT * 8) blocks = (long long)RAFTK_SM_COUNT * 8;
-    split_bf16_kernel<<<(unsigned)blocks, 256, 0, s>>>(fmap1, fmap2, a_split, b_split, rows1, rows2, D);
+    split_bf16_kernel<<<(unsigned)blocks, 256, 0, s>>>(fmap1, fmap2, a_split, b_split, rows1, rows2, D,
+                                                      1.0f / (float)sqrt((double)D));
     rc = launch_status();
     if (rc != RAFTK_OK) return rc;
   }
 
+  // CTA pairs whenever a pair's 256-query tile is not mostly padding
+  const int CG = nq > BM ? 2 : 1;
   CUtensorMap tmA, tmB;
   {
     const cuuint64_t dims[3] = {(cuuint64_t)(2 * D), (cuuint64_t)nq, (cuuint64_t)B};
@@ -588,7 +704,7 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   {
     const cuuint64_t dims[4] = {(cuuint64_t)(2 * D), (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)B};
     const cuuint64_t strides[3] = {(cuuint64_t)(2 * D) * 2, (cuuint64_t)w * 2 * D * 2, (cuuint64_t)h * w * 2 * D * 2};
-    const cuuint32_t box[4] = {KBLK, PW, PH, 1};
+    const cuuint32_t box[4] = {KBLK, PW, (cuuint32_t)(PH / CG), 1};  // a CTA pair loads half a patch each
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     if (encode(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, b_split, dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -604,29 +720,59 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
     p.lw[l] = w >> l;
     p.vec_ok[l] = ((w >> l) % 4 == 0) && (((uintptr_t)levels[l] & 15) == 0);
   }
+  // output tensor maps (x, y, query, pair) for the levels whose pitch and base TMA accepts; the
+  // others are written with plain stores
+  CUtensorMap tmO[4];
+  memset(tmO, 0, sizeof(tmO));
+  for (int l = 0; l < p.L; ++l) {
+    if (!p.vec_ok[l]) continue;
+    const cuuint64_t lw = (cuuint64_t)(w >> l), lh = (cuuint64_t)(h >> l);
+    const cuuint64_t dims[4] = {lw, lh, (cuuint64_t)nq, (cuuint64_t)B};
+    const cuuint64_t strides[3] = {lw * 4, lh * lw * 4, (cuuint64_t)nq * lh * lw * 4};
+    const cuuint32_t box[4] = {(cuuint32_t)(PW >> l), 1, 32, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (encode(&tmO[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, levels[l], dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, l == 0 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+               CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      p.vec_ok[l] = 0;
+  }
   p.B = B;
   p.nq = nq;
   p.h = h;
   p.w = w;
   p.D = D;
-  p.m_tiles = (nq + BM - 1) / BM;
+  p.m_tiles = (nq + BM * CG - 1) / (BM * CG);
   p.px_tiles = (w + PW - 1) / PW;
   p.n_tiles = p.px_tiles * ((h + PH - 1) / PH);
   p.total_tiles = (long long)B * p.m_tiles * p.n_tiles;
-  p.scale = 1.0f / (float)sqrt((double)D);
   const int a_bytes = 2 * (D / KBLK) * A_BLOCK_BYTES;
   const int fixed = 1024 + a_bytes + NUM_EPI_WARPS * STAGING_PER_WARP + 256;
-  int stages = (SMEM_LIMIT - fixed) / B_STAGE_BYTES;
+  const int b_stage = B_STAGE_BYTES / CG;
+  int stages = (SMEM_LIMIT - fixed) / b_stage;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages < 2) return RAFTK_ERR_UNSUPPORTED;
   p.num_stages = stages;
-  const int smem_bytes = fixed + stages * B_STAGE_BYTES;
+  const int smem_bytes = fixed + stages * b_stage;
+  const long long max_units = RAFTK_SM_COUNT / CG;
+  const int units = (int)(p.total_tiles < max_units ? p.total_tiles : max_units);
+  auto kernel = CG == 2 ? corr_pyramid_tc_kernel<2> : corr_pyramid_tc_kernel<1>;
   // per-device attribute; cheap enough to set on every call (keeps the library stateless)
-  if (cudaFuncSetAttribute(corr_pyramid_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT) !=
-      cudaSuccess)
+  if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT) != cudaSuccess)
     return launch_status();
-  const int grid = (int)(p.total_tiles < RAFTK_SM_COUNT ? p.total_tiles : RAFTK_SM_COUNT);
-  corr_pyramid_tc_kernel<<<grid, NUM_THREADS, smem_bytes, s>>>(tmA, tmB, p);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(units * CG);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, tmO[0], tmO[1], tmO[2], tmO[3], p) != cudaSuccess)
+    return launch_status();
   rc = launch_status();
   if (rc != RAFTK_OK) return rc;
   // levels beyond the 8x32 patch's reach (only if a caller asks for more than 4)
