@@ -122,30 +122,31 @@ def cpu_oracle_pairs_per_s(steps: int, warmup: int, budget_s: float):
     (one 440x1024 pair, ``sample_iters`` of the 32 iterations, per-iteration phases scaled to 32)."""
     import torch
 
-    from oracle import raft_cpu
+    from oracle import corr_oracle_c, raft_cpu
 
+    corr_oracle_c.build()
     cores = torch.get_num_threads()
     net = raft_cpu.build_modules("raft_large", seed=0)
     img1, img2 = synthetic_pairs(1, seed=1)
     # probe: 1 iteration, to size the sample so that (steps + warmup) samples fit the budget
     t0 = time.perf_counter()
-    _, probe = raft_cpu.time_pair(net, img1, img2, 1, ITERS)
+    _, probe = raft_cpu.time_pair(net, img1, img2, 1, ITERS, hot=corr_oracle_c)
     probe_s = time.perf_counter() - t0
     fixed = probe["encoders"] + probe["build_pyramid"]
     per_iter = max(probe_s - fixed, 1e-3)
     per_step_budget = budget_s / max(steps + warmup, 1)
     sample_iters = int(max(1, min(ITERS, (per_step_budget - fixed) / per_iter)))
     for _ in range(warmup):
-        raft_cpu.time_pair(net, img1, img2, sample_iters, ITERS)
+        raft_cpu.time_pair(net, img1, img2, sample_iters, ITERS, hot=corr_oracle_c)
     times, phases = [], {}
     for _ in range(steps):
-        t, ph = raft_cpu.time_pair(net, img1, img2, sample_iters, ITERS)
+        t, ph = raft_cpu.time_pair(net, img1, img2, sample_iters, ITERS, hot=corr_oracle_c)
         times.append(t)
         for k, v in ph.items():
             phases[k] = phases.get(k, 0.0) + v / steps
     per_pair = sum(times) / len(times)
     sample = (f"1 pair 440x1024, {sample_iters} of {ITERS} iterations timed per step, per-iteration phases "
-              f"scaled to {ITERS}; {steps} steps after {warmup} warm-up; torch CPU convs + NumPy oracle hot path")
+              f"scaled to {ITERS}; {steps} steps after {warmup} warm-up; torch CPU convs + C/OpenMP oracle hot path (oracle/corr_oracle.c)")
     return 1.0 / per_pair, per_pair, cores, sample, phases
 
 

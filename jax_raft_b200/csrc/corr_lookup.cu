@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const Lo
 //
 // Persistent warps, one query at a time.  Phase 1 fetches each footprint row as the aligned
 // 16-byte chunks that cover it (3 or 4 per row) — 5 LDG.128 per lane per query instead of 13
-// scalar loads, touching the same 32-byte sectors — into a [2r+3][16] tile per level whose
+// scalar loads, touching the same 32-byte sectors — into a [2r+3][20] tile per level (16 used columns) whose
 // column origin is floor4(x0): chunks outside the level or past the footprint are written as
 // zeros, and a guard row below the footprint stays zero, so phase 2 needs no bounds checks.
 // Phase 2 evaluates taps lane, lane+32, lane+64 of each level with per-lane tap constants
@@ -97,7 +97,9 @@ constexpr int kFastWarps = 8;
 
 template <int R>
 __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const LookupParams p) {
-  constexpr int S = 2 * R + 1, FP = 2 * R + 2, ROWS = FP + 1, PITCH = 16, TILE = ROWS * PITCH;
+  // PITCH 20 (not 16): rows land 20 banks apart, so the taps of a warp (9 rows x 4 columns) read
+  // 32 different banks; 16 would fold them onto 8
+  constexpr int S = 2 * R + 1, FP = 2 * R + 2, ROWS = FP + 1, PITCH = 20, TILE = ROWS * PITCH;
   constexpr int NTAP = (S * S + 31) / 32;
   extern __shared__ float smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -228,7 +230,7 @@ extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, con
   for (int l = 0; l < num_levels && fast; ++l)
     fast = (p.lw[l] % 4 == 0) && (((uintptr_t)p.level[l] & 15) == 0);
   if (fast) {
-    const int tile = (2 * radius + 3) * 16;
+    const int tile = (2 * radius + 3) * 20;  // ROWS * PITCH of the kernel
     const size_t smem = (size_t)kFastWarps * 4 * tile * sizeof(float);
     int blocks = (Q + kFastWarps - 1) / kFastWarps;
     if (blocks > RAFTK_SM_COUNT * 8) blocks = RAFTK_SM_COUNT * 8;  // persistent grid

@@ -408,9 +408,13 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
   // contiguous, balanced range of the linearised tile list (pair, m tile, n tile); with CG = 2
   // both CTAs of a pair walk the same range
+  // Work split: every image pair's tile list (m tile major, n tile minor) is cut into equal
+  // contiguous ranges, one per CTA (pair).  All CTAs therefore work on the same image pair at the
+  // same time, which keeps that pair's split operands (7 MB) resident in L2 at any batch size.
   const long long unit = blockIdx.x / CG, units = gridDim.x / CG;
-  const long long t_begin = p.total_tiles * unit / units;
-  const long long t_end = p.total_tiles * (unit + 1) / units;
+  const long long tiles_per_pair = (long long)p.m_tiles * p.n_tiles;
+  const long long t_begin = tiles_per_pair * unit / units;
+  const long long t_end = tiles_per_pair * (unit + 1) / units;
   // barriers the pair shares live in the leader CTA
   const uint32_t a_full_lead = CG == 2 ? mapa_shared(smem_u32(a_full), 0) : 0u;
 
@@ -420,9 +424,10 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       int stage = 0;
       uint32_t phase = 0, a_phase = 0;
       long long cur_bm = -1;
+      for (int pair_b = 0; pair_b < p.B; ++pair_b)
       for (long long t = t_begin; t < t_end; ++t) {
-        const long long bm = t / p.n_tiles;
-        const int nt = (int)(t - bm * p.n_tiles);
+        const long long bm = (long long)pair_b * p.m_tiles + t / p.n_tiles;
+        const int nt = (int)(t % p.n_tiles);
         const int b = (int)(bm / p.m_tiles);
         if (bm != cur_bm) {
           cur_bm = bm;
@@ -470,8 +475,9 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       uint32_t phase = 0, a_phase = 0, acc_phase = 0;
       long long cur_bm = -1;
       bool have_a = false;
+      for (int pair_b = 0; pair_b < p.B; ++pair_b)
       for (long long t = t_begin; t < t_end; ++t) {
-        const long long bm = t / p.n_tiles;
+        const long long bm = (long long)pair_b * p.m_tiles + t / p.n_tiles;
         if (bm != cur_bm) {
           if (have_a) commit(a_empty);  // everything issued so far has finished reading A
           cur_bm = bm;
@@ -540,9 +546,10 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                              {&tmO3, p.level[3], p.lh[3], p.lw[3], p.vec_ok[3] != 0}};
     int buf = 0;
     uint32_t acc_phase = 0;
+    for (int pair_b = 0; pair_b < p.B; ++pair_b)
     for (long long t = t_begin; t < t_end; ++t) {
-      const long long bm = t / p.n_tiles;
-      const int nt = (int)(t - bm * p.n_tiles);
+      const long long bm = (long long)pair_b * p.m_tiles + t / p.n_tiles;
+      const int nt = (int)(t % p.n_tiles);
       const int b = (int)(bm / p.m_tiles);
       const int m0 = (int)(bm - (long long)b * p.m_tiles) * (BM * CG) + (int)rank * BM + quarter * 32;  // first query of this warp
       const int x0 = (nt % p.px_tiles) * PW, y0 = (nt / p.px_tiles) * PH;
@@ -754,7 +761,8 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   p.num_stages = stages;
   const int smem_bytes = fixed + stages * b_stage;
   const long long max_units = RAFTK_SM_COUNT / CG;
-  const int units = (int)(p.total_tiles < max_units ? p.total_tiles : max_units);
+  const long long tiles_per_pair = (long long)p.m_tiles * p.n_tiles;
+  const int units = (int)(tiles_per_pair < max_units ? tiles_per_pair : max_units);
   auto kernel = CG == 2 ? corr_pyramid_tc_kernel<2> : corr_pyramid_tc_kernel<1>;
   // per-device attribute; cheap enough to set on every call (keeps the library stateless)
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT) != cudaSuccess)

@@ -45,9 +45,13 @@ def _nhwc(t: torch.Tensor) -> np.ndarray:
 
 @torch.no_grad()
 def forward(net, image1: np.ndarray, image2: np.ndarray, num_flow_updates: int = 12,
-            timers: Dict[str, float] | None = None) -> np.ndarray:
-    """image1/2 (B, H, W, 3) float32 in [-1, 1] -> flows (N, B, H, W, 2).  model.py:557-605."""
+            timers: Dict[str, float] | None = None, hot=None) -> np.ndarray:
+    """image1/2 (B, H, W, 3) float32 in [-1, 1] -> flows (N, B, H, W, 2).  model.py:557-605.
+
+    ``hot``: the module providing build_pyramid / index_pyramid / upsample_flow — the NumPy oracle
+    (default) or its multi-threaded C twin ``oracle.corr_oracle_c`` (the timed CPU baseline)."""
     t = timers if timers is not None else {}
+    H_ = hot if hot is not None else O
 
     def tick(key, t0):
         t[key] = t.get(key, 0.0) + (time.perf_counter() - t0)
@@ -64,7 +68,7 @@ def forward(net, image1: np.ndarray, image2: np.ndarray, num_flow_updates: int =
     tick("encoders", t0)
 
     t0 = time.perf_counter()
-    pyramid = O.build_pyramid(fmap1, fmap2, num_levels)  # :567
+    pyramid = H_.build_pyramid(fmap1, fmap2, num_levels)  # :567
     tick("build_pyramid", t0)
 
     t0 = time.perf_counter()
@@ -79,7 +83,7 @@ def forward(net, image1: np.ndarray, image2: np.ndarray, num_flow_updates: int =
     flows: List[np.ndarray] = []
     for _ in range(num_flow_updates):  # nn.scan(UpdateCell), :589-603
         t0 = time.perf_counter()
-        corr_features = O.index_pyramid(pyramid, coords1, radius)  # :499
+        corr_features = H_.index_pyramid(pyramid, coords1, radius)  # :499
         tick("index_pyramid", t0)
 
         t0 = time.perf_counter()
@@ -90,17 +94,18 @@ def forward(net, image1: np.ndarray, image2: np.ndarray, num_flow_updates: int =
         tick("update_block", t0)
 
         t0 = time.perf_counter()
-        flows.append(O.upsample_flow(coords1 - coords0, up_mask))  # :508
+        flows.append(H_.upsample_flow(coords1 - coords0, up_mask))  # :508
         tick("upsample_flow", t0)
     return np.stack(flows, axis=0)
 
 
-def time_pair(net, image1: np.ndarray, image2: np.ndarray, sample_iters: int, full_iters: int) -> Tuple[float, Dict[str, float]]:
+def time_pair(net, image1: np.ndarray, image2: np.ndarray, sample_iters: int, full_iters: int,
+              hot=None) -> Tuple[float, Dict[str, float]]:
     """Seconds per image pair at ``full_iters`` iterations, measured on a bounded sample of
     ``sample_iters`` iterations: one-off phases (encoders, pyramid) counted once, per-iteration
     phases scaled by ``full_iters / sample_iters``.  Exact when ``sample_iters == full_iters``."""
     timers: Dict[str, float] = {}
-    forward(net, image1, image2, sample_iters, timers)
+    forward(net, image1, image2, sample_iters, timers, hot=hot)
     scale = full_iters / float(sample_iters)
     per_pair = timers["encoders"] + timers["build_pyramid"] + scale * (
         timers["index_pyramid"] + timers["update_block"] + timers["upsample_flow"])

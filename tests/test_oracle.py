@@ -125,3 +125,25 @@ def test_alt_index_equals_volume_lookup():
     np.testing.assert_allclose(alt, full, rtol=1e-4, atol=1e-5)
     rows = O.alt_index(f1, O.pool_fmap2(f2), coords, 4, row_range=(5, 11))
     np.testing.assert_allclose(rows, full[:, 5:11], rtol=1e-4, atol=1e-5)
+
+
+def test_c_oracle_equals_numpy_oracle():
+    """oracle/corr_oracle.c (the multi-threaded CPU baseline) against the NumPy oracle: pooling and
+    lookup bit-identical (same float32 operations in the same order), upsampling to expf rounding."""
+    from oracle import corr_oracle_c as C
+
+    rng = np.random.default_rng(0)
+    b, h, w, d = 2, 19, 22, 32
+    f1 = rng.standard_normal((b, h, w, d)).astype(F32)
+    f2 = rng.standard_normal((b, h, w, d)).astype(F32)
+    p_np, p_c = O.build_pyramid(f1, f2), C.build_pyramid(f1, f2)
+    for a, c in zip(p_np, p_c):
+        np.testing.assert_array_equal(a, c)
+    coords = O.make_coords_grid(b, h, w) + rng.uniform(-8, 8, (b, h, w, 2)).astype(F32)
+    coords[0, 0, 0] = (1e7, -3.0)
+    coords[0, 1, 1] = (-1e-9, -1e-9)
+    for r in (3, 4):
+        np.testing.assert_array_equal(O.index_pyramid(p_np, coords, r), C.index_pyramid(p_np, coords, r))
+    flow = rng.standard_normal((b, h, w, 2)).astype(F32) * 4
+    mask = rng.standard_normal((b, h, w, 576)).astype(F32)
+    np.testing.assert_allclose(C.upsample_flow(flow, mask), O.upsample_flow(flow, mask), rtol=0, atol=2e-5)
