@@ -52,6 +52,28 @@ def synthetic_pairs(batch: int, seed: int):
     return img1, np.clip(img2, -1, 1).astype(np.float32)
 
 
+def ncu_traffic_per_launch(kernel_substr: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel_substr`, from the latest
+    committed `ncu --set full` capture of the batch-1 hot path (profiles/*_hot_b1_raw.csv)."""
+    import csv
+    import glob
+
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_hot_b1_raw.csv")))
+    if not files:
+        return None, None
+    rows = list(csv.reader(open(files[-1])))
+    hdr, units = rows[0], rows[1]
+    idx = {h: i for i, h in enumerate(hdr)}
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for r in rows[2:]:
+        if kernel_substr in r[idx["Kernel Name"]]:
+            tot = 0.0
+            for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(r[idx[m]].replace(",", "")) * scale.get(units[idx[m]], 1.0)
+            return tot, os.path.relpath(files[-1], ROOT)
+    return None, None
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -385,6 +407,7 @@ def run_b200(args):
     pyr_bytes = 4 * (2 * B * N * 256 + B * N * P_l)
     pyr_ms = sum(bd_ms) / len(bd_ms)
 
+    traffic, traffic_src = ncu_traffic_per_launch("corr_lookup") if B == 1 else (None, None)
     pairs = world * B * args.steps
     line = {
         "metric": METRIC, "value": pairs / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
@@ -405,8 +428,9 @@ def run_b200(args):
         "gpu_launches_per_step": int(per_forward),
         "clocks": clocks,
         "roofline": {
-            "kernel": "corr_lookup_kernel<4> (raftk_corr_lookup)", "bound": "hbm", "achieved": achieved,
-            "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": None,
+            "kernel": "corr_lookup_fast_kernel<4> (raftk_corr_lookup)", "bound": "hbm", "achieved": achieved,
+            "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": traffic,
+            "traffic_source": traffic_src,
             "peak_source": peak_src, "algorithmic_bytes_per_launch": lookup_bytes,
             "mean_launch_ms": lk_mean_ms, "launches_timed": len(lk_ms),
             "how": how,
