@@ -499,11 +499,17 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
         raise TypeError(
             f"unsupported keyword(s) {sorted(kwargs)}: this build replaces the correlation block "
             "(corr_block=) only; encoders, update block and mask predictor are fixed by the architecture")
+    if isinstance(pretrained, (str, bytes)) or hasattr(pretrained, "__fspath__"):
+        # a local copy of the reference's released .msgpack (model.py:17-21) or of a converted one
+        from .checkpoint import load_msgpack
+
+        model = RAFT(cfg, corr_block=corr_block, precision=precision)
+        return model, load_msgpack(pretrained)
     if pretrained:
         # model.py:684-689 downloads a msgpack from GitHub; this environment has no network.
         raise RuntimeError(
-            "pretrained=True needs network access (model.py:17-21, 684-689); load a converted checkpoint with "
-            "variables_from_torch_state_dict(torch.load(path)) instead")
+            "pretrained=True needs network access (model.py:17-21, 684-689); pass pretrained='<file>.msgpack' "
+            "(a local copy of the released checkpoint) or use variables_from_torch_state_dict(torch.load(path))")
     model = RAFT(cfg, corr_block=corr_block, precision=precision)
     return model, model.init(seed)
 

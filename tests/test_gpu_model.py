@@ -67,3 +67,28 @@ def test_apply_checks_inputs(cuda, lib):
     with pytest.raises(AssertionError, match="same shape"):
         model.apply(variables, np.zeros((1, 128, 128, 3), np.float32), np.zeros((1, 128, 136, 3), np.float32),
                     use_cuda_graph=False)
+
+
+def test_validation_loop_on_synthetic_pairs(cuda, lib):
+    """f4: the validate_sintel_jax loop (pad to /8, normalise, forward, unpad, EPE) on a frame size
+    that needs padding (436-style), against the CPU oracle run on the same padded inputs."""
+    from jax_raft_b200 import validation as V
+    from oracle import raft_cpu
+
+    rng = np.random.default_rng(5)
+    h, w = 124, 160  # -> padded to 128 x 160, 2 rows top and bottom
+    frames = [(rng.uniform(0, 255, (h, w, 3)).astype(np.float32),) * 2 for _ in range(2)]
+    net = raft_cpu.build_modules("raft_small", seed=0)
+    variables = J.variables_from_torch_state_dict(net.state_dict())
+    model, _ = J.raft_small(precision="fp32")
+    pairs, refs = [], []
+    for (a, _), shift in zip(frames, (2, -3)):
+        b = np.roll(a, shift, axis=1)
+        im1 = (a / 255.0 * 2 - 1)[None]
+        im2 = (b / 255.0 * 2 - 1)[None]
+        padder = V.InputPadder(im1.shape)
+        p1, p2 = padder.pad(im1, im2)
+        ref = padder.unpad(raft_cpu.forward(net, p1.astype(np.float32), p2.astype(np.float32), 4)[-1])[0]
+        pairs.append((a, b, ref))  # "ground truth" = the CPU oracle's flow
+    out = V.validate_pairs(model, variables, pairs, iters=4)
+    assert out["epe"] <= 0.01 and out["1px"] == 1.0

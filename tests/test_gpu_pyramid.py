@@ -124,3 +124,30 @@ def test_checksum_property_at_batch_size(cuda, lib):
         cover = pyr[0][:, : (h >> l) * s, : (w >> l) * s].double().sum(dim=(1, 2, 3))
         assert torch.allclose(pyr[l].double().sum(dim=(1, 2, 3)) * (4 ** l), cover, rtol=0,
                               atol=1e-3 * float(cover.abs().mean()) + 1e-2)
+
+
+def test_1080p_shape_properties_and_altcorr_agreement(cuda, lib):
+    """Largest named configuration (BASELINE config 4 shape: 1088x1920 -> 136x240, N = 32640,
+    5.7 GB pyramid), where the CPU oracle is not run: row-sum checksum of the volume, pooled levels
+    consistent with level 0, and the materialised-volume lookup equal to the on-the-fly alt_corr
+    lookup (two independent kernels) on a band of query rows."""
+    b, h, w, d, r = 1, 136, 240, 256, 4
+    gen = torch.Generator(device=cuda).manual_seed(0)
+    f1 = torch.randn((b, h, w, d), device=cuda, generator=gen)
+    f2 = torch.randn((b, h, w, d), device=cuda, generator=gen)
+    cb = J.CorrBlock(4, r)
+    pyr = cb.build_pyramid(f1, f2)
+    assert [tuple(p.shape) for p in pyr] == [(h * w, h >> l, w >> l, 1) for l in range(4)]
+    row_sum = pyr[0].double().sum(dim=(1, 2, 3))
+    expect = (f1.view(h * w, d).double() @ f2.view(h * w, d).double().sum(0)) / d ** 0.5
+    assert torch.allclose(row_sum, expect, rtol=0, atol=2e-3 * float(expect.abs().mean()) + 1e-2)
+    for l in range(1, 4):
+        s = 2 ** l
+        cover = pyr[0][:, : (h >> l) * s, : (w >> l) * s].double().sum(dim=(1, 2, 3))
+        assert torch.allclose(pyr[l].double().sum(dim=(1, 2, 3)) * (4 ** l), cover, rtol=0,
+                              atol=1e-3 * float(cover.abs().mean()) + 1e-2)
+    coords = J.make_coords_grid(b, h, w, device=cuda) + (torch.rand((b, h, w, 2), device=cuda, generator=gen) - 0.5) * 16
+    vol = cb.index_pyramid(pyr, coords)
+    alt = J.AltCorrBlock(4, r)
+    band = alt.index_pyramid(alt.build_pyramid(f1, f2, query_rows=(40, 57)), coords[:, 40:57].contiguous())
+    assert float((band - vol[:, 40:57]).abs().max()) <= 1e-3 * max(1.0, float(vol.abs().mean()))

@@ -88,3 +88,64 @@ def test_product_package_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")):
                 text = open(os.path.join(root, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+
+
+def test_checkpoint_msgpack_round_trip_and_torch_conversion(tmp_path):
+    """f3: scripts/convert_checkpoint.py's path (torch state_dict -> Flax tree -> msgpack) and back."""
+    import torchvision.models.optical_flow as tvof
+
+    from jax_raft_b200 import checkpoint
+
+    torch.manual_seed(3)
+    net = tvof.raft_small(weights=None)
+    pth = tmp_path / "raft_small.pth"
+    torch.save(net.state_dict(), pth)
+    out = tmp_path / "raft_small.msgpack"
+    variables = checkpoint.convert_checkpoint(str(pth), str(out))
+    loaded = checkpoint.load_msgpack(str(out))
+    a, b = dict(_tree_items(variables)), dict(_tree_items(loaded))
+    assert set(a) == set(b)
+    for k in a:
+        assert b[k].dtype == np.float32 and np.array_equal(a[k], b[k]), k
+    # the tree loads back into torchvision bit-for-bit
+    sd = J.torch_state_dict_from_variables(loaded)
+    for k, v in net.state_dict().items():
+        if not k.endswith("num_batches_tracked"):
+            assert torch.equal(sd[k], v), k
+    # ext-type framing as flax writes it: ExtType(1, packb((shape, dtype, bytes)))
+    import msgpack
+
+    model, from_file = J.raft_small(pretrained=str(out))  # local file in place of the download (model.py:684-689)
+    assert np.array_equal(from_file["params"]["feature_encoder"]["conv"]["kernel"], a["params/feature_encoder/conv/kernel"])
+    raw = msgpack.unpackb(out.read_bytes(), raw=False, strict_map_key=False)
+    leaf = raw["params"]["feature_encoder"]["conv"]["bias"]
+    assert isinstance(leaf, msgpack.ExtType) and leaf.code == 1
+    shape, dtype, buf = msgpack.unpackb(leaf.data, raw=True)
+    assert tuple(shape) == (128,) and dtype == b"float32" and len(buf) == 512
+
+
+def test_validation_helpers(tmp_path):
+    """f4: InputPadder / .flo / EPE metrics of scripts/validate_sintel.py."""
+    from jax_raft_b200 import validation as V
+
+    img = np.arange(436 * 1024 * 3, dtype=np.float32).reshape(1, 436, 1024, 3)
+    padder = V.InputPadder(img.shape)  # Sintel 436x1024 -> 440x1024 (validate_sintel.py:23-35)
+    (padded,) = padder.pad(img)
+    assert padded.shape == (1, 440, 1024, 3)
+    assert np.array_equal(padded[0, 0], img[0, 0]) and np.array_equal(padded[0, 1], img[0, 0])  # replicate, 2 rows on top
+    assert np.array_equal(padder.unpad(padded), img)
+    other = V.InputPadder((1, 370, 1226, 3), mode="kitti")
+    (p2,) = other.pad(np.zeros((1, 370, 1226, 3), np.float32))
+    assert p2.shape == (1, 376, 1232, 3)
+    # torch's F.pad(replicate) is the reference's implementation
+    ref = torch.nn.functional.pad(torch.from_numpy(img).permute(0, 3, 1, 2), [0, 0, 2, 2], mode="replicate")
+    assert np.array_equal(padded, ref.permute(0, 2, 3, 1).numpy())
+
+    flow = np.random.default_rng(0).standard_normal((7, 9, 2)).astype(np.float32)
+    V.write_flo(str(tmp_path / "a.flo"), flow)
+    assert np.array_equal(V.read_flo(str(tmp_path / "a.flo")), flow)
+    (tmp_path / "bad.flo").write_bytes(b"\x00" * 32)
+    assert V.read_flo(str(tmp_path / "bad.flo")) is None
+
+    m = V.epe_metrics(np.array([0.5, 2.0, 4.0, 10.0]))
+    assert m == {"epe": 4.125, "1px": 0.25, "3px": 0.5, "5px": 0.75}
