@@ -119,6 +119,186 @@ __global__ void __launch_bounds__(kAltWarps * 32) altcorr_lookup_kernel(const Al
   lookup_taps<R>(F, cx, cy, p.L, r, p.out + q * (p.L * S * S), lane);
 }
 
+// ------------------------------------------------------------------------------------------
+// Tiled alt_corr: a block owns an 8x8 patch of query pixels at ONE pyramid level.  Neighbouring
+// queries have overlapping windows (optical flow is smooth), so the block fetches the bounding
+// box of its 64 windows once — 32 channels at a time into shared memory — instead of every warp
+// re-reading its own 100 target pixels (1 KB each) from L2: 16x less L2 traffic in the common
+// case.  Thread (query, sub) accumulates the dot products of cells sub, sub+4, ... of its query's
+// (2r+2)^2 footprint, each as one sequential fma chain over d = 0..D-1, so the value of a cell
+// does not depend on which tile or path computed it.  If the 64 windows do not fit the box
+// (rough flow, or far-out-of-range coordinates) the block falls back to a per-query loop with
+// the same summation order.  Taps are then evaluated by the shared lookup code, level by level.
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ T pick_level(const T* arr, int l) {  // block-uniform select: keeps params out of local memory
+  T v = arr[0];
+#pragma unroll
+  for (int i = 1; i < RAFTK_MAX_LEVELS; ++i)
+    if (l == i) v = arr[i];
+  return v;
+}
+
+constexpr int kTileThreads = 256;
+constexpr int kTileQ = 64;          // 8 x 8 queries
+constexpr int kCellCap = 576;       // bounding-box cells held in shared memory (e.g. 24 x 24)
+constexpr int kCellPitch = 36;      // floats per cell per 32-channel chunk (+4: bank spread, 16-byte aligned)
+
+template <int R>
+__global__ void __launch_bounds__(kTileThreads) altcorr_tile_kernel(const AltParams p, int rows_q, int w_q) {
+  constexpr int FP = 2 * R + 2, S = 2 * R + 1, NCELL = FP * FP, NC = NCELL / 4;
+  extern __shared__ float smem[];
+  float* cellbuf = smem;                              // [kCellCap][kCellPitch]
+  float* Fq = smem + kCellCap * kCellPitch;           // [kTileQ][NCELL]
+  __shared__ int red[4][8];
+  __shared__ int box[5];
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int qi = t >> 2, sub = t & 3;
+  if (t == 0) box[4] = 0;
+  __syncthreads();
+  const int tiles_x = (w_q + 7) >> 3, tiles_y = (rows_q + 7) >> 3;
+  int bid = blockIdx.x;
+  const int l = bid % p.L;
+  bid /= p.L;
+  const int txi = bid % tiles_x;
+  bid /= tiles_x;
+  const int tyi = bid % tiles_y;
+  const int b = bid / tiles_y;
+  const int qy = tyi * 8 + (qi >> 3), qx = txi * 8 + (qi & 7);
+  const bool qvalid = qy < rows_q && qx < w_q;
+  const long long q = (long long)b * p.nq + (long long)qy * w_q + qx;
+
+  const int lh = pick_level(p.lh, l), lw = pick_level(p.lw, l);
+  const float* f2b = pick_level(p.f2, l) + (long long)b * lh * lw * p.D;
+  const float sc = __int_as_float((127 - l) << 23);
+  float cx = 0.0f, cy = 0.0f;
+  if (qvalid) {
+    cx = __ldg(p.coords + 2 * q);
+    cy = __ldg(p.coords + 2 * q + 1);
+  }
+  const bool normal = fabsf(cx) <= 1.0e6f && fabsf(cy) <= 1.0e6f;
+  const int bx = clamp_to_int(floorf(cx * sc)) - R, by = clamp_to_int(floorf(cy * sc)) - R;
+
+  // ---- bounding box of the tile's windows ----
+  {
+    int mnx = qvalid ? bx : 0x7fffffff, mxx = qvalid ? bx : -0x7fffffff;
+    int mny = qvalid ? by : 0x7fffffff, mxy = qvalid ? by : -0x7fffffff;
+    int bad = (qvalid && !normal) ? 1 : 0;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, off));
+      mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, off));
+      mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, off));
+      mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, off));
+      bad |= __shfl_xor_sync(0xffffffffu, bad, off);
+    }
+    if (lane == 0) {
+      red[0][warp] = mnx;
+      red[1][warp] = mxx;
+      red[2][warp] = mny;
+      red[3][warp] = mxy;
+      if (bad) atomicOr(&box[4], 1);
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    int mnx = red[0][0], mxx = red[1][0], mny = red[2][0], mxy = red[3][0];
+    for (int i = 1; i < 8; ++i) {
+      mnx = min(mnx, red[0][i]);
+      mxx = max(mxx, red[1][i]);
+      mny = min(mny, red[2][i]);
+      mxy = max(mxy, red[3][i]);
+    }
+    box[0] = mnx;
+    box[1] = mny;
+    box[2] = mxx - mnx + FP;  // width in cells
+    box[3] = mxy - mny + FP;  // height
+  }
+  __syncthreads();
+  const int X0 = box[0], Y0 = box[1], BW = box[2], BH = box[3];
+  const bool shared_path = box[4] == 0 && BW > 0 && BH > 0 && (long long)BW * BH <= kCellCap;
+
+  float acc[NC];
+#pragma unroll
+  for (int i = 0; i < NC; ++i) acc[i] = 0.0f;
+  const float* f1q = p.f1 + (qvalid ? q : 0) * p.D;
+
+  if (shared_path) {
+    const int ncell = BW * BH;
+    const int rel = (by - Y0) * BW + (bx - X0);  // this query's window origin inside the box
+    for (int c0 = 0; c0 < p.D; c0 += 32) {
+      __syncthreads();  // the previous chunk has been consumed
+      for (int idx = t; idx < ncell * 8; idx += kTileThreads) {
+        const int cell = idx >> 3, part = idx & 7;
+        const int cyy = cell / BW, cxx = cell - cyy * BW;
+        const int gy = Y0 + cyy, gx = X0 + cxx;
+        float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if ((unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw)
+          v = __ldg(reinterpret_cast<const float4*>(f2b + ((long long)gy * lw + gx) * p.D + c0) + part);
+        *reinterpret_cast<float4*>(cellbuf + cell * kCellPitch + part * 4) = v;
+      }
+      __syncthreads();
+      if (qvalid) {
+        float4 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = __ldg(reinterpret_cast<const float4*>(f1q + c0) + k);
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+          const int e = sub + 4 * i;
+          const int ry = e / FP, rx = e - ry * FP;
+          const float4* cp = reinterpret_cast<const float4*>(cellbuf + (rel + ry * BW + rx) * kCellPitch);
+          float s = acc[i];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float4 v = cp[k];
+            s = fmaf(a[k].x, v.x, s);
+            s = fmaf(a[k].y, v.y, s);
+            s = fmaf(a[k].z, v.z, s);
+            s = fmaf(a[k].w, v.w, s);
+          }
+          acc[i] = s;
+        }
+      }
+    }
+  } else if (qvalid) {
+    // rough flow: every thread walks its own cells in global memory, same summation order
+#pragma unroll 1
+    for (int i = 0; i < NC; ++i) {
+      const int e = sub + 4 * i;
+      const int ry = e / FP, rx = e - ry * FP;
+      const int gy = by + ry, gx = bx + rx;
+      float s = 0.0f;
+      if (normal && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) {
+        const float4* cp = reinterpret_cast<const float4*>(f2b + ((long long)gy * lw + gx) * p.D);
+        const float4* ap = reinterpret_cast<const float4*>(f1q);
+        for (int k = 0; k < p.D / 4; ++k) {
+          const float4 v = __ldg(cp + k), a = __ldg(ap + k);
+          s = fmaf(a.x, v.x, s);
+          s = fmaf(a.y, v.y, s);
+          s = fmaf(a.z, v.z, s);
+          s = fmaf(a.w, v.w, s);
+        }
+      }
+      acc[i] = s;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NC; ++i) Fq[qi * NCELL + sub + 4 * i] = acc[i] * p.inv_sqrt_d;
+  __syncthreads();
+
+  // ---- taps of level l: warp w takes queries 8w .. 8w+7 of the tile ----
+  const int C = p.L * S * S;
+  for (int k = 0; k < 8; ++k) {
+    const int qj = warp * 8 + k;
+    const int yj = tyi * 8 + (qj >> 3), xj = txi * 8 + (qj & 7);
+    if (yj >= rows_q || xj >= w_q) continue;
+    const long long qq = (long long)b * p.nq + (long long)yj * w_q + xj;
+    const float ccx = __ldg(p.coords + 2 * qq), ccy = __ldg(p.coords + 2 * qq + 1);
+    lookup_taps_level<R>(Fq + qj * NCELL, ccx, ccy, l, p.out + qq * C, lane);
+  }
+}
+
 }  // namespace raftk
 
 extern "C" int raftk_altcorr_pool_fmap2(float* const* f2_levels, int num_levels, int B, int h, int w,
@@ -154,7 +334,8 @@ extern "C" int raftk_altcorr_lookup(const float* fmap1, const float* const* f2_l
       D <= 0 || radius < 0)
     return RAFTK_ERR_SHAPE;
   if ((h >> (num_levels - 1)) < 1 || (w >> (num_levels - 1)) < 1) return RAFTK_ERR_TOO_SMALL;
-  if (D % 128 || D > 128 * kAltMaxD4 || radius > 7) return RAFTK_ERR_UNSUPPORTED;
+  const bool tiled = (radius == 3 || radius == 4) && D % 32 == 0 && nq % w == 0;
+  if (!tiled && (D % 128 || D > 128 * kAltMaxD4 || radius > 7)) return RAFTK_ERR_UNSUPPORTED;
   if ((long long)B * nq == 0) return RAFTK_OK;  // empty batch: pointers may be NULL
   if (!fmap1 || !f2_levels || !coords || !out) return RAFTK_ERR_NULL;
   if ((uintptr_t)fmap1 & 15) return RAFTK_ERR_ALIGN;
@@ -177,11 +358,29 @@ extern "C" int raftk_altcorr_lookup(const float* fmap1, const float* const* f2_l
   p.L = num_levels;
   p.r = radius;
   p.inv_sqrt_d = 1.0f / (float)sqrt((double)D);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // Tiled kernel: queries form whole image rows of width w (the full map or a band of rows)
+  if (tiled) {
+    const int rows_q = nq / w;
+    const int FPt = 2 * radius + 2;
+    const size_t smem_t = (size_t)(kCellCap * kCellPitch + kTileQ * FPt * FPt) * sizeof(float);
+    const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8) * num_levels;
+    if (nblk > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
+    if (radius == 4) {
+      if (cudaFuncSetAttribute(altcorr_tile_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t) != cudaSuccess)
+        return launch_status();
+      altcorr_tile_kernel<4><<<(unsigned)nblk, kTileThreads, smem_t, s>>>(p, rows_q, w);
+    } else {
+      if (cudaFuncSetAttribute(altcorr_tile_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t) != cudaSuccess)
+        return launch_status();
+      altcorr_tile_kernel<3><<<(unsigned)nblk, kTileThreads, smem_t, s>>>(p, rows_q, w);
+    }
+    return launch_status();
+  }
   const int FP = 2 * radius + 2;
   const size_t smem = (size_t)kAltWarps * num_levels * FP * FP * sizeof(float);
   const long long blocks = (Q + kAltWarps - 1) / kAltWarps;
   if (blocks > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (radius == 4)
     altcorr_lookup_kernel<4><<<(unsigned)blocks, kAltWarps * 32, smem, s>>>(p);
   else if (radius == 3)

@@ -56,4 +56,35 @@ __device__ __forceinline__ void lookup_taps(const float* F, float cx, float cy, 
   }
 }
 
+// The taps of ONE level l from that level's staged footprint Fl[(2r+2)][(2r+2)]; same arithmetic
+// as lookup_taps, channels l*(2r+1)^2 ... of orow.
+template <int R>
+__device__ __forceinline__ void lookup_taps_level(const float* Fl, float cx, float cy, int l, float* orow, int lane) {
+  constexpr int S = 2 * R + 1, FP = 2 * R + 2;
+  const float scl = __int_as_float((127 - l) << 23);  // 2^-l, exact
+  const float cxl = cx * scl, cyl = cy * scl;
+  const int bx = clamp_to_int(floorf(cxl)) - R;
+  const int by = clamp_to_int(floorf(cyl)) - R;
+  for (int k = lane; k < S * S; k += 32) {
+    const int i = k / S, j = k - i * S;
+    const float sx = __fadd_rn(cxl, (float)(i - R));
+    const float sy = __fadd_rn(cyl, (float)(j - R));
+    const float fx0 = floorf(sx), fy0 = floorf(sy);
+    const float wx1 = __fadd_rn(sx, -fx0), wy1 = __fadd_rn(sy, -fy0);
+    const float wx0 = __fadd_rn(1.0f, -wx1), wy0 = __fadd_rn(1.0f, -wy1);
+    const int rx = clamp_to_int(fx0) - bx, ry = clamp_to_int(fy0) - by;
+    const bool x0in = (unsigned)rx < (unsigned)FP, x1in = (unsigned)(rx + 1) < (unsigned)FP;
+    const bool y0in = (unsigned)ry < (unsigned)FP, y1in = (unsigned)(ry + 1) < (unsigned)FP;
+    const float v00 = (y0in && x0in) ? Fl[ry * FP + rx] : 0.0f;
+    const float v01 = (y0in && x1in) ? Fl[ry * FP + rx + 1] : 0.0f;
+    const float v10 = (y1in && x0in) ? Fl[(ry + 1) * FP + rx] : 0.0f;
+    const float v11 = (y1in && x1in) ? Fl[(ry + 1) * FP + rx + 1] : 0.0f;
+    float acc = __fmul_rn(__fmul_rn(wy0, wx0), v00);
+    acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy0, wx1), v01));
+    acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx0), v10));
+    acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx1), v11));
+    orow[l * S * S + k] = acc;
+  }
+}
+
 }  // namespace raftk

@@ -40,7 +40,9 @@ B, h, w, D, r = 1, args.h, args.w, 256, 4
 g = torch.Generator(device=dev).manual_seed(0)  # same maps on every rank; each keeps only its band
 f1 = torch.randn((B, h, w, D), device=dev, generator=g) * 1.45
 f2 = torch.randn((B, h, w, D), device=dev, generator=g) * 1.45
-flow = (torch.rand((B, h, w, 2), device=dev, generator=g) - 0.5) * 16
+# a smooth flow field (what RAFT sees between iterations), +-8 px
+yy, xx = torch.meshgrid(torch.arange(h, device=dev), torch.arange(w, device=dev), indexing="ij")
+flow = torch.stack([8 * torch.sin(6.28 * (xx / w + 0.3 * yy / h)), 8 * torch.cos(6.28 * (yy / h - 0.2 * xx / w))], -1)[None].float()
 y0, y1 = sharding.row_range(h, world, rank)
 f1_rows, f2_rows = f1[:, y0:y1].contiguous(), f2[:, y0:y1].contiguous()
 coords_rows = (J.make_coords_grid(B, h, w, device=dev) + flow)[:, y0:y1].contiguous()

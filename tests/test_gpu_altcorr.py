@@ -55,3 +55,33 @@ def test_query_row_band(cuda, lib):
     # already-sliced fmap1 (what a row-sharded rank holds)
     band2 = alt.index_pyramid(alt.build_pyramid(t1[:, 7:15].contiguous(), t2, query_rows=(7, 15)), tc[:, 7:15].contiguous())
     assert torch.equal(band2, band)
+
+
+def _smooth_flow(b, h, w, rng, amp=6.0):
+    """A low-frequency flow field (what RAFT actually sees): neighbouring windows overlap, so the
+    tiled kernel takes its shared bounding-box path; random per-pixel flow takes the fallback."""
+    yy, xx = np.meshgrid(np.arange(h), np.arange(w), indexing="ij")
+    fx = amp * np.sin(2 * np.pi * (xx / w + 0.3 * yy / h) + rng.uniform(0, 6)) + rng.uniform(-3, 3)
+    fy = amp * np.cos(2 * np.pi * (yy / h - 0.2 * xx / w) + rng.uniform(0, 6)) + rng.uniform(-3, 3)
+    return np.tile(np.stack([fx, fy], -1).astype(F32)[None], (b, 1, 1, 1))
+
+
+@pytest.mark.parametrize("shape,r", [((1, 24, 40, 128), 4), ((2, 19, 21, 64), 3), ((1, 46, 62, 128), 3), ((1, 55, 128, 256), 4)])
+def test_smooth_flow_shared_path_against_oracle(cuda, lib, shape, r):
+    b, h, w, d = shape
+    rng = np.random.default_rng(h + w)
+    f1 = (rng.standard_normal((b, h, w, d)) * 1.45).astype(F32)
+    f2 = (rng.standard_normal((b, h, w, d)) * 1.45).astype(F32)
+    coords = O.make_coords_grid(b, h, w) + _smooth_flow(b, h, w, rng)
+    coords[0, 0, 0] = (1e7, 3.0)       # one far-out query: its tile falls back, the rest must not change
+    coords[0, h - 1, w - 1] = (-40.0, h + 30.0)
+    alt = J.AltCorrBlock(4, r)
+    t1, t2, tc = (torch.from_numpy(x).to(cuda) for x in (f1, f2, coords))
+    out = alt.index_pyramid(alt.build_pyramid(t1, t2), tc).cpu().numpy()
+    ref = O.alt_index(f1, O.pool_fmap2(f2), coords, r)
+    _scale_close(out, ref)
+    assert not out[0, 0, 0].any()
+    # a band of rows gives bit-identical values: each cell's dot product is one fixed fma chain,
+    # whatever tile or path computed it
+    band = alt.index_pyramid(alt.build_pyramid(t1, t2, query_rows=(3, 17)), tc[:, 3:17].contiguous()).cpu().numpy()
+    assert np.array_equal(band, out[:, 3:17])
