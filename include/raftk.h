@@ -111,6 +111,13 @@ int raftk_corr_pyramid_simt(const float* fmap1, const float* fmap2, float* const
 int raftk_corr_lookup(const float* const* levels, int num_levels, const float* coords,
                       float* out, int Q, int h, int w, int radius, void* stream);
 
+/* Stand-alone form of the reference's grid_sample helper, model.py:24-34 (bilinear sample of an
+ * NHWC image at absolute pixel coordinates, each corner zero outside; jax map_coordinates order=1
+ * mode='constant').  img (n, h, w, c); grid (n, gh, gw, 2) as (x, y); out (n, gh, gw, c).  Same
+ * float32 operation order as the lookup, so results match a float32 CPU evaluation bit for bit. */
+int raftk_grid_sample(const float* img, const float* grid, float* out, int n, int h, int w, int c,
+                      int gh, int gw, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Kernel family 2b — "alt_corr": the same lookup computed on the fly from the feature
  * maps, never materialising the volume (no reference counterpart; equals

@@ -40,6 +40,7 @@ SIGNATURES = {
         c_int,
         [_FloatPtrArray, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
     ),
+    "raftk_grid_sample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_altcorr_pool_fmap2": (c_int, [_FloatPtrArray, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_altcorr_lookup": (
         c_int,

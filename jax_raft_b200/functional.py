@@ -23,6 +23,34 @@ def make_coords_grid(batch_size: int, h: int, w: int, device="cuda") -> torch.Te
     return coords[None].repeat(batch_size, 1, 1, 1)
 
 
+def grid_sample(img: torch.Tensor, grid: torch.Tensor) -> torch.Tensor:
+    """Bilinear sample of ``img`` (n, h, w, c) at absolute pixel coords ``grid`` (n, gh, gw, 2), given
+    as (x, y); zero outside (model.py:24-34)."""
+    assert img.shape[-3] > 1  # model.py:25
+    assert grid.ndim == 4 and grid.shape[-1] == 2  # model.py:26
+    img = _check_cuda_f32("img", img)
+    grid = _check_cuda_f32("grid", grid)
+    n, h, w, c = img.shape
+    assert grid.shape[0] == n
+    gh, gw = int(grid.shape[1]), int(grid.shape[2])
+    out = torch.empty((n, gh, gw, c), dtype=torch.float32, device=img.device)
+    lib = _lib.load()
+    with torch.cuda.device(img.device):
+        rc = lib.raftk_grid_sample(img.data_ptr(), grid.data_ptr(), out.data_ptr(), n, h, w, c, gh, gw,
+                                   _lib.current_stream_ptr(img.device))
+    _lib.check("raftk_grid_sample", rc)
+    _lib.count_launch(1)
+    return out
+
+
+def resize_with_aligned_corners(image: torch.Tensor, shape, method: str = "bilinear", antialias: bool = True) -> torch.Tensor:
+    """NHWC align-corners bilinear resize (model.py:43-66); host-framework code, not a kernel."""
+    assert method == "bilinear", "currently only bilinear interpolation is supported"
+    x = image.permute(0, 3, 1, 2)
+    out = F.interpolate(x, size=(int(shape[1]), int(shape[2])), mode="bilinear", align_corners=True)
+    return out.permute(0, 2, 3, 1).contiguous()
+
+
 def upsample_flow(flow: torch.Tensor, up_mask: Optional[torch.Tensor] = None, factor: int = 8) -> torch.Tensor:
     """Upsample flow (B, h, w, C) by ``factor`` (model.py:69-98).
 

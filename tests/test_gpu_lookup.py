@@ -100,3 +100,15 @@ def test_linearity_at_batch_size(cuda, lib):
     assert torch.equal(o2, 4.0 * o1)
     oz = cb.index_pyramid([torch.zeros_like(t) for t in p1], coords)
     assert not oz.any()
+
+
+@pytest.mark.parametrize("c", [1, 3, 4])
+def test_grid_sample_standalone(cuda, lib, c):
+    """raftk_grid_sample (model.py:24-34) against the oracle: bit-exact, including the border cases."""
+    rng = np.random.default_rng(c)
+    n, h, w = 3, 7, 9
+    img = rng.standard_normal((n, h, w, c)).astype(F32)
+    grid = rng.uniform(-3, 12, (n, 6, 5, 2)).astype(F32)
+    grid[0, 0, :4] = [[-1.0, 0.0], [w - 1.0, h - 1.0], [w - 0.5, 2.0], [1e6, -1e6]]
+    got = J.grid_sample(torch.from_numpy(img).to(cuda), torch.from_numpy(grid).to(cuda)).cpu().numpy()
+    _assert_bit_exact(got, O.grid_sample(img, grid))
