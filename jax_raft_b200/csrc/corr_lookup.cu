@@ -128,6 +128,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
   const int lhx = lvx == 0 ? p.lh[0] : lvx == 1 ? p.lh[1] : lvx == 2 ? p.lh[2] : p.lh[3];
   const int lwx = lvx == 0 ? p.lw[0] : lvx == 1 ? p.lw[1] : lvx == 2 ? p.lw[2] : p.lw[3];
   constexpr int C = 4 * S * S;  // the fast path is instantiated for L = 4 only
+  const uint64_t pol = l2_policy_evict_last();
   const int nwarps = gridDim.x * kFastWarps;
 
   for (int q = blockIdx.x * kFastWarps + warp; q < p.Q; q += nwarps) {
@@ -155,7 +156,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
         const int lh = p.lh[k], lw = p.lw[k];
         const int gy = by + row_u, gx = (bx & ~3) + 4 * chunk;
         if (row_u < FP && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw && gx <= bx + FP - 1)
-          v[k] = __ldg(reinterpret_cast<const float4*>(p.level[k] + ((size_t)q * lh + gy) * lw + gx));
+          v[k] = ldg_f4_l2hint(reinterpret_cast<const float4*>(p.level[k] + ((size_t)q * lh + gy) * lw + gx), pol);
       }
     }
     if (FP > 8) {
@@ -165,7 +166,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
         const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
         const int gy = by + rowx, gx = (bx & ~3) + 4 * chunk;
         if ((unsigned)gy < (unsigned)lhx && (unsigned)gx < (unsigned)lwx && gx <= bx + FP - 1)
-          v[4] = __ldg(reinterpret_cast<const float4*>(levelx + ((size_t)q * lhx + gy) * lwx + gx));
+          v[4] = ldg_f4_l2hint(reinterpret_cast<const float4*>(levelx + ((size_t)q * lhx + gy) * lwx + gx), pol);
       }
     }
 #pragma unroll

@@ -46,4 +46,21 @@ __device__ __forceinline__ float4 ldg_nc_f4(const float4* p) {
   return r;
 }
 
+// L2 eviction-priority hints.  The lookup touches the same ~19 MB of pyramid rows in every one of
+// the 32 iterations of a pair (the flow moves little), while the convolutions in between stream
+// hundreds of MB through the 126 MB L2: marking the footprint reads evict_last keeps them resident
+// from one iteration to the next.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ float4 ldg_f4_l2hint(const float4* p, uint64_t pol) {
+  float4 r;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p), "l"(pol));
+  return r;
+}
+
 }  // namespace raftk
