@@ -92,3 +92,25 @@ def test_validation_loop_on_synthetic_pairs(cuda, lib):
         pairs.append((a, b, ref))  # "ground truth" = the CPU oracle's flow
     out = V.validate_pairs(model, variables, pairs, iters=4)
     assert out["epe"] <= 0.01 and out["1px"] == 1.0
+
+
+@pytest.mark.parametrize("name,h,w,iters", [("raft_small", 368, 496, 12), ("raft_large", 440, 1024, 32)])
+def test_named_configs_full_size_epe(cuda, lib, name, h, w, iters):
+    """BASELINE configs 1 and 2 at full size and iteration count (raft_small 368x496 x12;
+    raft_large 440x1024 x32 — the north-star target): final flow within 0.01 px mean EPE of the CPU
+    oracle on the same synthetic pair and the same random-init weights, through the
+    default path (TF32 library convolutions, CUDA graph)."""
+    from oracle import corr_oracle_c, raft_cpu
+
+    rng = np.random.default_rng(1)
+    img1 = rng.uniform(-1, 1, (1, h, w, 3)).astype(np.float32)
+    img2 = np.clip(np.roll(img1, (3, -5), axis=(1, 2)) + rng.normal(0, 0.02, img1.shape), -1, 1).astype(np.float32)
+    net = raft_cpu.build_modules(name, seed=0)
+    ref = raft_cpu.forward(net, img1, img2, iters, hot=corr_oracle_c)
+    variables = J.variables_from_torch_state_dict(net.state_dict())
+    model, _ = getattr(J, name)()
+    got = model.apply(variables, img1, img2, train=False, num_flow_updates=iters).cpu().numpy()
+    assert got.shape == (iters, 1, h, w, 2)
+    epe_last = _epe(got[-1], ref[-1])
+    epe_max = max(_epe(got[i], ref[i]) for i in range(iters))
+    assert epe_last <= 0.01 and epe_max <= 0.01, (epe_last, epe_max)
