@@ -148,6 +148,20 @@ int raftk_altcorr_lookup(const float* fmap1, const float* const* f2_levels, int 
 int raftk_convex_upsample(const float* flow, const float* mask, float* out, int B, int h,
                           int w, void* stream);
 
+/* Host-model glue, not a hot-path row: in place y = act(x + bias[c]) on an NHWC conv output
+ * (npix, c); act 0 none, 1 relu, 2 sigmoid, 3 tanh.  Used by jax_raft_b200/model.py after the
+ * library convolutions (ConvNormActivation / ConvGRU / FlowHead epilogues, model.py:120-159,
+ * 293-350), which are called without bias. */
+int raftk_bias_act_nhwc(float* x, const float* bias, long long npix, int c, int act, void* stream);
+
+/* Host-model glue, not a hot-path row: in place InstanceNorm (+ ReLU) of an NHWC tensor (n, npix, c),
+ * the feature encoder's norm layer (model.py:706-707, applied in ConvNormActivation, model.py:146-158):
+ * y = (x - mean[n,c]) / sqrt(var[n,c] + eps), biased variance.  c % 4 == 0, c <= 1024.
+ * scratch: raftk_instance_norm_scratch_bytes(n, c) bytes, 8-byte aligned (float64 sums). */
+size_t raftk_instance_norm_scratch_bytes(int n, int c);
+int raftk_instance_norm_nhwc(float* x, int n, int npix, int c, float eps, int relu, void* scratch,
+                             size_t scratch_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

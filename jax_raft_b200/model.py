@@ -26,6 +26,7 @@ import numpy as np
 import torch
 import torch.nn.functional as F
 
+from . import _lib
 from .corr import CorrBlock
 from .functional import make_coords_grid, upsample_flow
 
@@ -272,8 +273,53 @@ def _prepare(cfg: RaftConfig, variables: Tree, device) -> Dict[str, _ConvP]:
 # ---------------------------------------------------------------------------------------
 # Forward pieces (NCHW-shaped channels_last tensors == NHWC memory)
 # ---------------------------------------------------------------------------------------
-def _conv(x, p: _ConvP, stride=1, padding=0):
-    return F.conv2d(x, p.w, p.b, stride=stride, padding=padding)
+_ACT = {None: 0, "relu": 1, "sigmoid": 2, "tanh": 3}
+
+
+def _conv(x, p: _ConvP, stride=1, padding=0, act=None, bias=True):
+    """Library convolution + (bias, activation) epilogue.  The bias is not given to the convolution:
+    on channels_last tensors torch adds it with a strided broadcast kernel that costs more than the
+    1x1 convolutions themselves; ``raftk_bias_act_nhwc`` applies bias and activation in one pass."""
+    y = F.conv2d(x, p.w, None, stride=stride, padding=padding)
+    if not bias and act is None:
+        return y
+    if not y.is_contiguous(memory_format=torch.channels_last):
+        y = y.contiguous(memory_format=torch.channels_last)
+    n, c, h, w = y.shape
+    if not bias:
+        zero = getattr(p, "_zero_bias", None)
+        if zero is None:
+            zero = torch.zeros_like(p.b)
+            p._zero_bias = zero
+        b = zero
+    else:
+        b = p.b
+    lib = _lib.load()
+    with torch.cuda.device(y.device):
+        rc = lib.raftk_bias_act_nhwc(y.data_ptr(), b.data_ptr(), n * h * w, c, _ACT[act], _lib.current_stream_ptr(y.device))
+    _lib.check("raftk_bias_act_nhwc", rc)
+    _lib.count_launch(1)
+    return y
+
+
+def _instance_norm_(y, relu: bool, eps: float = 1e-5):
+    """In-place InstanceNorm(+ReLU) of a conv output through the glue kernel; shapes it does not
+    cover (channel counts not a multiple of 4) use the library op."""
+    n, c, h, w = y.shape
+    if c % 4 or c > 1024:
+        y = F.instance_norm(y, eps=eps)
+        return F.relu(y) if relu else y
+    if not y.is_contiguous(memory_format=torch.channels_last):
+        y = y.contiguous(memory_format=torch.channels_last)
+    lib = _lib.load()
+    nbytes = lib.raftk_instance_norm_scratch_bytes(n, c)
+    scratch = torch.empty((nbytes,), dtype=torch.uint8, device=y.device)
+    with torch.cuda.device(y.device):
+        rc = lib.raftk_instance_norm_nhwc(y.data_ptr(), n, h * w, c, eps, 1 if relu else 0, scratch.data_ptr(), nbytes,
+                                          _lib.current_stream_ptr(y.device))
+    _lib.check("raftk_instance_norm_nhwc", rc)
+    _lib.count_launch(2)
+    return y
 
 
 def _cna(P, path, x, norm, stride=1, padding=None, act=True):
@@ -281,10 +327,10 @@ def _cna(P, path, x, norm, stride=1, padding=None, act=True):
     p = P[f"{path}/layers_0"]
     if padding is None:
         padding = ((p.w.shape[2] - 1) // 2, (p.w.shape[3] - 1) // 2)
-    x = _conv(x, p, stride, padding)
     if norm == "instance":  # nn.InstanceNorm(epsilon=1e-5, no scale/bias), model.py:706-707
-        x = F.instance_norm(x, eps=1e-5)
-    return F.relu(x) if act else x
+        # a per-channel bias cancels in (x - mean) / std, so the conv bias is not applied at all
+        return _instance_norm_(_conv(x, p, stride, padding, bias=False), relu=act)
+    return _conv(x, p, stride, padding, act="relu" if act else None)
 
 
 def _encoder(P, prefix, x, layers, block, norm, strides):
@@ -321,10 +367,10 @@ def _motion_encoder(P, cfg, flow, corr_features):
 def _conv_gru(P, path, h, x, padding):
     """model.py:293-312."""
     hx = torch.cat([h, x], dim=1)
-    z = torch.sigmoid(_conv(hx, P[f"{path}/convz"], padding=padding))
-    r = torch.sigmoid(_conv(hx, P[f"{path}/convr"], padding=padding))
-    q = torch.tanh(_conv(torch.cat([r * h, x], dim=1), P[f"{path}/convq"], padding=padding))
-    return (1 - z) * h + z * q
+    z = _conv(hx, P[f"{path}/convz"], padding=padding, act="sigmoid")
+    r = _conv(hx, P[f"{path}/convr"], padding=padding, act="sigmoid")
+    q = _conv(torch.cat([r * h, x], dim=1), P[f"{path}/convq"], padding=padding, act="tanh")
+    return torch.lerp(h, q, z)  # (1 - z) * h + z * q (model.py:311) in one pass: h + z * (q - h)
 
 
 class RAFT:
@@ -399,7 +445,7 @@ class RAFT:
         x = torch.cat([context, motion], dim=1)
         for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
             hidden_state = _conv_gru(P, f"update_block/recurrent_block/convgru{gi}", hidden_state, x, pad)
-        d = F.relu(_conv(hidden_state, P["update_block/flow_head/conv1"], padding=1))
+        d = _conv(hidden_state, P["update_block/flow_head/conv1"], padding=1, act="relu")
         delta_flow = _conv(d, P["update_block/flow_head/conv2"], padding=1)
         coords1 = coords1 + delta_flow.permute(0, 2, 3, 1)
         up_mask = None
