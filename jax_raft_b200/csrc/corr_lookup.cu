@@ -1,11 +1,12 @@
 // Kernel family 2: radius-r bilinear window lookup over the correlation pyramid.
 // Replaces CorrBlock.index_pyramid (model.py:448-470) + grid_sample (model.py:24-34).
 //
-// One warp per query pixel.  Phase 1 stages, per level, the (2r+2)x(2r+2) footprint
-// that all (2r+1)^2 taps of that level touch into shared memory with lanes running along
-// footprint rows (coalesced 4-byte loads; rows are 4-byte aligned only).  Phase 2 gives
-// each lane output channels lane, lane+32, ... so the 4*(2r+1)^2*4-byte output row is
-// written with full 128-byte warp stores.
+// Two kernels, same arithmetic, same bits:
+//   corr_lookup_fast_kernel  L = 4, r in {3, 4} (the reference's configurations) — see below;
+//   corr_lookup_kernel       other radii (r <= 7) and level counts (<= 6): one warp per query pixel; phase 1
+//                            stages each level's (2r+2)^2 footprint in shared memory with lanes
+//                            along footprint rows (4-byte loads), phase 2 gives each lane channels
+//                            lane, lane+32, ... so the output row goes out as 128-byte warp stores.
 //
 // Arithmetic follows jax.scipy.ndimage.map_coordinates(order=1, mode='constant') as the
 // reference calls it, PER TAP and in float32 with no FMA contraction:
@@ -25,6 +26,7 @@ struct LookupParams {
   const float* level[RAFTK_MAX_LEVELS];
   int lh[RAFTK_MAX_LEVELS];
   int lw[RAFTK_MAX_LEVELS];
+  int aligned[RAFTK_MAX_LEVELS];  // level rows can be read as 16-byte chunks (pitch % 4 == 0, base % 16 == 0)
   const float* coords;
   float* out;
   int Q;
@@ -80,8 +82,9 @@ __global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const Lo
 }
 
 // ------------------------------------------------------------------------------------------
-// Fast path: every level has a row pitch that is a multiple of 4 floats and a 16-byte aligned
-// base (true for 440x1024 and most 32-aligned frame widths), L = 4, r in {3, 4}.
+// Fast path: L = 4, r in {3, 4}.  Levels whose row pitch is a multiple of 4 floats (and whose base
+// is 16-byte aligned: 440x1024, 1088x1920 levels 0-2, ...) are read as 16-byte chunks, the others
+// (e.g. every level of raft_small's 46x62 map) as the same chunks in four 4-byte loads.
 //
 // Persistent warps, one query at a time.  Phase 1 fetches each footprint row as the aligned
 // 16-byte chunks that cover it (3 or 4 per row) — 5 LDG.128 per lane per query instead of 13
@@ -93,6 +96,24 @@ __global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const Lo
 // lookup_taps (bit-identical results).  Coordinates beyond +-1e6 or non-finite take the generic
 // per-query routine (warp-uniform branch).
 // ------------------------------------------------------------------------------------------
+// One footprint chunk: floats [gx, gx+4) of row gy of a level slab (gx % 4 == 0), zeros where the
+// chunk leaves the level.  Aligned levels use one 16-byte load; others four 4-byte loads.
+__device__ __forceinline__ float4 load_chunk(const float* slab, int lh, int lw, int gy, int gx, bool aligned,
+                                             uint64_t pol) {
+  float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  if ((unsigned)gy >= (unsigned)lh) return v;
+  const float* row = slab + (size_t)gy * lw;
+  if (aligned) {
+    if ((unsigned)gx < (unsigned)lw) v = ldg_f4_l2hint(reinterpret_cast<const float4*>(row + gx), pol);
+  } else {
+    if ((unsigned)gx < (unsigned)lw) v.x = __ldg(row + gx);
+    if ((unsigned)(gx + 1) < (unsigned)lw) v.y = __ldg(row + gx + 1);
+    if ((unsigned)(gx + 2) < (unsigned)lw) v.z = __ldg(row + gx + 2);
+    if ((unsigned)(gx + 3) < (unsigned)lw) v.w = __ldg(row + gx + 3);
+  }
+  return v;
+}
+
 constexpr int kFastWarps = 8;
 
 template <int R>
@@ -127,6 +148,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
   const float* levelx = lvx == 0 ? p.level[0] : lvx == 1 ? p.level[1] : lvx == 2 ? p.level[2] : p.level[3];
   const int lhx = lvx == 0 ? p.lh[0] : lvx == 1 ? p.lh[1] : lvx == 2 ? p.lh[2] : p.lh[3];
   const int lwx = lvx == 0 ? p.lw[0] : lvx == 1 ? p.lw[1] : lvx == 2 ? p.lw[2] : p.lw[3];
+  const bool alignedx = (lvx == 0 ? p.aligned[0] : lvx == 1 ? p.aligned[1] : lvx == 2 ? p.aligned[2] : p.aligned[3]) != 0;
   constexpr int C = 4 * S * S;  // the fast path is instantiated for L = 4 only
   const uint64_t pol = l2_policy_evict_last();
   const int nwarps = gridDim.x * kFastWarps;
@@ -155,8 +177,8 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
         const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
         const int lh = p.lh[k], lw = p.lw[k];
         const int gy = by + row_u, gx = (bx & ~3) + 4 * chunk;
-        if (row_u < FP && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw && gx <= bx + FP - 1)
-          v[k] = ldg_f4_l2hint(reinterpret_cast<const float4*>(p.level[k] + ((size_t)q * lh + gy) * lw + gx), pol);
+        if (row_u < FP && gx <= bx + FP - 1)
+          v[k] = load_chunk(p.level[k] + (size_t)q * lh * lw, lh, lw, gy, gx, p.aligned[k] != 0, pol);
       }
     }
     if (FP > 8) {
@@ -165,8 +187,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
         const float sc = __int_as_float((127 - lvx) << 23);
         const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
         const int gy = by + rowx, gx = (bx & ~3) + 4 * chunk;
-        if ((unsigned)gy < (unsigned)lhx && (unsigned)gx < (unsigned)lwx && gx <= bx + FP - 1)
-          v[4] = ldg_f4_l2hint(reinterpret_cast<const float4*>(levelx + ((size_t)q * lhx + gy) * lwx + gx), pol);
+        if (gx <= bx + FP - 1) v[4] = load_chunk(levelx + (size_t)q * lhx * lwx, lhx, lwx, gy, gx, alignedx, pol);
       }
     }
 #pragma unroll
@@ -227,9 +248,9 @@ extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, con
   p.L = num_levels;
   p.r = radius;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  bool fast = (radius == 3 || radius == 4) && num_levels == 4;
-  for (int l = 0; l < num_levels && fast; ++l)
-    fast = (p.lw[l] % 4 == 0) && (((uintptr_t)p.level[l] & 15) == 0);
+  const bool fast = (radius == 3 || radius == 4) && num_levels == 4;
+  for (int l = 0; l < num_levels; ++l)
+    p.aligned[l] = (p.lw[l] % 4 == 0) && (((uintptr_t)p.level[l] & 15) == 0);
   if (fast) {
     const int tile = (2 * radius + 3) * 20;  // ROWS * PITCH of the kernel
     const size_t smem = (size_t)kFastWarps * 4 * tile * sizeof(float);

@@ -1,7 +1,7 @@
 // Host-model glue, NOT a row of SURVEY.md §8: InstanceNorm (+ ReLU) on an NHWC tensor, the norm
 // layer of the feature encoder (model.py:706-707: nn.InstanceNorm(epsilon=1e-5, no scale / bias);
 // applied inside ConvNormActivation, model.py:146-158).  torch runs it as two batch-norm kernels
-// (~100 us per call at 220x512x64); this is one statistics pass + one normalise pass.
+// (~100 us per call at 220x512x64); this is one statistics pass, a tiny finalise and one normalise pass.
 //
 //   y[n, p, c] = (x[n, p, c] - mean[n, c]) / sqrt(var[n, c] + eps),  var = E[x^2] - mean^2 (biased),
 // statistics accumulated in float64 so the one-pass variance does not cancel.
@@ -35,18 +35,42 @@ instnorm_stats_kernel(const float* __restrict__ x, double* __restrict__ stats, i
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) { s[i] += fs[i]; q[i] += fq[i]; }
+  }
+  // block reduction over the pixel rows, then ONE atomic per channel statistic per block
+  __shared__ double red[256][8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    red[threadIdx.x][2 * i] = s[i];
+    red[threadIdx.x][2 * i + 1] = q[i];
+  }
+  __syncthreads();
+  if (tr == 0) {
+    double acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = red[tc][i];
+    for (int r = 1; r < rows; ++r)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] += red[r * lanes_c + tc][i];
     double* dst = stats + ((size_t)n * c4 * 4 + tc * 4) * 2;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      atomicAdd(dst + 2 * i, s[i]);
-      atomicAdd(dst + 2 * i + 1, q[i]);
-    }
+    for (int i = 0; i < 8; ++i) atomicAdd(dst + i, acc[i]);
   }
+}
+
+// (sum, sum of squares) in float64 -> (mean, 1/sqrt(var + eps)) in float32, in place: slot i keeps
+// its 16 bytes, the first 8 now hold the float pair.
+__global__ void __launch_bounds__(256) instnorm_finalize_kernel(double* __restrict__ stats, int count, int npix, float eps) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const double mean = stats[2 * i] / npix;
+  const double var = stats[2 * i + 1] / npix - mean * mean;
+  const float2 mi = make_float2((float)mean, rsqrtf((float)var + eps));
+  *reinterpret_cast<float2*>(stats + 2 * i) = mi;
 }
 
 template <bool RELU>
 __global__ void __launch_bounds__(256)
-instnorm_apply_kernel(float* __restrict__ x, const double* __restrict__ stats, int npix, int c4, float eps, long long total4) {
+instnorm_apply_kernel(float* __restrict__ x, const double* __restrict__ stats, int npix, int c4, long long total4) {
   float4* x4 = reinterpret_cast<float4*>(x);
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total4; t += (long long)gridDim.x * blockDim.x) {
     const int cc = (int)(t % c4);
@@ -56,10 +80,8 @@ instnorm_apply_kernel(float* __restrict__ x, const double* __restrict__ stats, i
     float* pv = reinterpret_cast<float*>(&v);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const double mean = st[2 * i] / npix;
-      const double var = st[2 * i + 1] / npix - mean * mean;
-      const float inv = rsqrtf((float)var + eps);
-      float y = (pv[i] - (float)mean) * inv;
+      const float2 mi = __ldg(reinterpret_cast<const float2*>(st + 2 * i));
+      const float y = (pv[i] - mi.x) * mi.y;
       pv[i] = RELU ? fmaxf(y, 0.0f) : y;
     }
     x4[t] = v;
@@ -88,9 +110,10 @@ extern "C" int raftk_instance_norm_nhwc(float* x, int n, int npix, int c, float 
   const long long total4 = (long long)n * npix * (c / 4);
   long long blocks = (total4 + 255) / 256;
   if (blocks > (long long)RAFTK_SM_COUNT * 16) blocks = (long long)RAFTK_SM_COUNT * 16;
+  instnorm_finalize_kernel<<<(n * c + 255) / 256, 256, 0, s>>>(static_cast<double*>(scratch), n * c, npix, eps);
   if (relu)
-    instnorm_apply_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, eps, total4);
+    instnorm_apply_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, total4);
   else
-    instnorm_apply_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, eps, total4);
+    instnorm_apply_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, total4);
   return launch_status();
 }

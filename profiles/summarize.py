@@ -42,6 +42,34 @@ if os.path.exists(fn):
         f.writelines(rows)
     lines.append("")
 
+# ---- launch list of bench.py itself (kernels inside the CUDA graphs), aggregated per kernel ----
+fn = os.path.join(GO, f"{tag}_bench_launches.csv")
+if os.path.exists(fn):
+    rows = [l for l in open(fn) if not l.startswith("==")]
+    recs = [(r["Kernel Name"], float(r["Metric Value"].replace(",", ""))) for r in csv.DictReader(rows)
+            if r.get("Metric Name") == "gpu__time_duration.sum"]
+    tot = sum(v for _, v in recs)
+    agg = collections.defaultdict(lambda: [0, 0.0])
+    for k, v in recs:
+        k = re.sub(r"\(.*", "", k)[:100]
+        agg[k][0] += 1
+        agg[k][1] += v
+    with open(os.path.join(OUT, f"{tag}_bench_launches_summary.csv"), "w") as f:
+        f.write("kernel,launches,total_ns,mean_ns,share\n")
+        for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            f.write(f'"{k}",{n},{t:.0f},{t / n:.0f},{t / tot:.5f}\n')
+    mine = sum(t for k, (n, t) in agg.items() if "raftk" in k)
+    lines += [f"## `python bench.py --steps 2 --warmup 3 --skip-cpu-baseline --micro-batch 0` under the same ncu pass "
+              f"(`{tag}_bench_launches_summary.csv`)\n",
+              f"{len(recs)} launches over the whole command (eager warm-ups, graph capture, replays, event-timed pass); "
+              f"raftk kernels = {100 * mine / tot:.1f} % of the summed kernel time "
+              f"(of which hot-path rows: {100 * sum(t for k, (n, t) in agg.items() if 'raftk' in k and 'bias_act' not in k and 'instnorm' not in k) / tot:.1f} %).\n",
+              "| share | launches | mean us | kernel |", "|---|---|---|---|"]
+    for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        if "raftk" in k:
+            lines.append(f"| {100 * t / tot:.2f} % | {n} | {t / n / 1e3:.1f} | `{k[:70]}` |")
+    lines.append("")
+
 # ---- full captures ----
 WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "dram__throughput.avg.pct_of_peak_sustained_elapsed", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
