@@ -162,6 +162,22 @@ size_t raftk_instance_norm_scratch_bytes(int n, int c);
 int raftk_instance_norm_nhwc(float* x, int n, int npix, int c, float eps, int relu, void* scratch,
                              size_t scratch_bytes, void* stream);
 
+/* Host-model glue, not hot-path rows: the element-wise parts of ConvGRU (model.py:293-312) on NHWC
+ * tensors.  `h` points at the hidden-state channel slice inside the z/r-convolution input buffer
+ * (pixel stride ldh floats; hidden, ldh, ld_rh even, pointers 8-byte aligned); zr_pre (npix, 2*hidden) is the output of the z and r filters stacked in
+ * one convolution, bias_zr their stacked biases.
+ *   gate:   z_out (npix, hidden) = sigmoid(z_pre + bz);  rh_out (pixel stride ld_rh) = sigmoid(r_pre + br) * h
+ *   update: h = (1 - z) * h + z * tanh(q_pre + bq), written in place and to h_dense (npix, hidden). */
+int raftk_gru_gate(const float* zr_pre, const float* bias_zr, const float* h, int ldh, float* z_out,
+                   float* rh_out, int ld_rh, long long npix, int hidden, void* stream);
+int raftk_gru_update(const float* q_pre, const float* bq, const float* z, float* h, int ldh, float* h_dense,
+                     long long npix, int hidden, void* stream);
+/* MotionEncoder tail (model.py:286-290): relu(cf_pre + bias) (npix, c_cf) followed by the 2 flow
+ * channels, written at dst_a and dst_b (pixel stride ld floats) — the motion slots of the two GRU
+ * convolution input buffers.  c_cf and ld even, pointers 8-byte aligned. */
+int raftk_motion_scatter(const float* cf_pre, const float* bias, const float* flow, float* dst_a, float* dst_b,
+                         int ld, long long npix, int c_cf, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

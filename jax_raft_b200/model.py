@@ -267,6 +267,12 @@ def _prepare(cfg: RaftConfig, variables: Tree, device) -> Dict[str, _ConvP]:
             w.to(torch.float32).to(device).contiguous(memory_format=torch.channels_last),
             b.to(torch.float32).to(device),
         )
+    # ConvGRU: the z and r filters read the same input (model.py:306-307); stacked, they are one convolution
+    for gi in range(1, len(cfg.recurrent_block_kernel_size) + 1):
+        base = f"update_block/recurrent_block/convgru{gi}"
+        z, r = out[f"{base}/convz"], out[f"{base}/convr"]
+        out[f"{base}/convzr"] = _ConvP(torch.cat([z.w, r.w], dim=0).contiguous(memory_format=torch.channels_last),
+                                       torch.cat([z.b, r.b], dim=0).contiguous())
     return out
 
 
@@ -364,6 +370,79 @@ def _motion_encoder(P, cfg, flow, corr_features):
     return torch.cat([cf, flow], dim=1)
 
 
+def _motion_encoder_pre(P, cfg, flow, corr_features):
+    """model.py:260-285 up to the last convolution, whose raw output (no bias, no relu) and parameters
+    are returned for ``raftk_motion_scatter``."""
+    me = "update_block/motion_encoder"
+    corr = _cna(P, f"{me}/convcorr1", corr_features, None)
+    if len(cfg.motion_encoder_corr_layers) == 2:
+        corr = _cna(P, f"{me}/convcorr2", corr, None)
+    fl = _cna(P, f"{me}/convflow1", flow, None)
+    fl = _cna(P, f"{me}/convflow2", fl, None)
+    p = P[f"{me}/conv/layers_0"]
+    pad = ((p.w.shape[2] - 1) // 2, (p.w.shape[3] - 1) // 2)
+    return _cl(F.conv2d(torch.cat([corr, fl], dim=1), p.w, None, padding=pad)), p
+
+
+def _cl(y):
+    return y if y.is_contiguous(memory_format=torch.channels_last) else y.contiguous(memory_format=torch.channels_last)
+
+
+class _RecurrentState:
+    """The two ConvGRU convolution input buffers with the hidden state, context and motion features in
+    channel slices (csrc/gru_glue.cu), so UpdateCell's three concatenations (model.py:289, 305, 308, 501)
+    are never materialised.  ``A = [h | context | motion | flow]``, ``B = [r*h | context | motion | flow]``."""
+
+    def __init__(self, cfg: RaftConfig, hidden: torch.Tensor, context: torch.Tensor):
+        n, hid, h, w = hidden.shape
+        ctx = context.shape[1]
+        self.hid, self.ctx, self.c_cf = hid, ctx, cfg.motion_encoder_out_channels - 2
+        self.ld = hid + ctx + cfg.motion_encoder_out_channels
+        self.npix = n * h * w
+        opts = dict(dtype=torch.float32, device=hidden.device, memory_format=torch.channels_last)
+        self.A = torch.empty((n, self.ld, h, w), **opts)
+        self.B = torch.empty((n, self.ld, h, w), **opts)
+        self.z = torch.empty((n, hid, h, w), **opts)
+        self.h = torch.empty((n, hid, h, w), **opts)  # dense copy of the hidden state for the heads
+        self.A[:, :hid] = hidden
+        self.h.copy_(hidden)
+        self.A[:, hid:hid + ctx] = context
+        self.B[:, hid:hid + ctx] = context
+
+    @staticmethod
+    def supported(cfg: RaftConfig) -> bool:
+        hid = cfg.recurrent_block_hidden_state_size
+        ld = cfg.context_encoder_layers[-1] + cfg.motion_encoder_out_channels  # hid + ctx + motion
+        return hid % 2 == 0 and ld % 2 == 0 and cfg.motion_encoder_out_channels % 2 == 0
+
+    def scatter_motion(self, cf_pre, p, flow_nhwc):
+        lib = _lib.load()
+        off = 4 * (self.hid + self.ctx)
+        with torch.cuda.device(cf_pre.device):
+            rc = lib.raftk_motion_scatter(cf_pre.data_ptr(), p.b.data_ptr(), flow_nhwc.data_ptr(), self.A.data_ptr() + off,
+                                          self.B.data_ptr() + off, self.ld, self.npix, self.c_cf,
+                                          _lib.current_stream_ptr(cf_pre.device))
+        _lib.check("raftk_motion_scatter", rc)
+        _lib.count_launch(1)
+
+    def gru(self, P, path, padding):
+        """model.py:293-312 on the slices."""
+        lib = _lib.load()
+        pzr, pq = P[f"{path}/convzr"], P[f"{path}/convq"]
+        dev = self.A.device
+        zr_pre = _cl(F.conv2d(self.A, pzr.w, None, padding=padding))
+        with torch.cuda.device(dev):
+            rc = lib.raftk_gru_gate(zr_pre.data_ptr(), pzr.b.data_ptr(), self.A.data_ptr(), self.ld, self.z.data_ptr(),
+                                    self.B.data_ptr(), self.ld, self.npix, self.hid, _lib.current_stream_ptr(dev))
+        _lib.check("raftk_gru_gate", rc)
+        q_pre = _cl(F.conv2d(self.B, pq.w, None, padding=padding))
+        with torch.cuda.device(dev):
+            rc = lib.raftk_gru_update(q_pre.data_ptr(), pq.b.data_ptr(), self.z.data_ptr(), self.A.data_ptr(), self.ld,
+                                      self.h.data_ptr(), self.npix, self.hid, _lib.current_stream_ptr(dev))
+        _lib.check("raftk_gru_update", rc)
+        _lib.count_launch(2)
+
+
 def _conv_gru(P, path, h, x, padding):
     """model.py:293-312."""
     hx = torch.cat([h, x], dim=1)
@@ -376,8 +455,11 @@ def _conv_gru(P, path, h, x, padding):
 class RAFT:
     """Counterpart of the reference's ``RAFT`` module (model.py:513-605) + ``UpdateCell`` (484-510)."""
 
-    def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32"):
+    def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32", fused_update: bool = True):
         assert precision in ("tf32", "fp32")
+        # fused_update: UpdateCell's element-wise work through csrc/gru_glue.cu (same arithmetic as the
+        # unfused path, which stays for configurations whose channel counts are odd and for A/B tests)
+        self.fused_update = fused_update and _RecurrentState.supported(config)
         self.config = config
         self.corr_block = corr_block or CorrBlock(config.corr_block_num_levels, config.corr_block_radius)
         expected = config.corr_block_num_levels * (2 * config.corr_block_radius + 1) ** 2
@@ -427,24 +509,33 @@ class RAFT:
 
             coords0 = make_coords_grid(batch_size, h // 8, w // 8, device=image1.device)
             coords1 = coords0.clone()
+            state = _RecurrentState(cfg, hidden_state, context) if self.fused_update else None
 
             flows = []
             for _ in range(num_flow_updates):  # nn.scan(UpdateCell), model.py:589-603
-                coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context)
+                coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context, state)
                 flows.append(up)
             return torch.stack(flows, dim=0)
         finally:
             torch.backends.cudnn.allow_tf32 = prev
 
     # -- model.py:494-510 ---------------------------------------------------------------
-    def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context):
+    def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context, state=None):
         cfg = self.config
         corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
-        flow = (coords1 - coords0).permute(0, 3, 1, 2)
-        motion = _motion_encoder(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
-        x = torch.cat([context, motion], dim=1)
-        for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
-            hidden_state = _conv_gru(P, f"update_block/recurrent_block/convgru{gi}", hidden_state, x, pad)
+        flow_nhwc = coords1 - coords0
+        flow = flow_nhwc.permute(0, 3, 1, 2)
+        if state is not None:
+            cf_pre, p = _motion_encoder_pre(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
+            state.scatter_motion(cf_pre, p, flow_nhwc)
+            for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
+                state.gru(P, f"update_block/recurrent_block/convgru{gi}", pad)
+            hidden_state = state.h
+        else:
+            motion = _motion_encoder(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
+            x = torch.cat([context, motion], dim=1)
+            for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
+                hidden_state = _conv_gru(P, f"update_block/recurrent_block/convgru{gi}", hidden_state, x, pad)
         d = _conv(hidden_state, P["update_block/flow_head/conv1"], padding=1, act="relu")
         delta_flow = _conv(d, P["update_block/flow_head/conv2"], padding=1)
         coords1 = coords1 + delta_flow.permute(0, 2, 3, 1)
@@ -541,6 +632,7 @@ class _GraphRunner:
 def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs):
     corr_block = kwargs.pop("corr_block", None)
     precision = kwargs.pop("precision", "tf32")
+    fused_update = kwargs.pop("fused_update", True)
     if kwargs:
         raise TypeError(
             f"unsupported keyword(s) {sorted(kwargs)}: this build replaces the correlation block "
@@ -549,14 +641,14 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
         # a local copy of the reference's released .msgpack (model.py:17-21) or of a converted one
         from .checkpoint import load_msgpack
 
-        model = RAFT(cfg, corr_block=corr_block, precision=precision)
+        model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update)
         return model, load_msgpack(pretrained)
     if pretrained:
         # model.py:684-689 downloads a msgpack from GitHub; this environment has no network.
         raise RuntimeError(
             "pretrained=True needs network access (model.py:17-21, 684-689); pass pretrained='<file>.msgpack' "
             "(a local copy of the released checkpoint) or use variables_from_torch_state_dict(torch.load(path))")
-    model = RAFT(cfg, corr_block=corr_block, precision=precision)
+    model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update)
     return model, model.init(seed)
 
 

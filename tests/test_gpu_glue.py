@@ -45,3 +45,73 @@ def test_instance_norm(cuda, lib, shape, relu):
                                           ctypes.c_void_p(torch.cuda.current_stream(cuda).cuda_stream))
     _lib.check("raftk_instance_norm_nhwc", rc)
     assert torch.allclose(y.double(), ref, rtol=0, atol=2e-5)
+
+
+def _stream(cuda):
+    return ctypes.c_void_p(torch.cuda.current_stream(cuda).cuda_stream)
+
+
+@pytest.mark.parametrize("hid,extra", [(128, 256), (96, 146), (6, 10)])
+def test_gru_gate_and_update(cuda, lib, hid, extra):
+    """ConvGRU's element-wise halves (model.py:306-311) on channel slices of the conv input buffers."""
+    gen = torch.Generator(device=cuda).manual_seed(hid)
+    npix, ld = 2 * 7 * 9, hid + extra
+    A = torch.randn((npix, ld), device=cuda, generator=gen)
+    B = torch.randn((npix, ld), device=cuda, generator=gen)
+    zr_pre = torch.randn((npix, 2 * hid), device=cuda, generator=gen) * 2
+    bzr = torch.randn((2 * hid,), device=cuda, generator=gen)
+    q_pre = torch.randn((npix, hid), device=cuda, generator=gen) * 2
+    bq = torch.randn((hid,), device=cuda, generator=gen)
+    h = A[:, :hid].clone()
+    z_ref = torch.sigmoid(zr_pre[:, :hid] + bzr[:hid])
+    rh_ref = torch.sigmoid(zr_pre[:, hid:] + bzr[hid:]) * h
+    h_ref = (1 - z_ref) * h + z_ref * torch.tanh(q_pre + bq)
+    A0, B0 = A.clone(), B.clone()
+
+    z = torch.empty((npix, hid), device=cuda)
+    with torch.cuda.device(cuda):
+        rc = lib.raftk_gru_gate(zr_pre.data_ptr(), bzr.data_ptr(), A.data_ptr(), ld, z.data_ptr(), B.data_ptr(), ld, npix, hid,
+                                _stream(cuda))
+    _lib.check("raftk_gru_gate", rc)
+    assert torch.allclose(z, z_ref, rtol=1e-6, atol=1e-6)
+    assert torch.allclose(B[:, :hid], rh_ref, rtol=1e-6, atol=1e-6)
+    assert torch.equal(B[:, hid:], B0[:, hid:]) and torch.equal(A, A0)  # nothing outside the slice moves
+
+    hd = torch.empty((npix, hid), device=cuda)
+    with torch.cuda.device(cuda):
+        rc = lib.raftk_gru_update(q_pre.data_ptr(), bq.data_ptr(), z.data_ptr(), A.data_ptr(), ld, hd.data_ptr(), npix, hid,
+                                  _stream(cuda))
+    _lib.check("raftk_gru_update", rc)
+    assert torch.allclose(hd, h_ref, rtol=1e-5, atol=1e-6)
+    assert torch.equal(A[:, :hid], hd) and torch.equal(A[:, hid:], A0[:, hid:])
+
+
+@pytest.mark.parametrize("c_cf,off,ld", [(126, 256, 384), (80, 160, 242)])
+def test_motion_scatter(cuda, lib, c_cf, off, ld):
+    """MotionEncoder tail (model.py:286-290): relu(conv + bias) ++ flow into both GRU input buffers."""
+    gen = torch.Generator(device=cuda).manual_seed(c_cf)
+    npix = 3 * 5 * 11
+    cf_pre = torch.randn((npix, c_cf), device=cuda, generator=gen)
+    bias = torch.randn((c_cf,), device=cuda, generator=gen)
+    flow = torch.randn((npix, 2), device=cuda, generator=gen)
+    A = torch.full((npix, ld), 7.0, device=cuda)
+    B = torch.full((npix, ld), 9.0, device=cuda)
+    with torch.cuda.device(cuda):
+        rc = lib.raftk_motion_scatter(cf_pre.data_ptr(), bias.data_ptr(), flow.data_ptr(), A.data_ptr() + 4 * off,
+                                      B.data_ptr() + 4 * off, ld, npix, c_cf, _stream(cuda))
+    _lib.check("raftk_motion_scatter", rc)
+    ref = torch.cat([F.relu(cf_pre + bias), flow], dim=1)
+    for buf, fill in ((A, 7.0), (B, 9.0)):
+        assert torch.equal(buf[:, off:off + c_cf + 2], ref)
+        assert (buf[:, :off] == fill).all() and (buf[:, off + c_cf + 2:] == fill).all()
+
+
+def test_gru_glue_rejects_bad_shapes(cuda, lib):
+    x = torch.zeros((64,), device=cuda)
+    p = x.data_ptr()
+    assert lib.raftk_gru_gate(p, p, p, 7, p, p, 8, 1, 4, None) == -2      # odd stride
+    assert lib.raftk_gru_gate(p, p, p, 2, p, p, 8, 1, 4, None) == -2      # stride < hidden
+    assert lib.raftk_gru_update(p, p, p, p + 4, 8, p, 1, 4, None) == -6   # 4-byte aligned pointer
+    assert lib.raftk_motion_scatter(p, p, p, p, p, 8, 1, 8, None) == -2   # ld < c_cf + 2
+    assert lib.raftk_gru_gate(None, p, p, 8, p, p, 8, 1, 4, None) == -1
+    assert lib.raftk_gru_gate(None, None, None, 8, None, None, 8, 0, 4, None) == 0  # empty batch

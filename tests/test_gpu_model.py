@@ -49,6 +49,20 @@ def test_flow_matches_cpu_reference(cuda, lib, golden, name, precision):
     assert _epe(a.cpu().numpy()[-1], got[-1]) <= 1e-3
 
 
+@pytest.mark.parametrize("name", ["raft_small", "raft_large"])
+def test_fused_update_block_matches_unfused(cuda, lib, golden, name):
+    """The channel-slice GRU path (csrc/gru_glue.cu) against the concatenating one: same arithmetic,
+    full-precision convolutions, so only the library's choice of convolution algorithm may differ."""
+    g = golden(f"e2e_{name}")
+    img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
+    fused, variables = getattr(J, name)(precision="fp32", seed=3)
+    plain, _ = getattr(J, name)(precision="fp32", fused_update=False)
+    assert fused.fused_update and not plain.fused_update
+    a = fused.apply(variables, img1, img2, num_flow_updates=iters, use_cuda_graph=False).cpu().numpy()
+    b = plain.apply(variables, img1, img2, num_flow_updates=iters, use_cuda_graph=False).cpu().numpy()
+    assert _epe(a[-1], b[-1]) <= 1e-3
+
+
 def test_alt_corr_block_drops_in(cuda, lib, golden):
     g = golden("e2e_raft_large")
     img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
