@@ -147,6 +147,10 @@ int raftk_altcorr_lookup(const float* fmap1, const float* const* f2_levels, int 
  * ---------------------------------------------------------------------------------- */
 int raftk_convex_upsample(const float* flow, const float* mask, float* out, int B, int h,
                           int w, void* stream);
+/* Same with logits mask + mask_bias[channel] (device, 576 floats, 16-byte aligned): lets the caller
+ * skip the bias pass of the mask predictor's last convolution (model.py:398-400). */
+int raftk_convex_upsample_bias(const float* flow, const float* mask, const float* mask_bias, float* out, int B,
+                               int h, int w, void* stream);
 
 /* Host-model glue, not a hot-path row: in place y = act(x + bias[c]) on an NHWC conv output
  * (npix, c); act 0 none, 1 relu, 2 sigmoid, 3 tanh.  Used by jax_raft_b200/model.py after the
@@ -175,6 +179,10 @@ int raftk_gru_update(const float* q_pre, const float* bq, const float* z, float*
 /* MotionEncoder tail (model.py:286-290): relu(cf_pre + bias) (npix, c_cf) followed by the 2 flow
  * channels, written at dst_a and dst_b (pixel stride ld floats) — the motion slots of the two GRU
  * convolution input buffers.  c_cf and ld even, pointers 8-byte aligned. */
+/* UpdateCell tail (model.py:504-506) on (npix, 2) NHWC arrays: coords1 += delta_pre + bias (in place),
+ * flow = coords1 - coords0.  bias: device, the flow head's two bias values, 8-byte aligned. */
+int raftk_flow_update(const float* delta_pre, const float* bias, const float* coords0, float* coords1,
+                      float* flow, long long npix, void* stream);
 int raftk_motion_scatter(const float* cf_pre, const float* bias, const float* flow, float* dst_a, float* dst_b,
                          int ld, long long npix, int c_cf, void* stream);
 

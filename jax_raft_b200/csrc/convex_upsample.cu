@@ -16,8 +16,11 @@ namespace raftk {
 
 constexpr int kUpsWarps = 8;
 
+// HAS_BIAS: the logits are mask + bias[channel] (the mask predictor's last convolution without its
+// bias pass; the sum is rounded exactly as a separate bias kernel would round it).
+template <bool HAS_BIAS>
 __global__ void __launch_bounds__(kUpsWarps * 32)
-convex_upsample_kernel(const float* __restrict__ flow, const float* __restrict__ mask,
+convex_upsample_kernel(const float* __restrict__ flow, const float* __restrict__ mask, const float* __restrict__ bias,
                        float* __restrict__ out, int B, int h, int w) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sub = lane & 15;  // owns sub-pixels 4*sub .. 4*sub+3
@@ -33,6 +36,14 @@ convex_upsample_kernel(const float* __restrict__ flow, const float* __restrict__
   float4 m[9];
 #pragma unroll
   for (int k = 0; k < 9; ++k) m[k] = ldg_nc_f4(mrow + k * 16);
+  if (HAS_BIAS) {
+    const float4* brow = reinterpret_cast<const float4*>(bias) + sub;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const float4 bk = __ldg(brow + k * 16);
+      m[k].x += bk.x; m[k].y += bk.y; m[k].z += bk.z; m[k].w += bk.w;
+    }
+  }
 
   // 8 * flow of the 9 neighbours (zero outside the image: SAME padding, model.py:91-92)
   float fxk[9], fyk[9];
@@ -77,18 +88,32 @@ convex_upsample_kernel(const float* __restrict__ flow, const float* __restrict__
 
 }  // namespace raftk
 
-extern "C" int raftk_convex_upsample(const float* flow, const float* mask, float* out, int B,
-                                     int h, int w, void* stream) {
+static int convex_upsample_launch(const float* flow, const float* mask, const float* bias, bool has_bias, float* out,
+                                  int B, int h, int w, void* stream) {
   using namespace raftk;
   if (B < 0 || h <= 0 || w <= 0) return RAFTK_ERR_SHAPE;
   if (B == 0) return RAFTK_OK;  // empty batch: pointers may be NULL
-  if (!flow || !mask || !out) return RAFTK_ERR_NULL;
-  if (((uintptr_t)flow & 7) || ((uintptr_t)mask & 15) || ((uintptr_t)out & 15)) return RAFTK_ERR_ALIGN;
+  if (!flow || !mask || !out || (has_bias && !bias)) return RAFTK_ERR_NULL;
+  if (((uintptr_t)flow & 7) || ((uintptr_t)mask & 15) || ((uintptr_t)out & 15) || ((uintptr_t)bias & 15))
+    return RAFTK_ERR_ALIGN;
   const long long npix = (long long)B * h * w;
   if (npix == 0) return RAFTK_OK;
   const long long blocks = (npix + 2 * kUpsWarps - 1) / (2 * kUpsWarps);
   if (blocks > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
-  convex_upsample_kernel<<<(unsigned)blocks, kUpsWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-      flow, mask, out, B, h, w);
+  auto s = static_cast<cudaStream_t>(stream);
+  if (has_bias)
+    convex_upsample_kernel<true><<<(unsigned)blocks, kUpsWarps * 32, 0, s>>>(flow, mask, bias, out, B, h, w);
+  else
+    convex_upsample_kernel<false><<<(unsigned)blocks, kUpsWarps * 32, 0, s>>>(flow, mask, nullptr, out, B, h, w);
   return launch_status();
+}
+
+extern "C" int raftk_convex_upsample(const float* flow, const float* mask, float* out, int B,
+                                     int h, int w, void* stream) {
+  return convex_upsample_launch(flow, mask, nullptr, false, out, B, h, w, stream);
+}
+
+extern "C" int raftk_convex_upsample_bias(const float* flow, const float* mask, const float* mask_bias, float* out,
+                                          int B, int h, int w, void* stream) {
+  return convex_upsample_launch(flow, mask, mask_bias, true, out, B, h, w, stream);
 }

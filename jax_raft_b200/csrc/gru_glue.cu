@@ -92,6 +92,21 @@ motion_scatter_kernel(const float* __restrict__ cf_pre, const float* __restrict_
   }
 }
 
+// UpdateCell tail (model.py:504-506): coords1 += delta_pre + bias;  flow = coords1 - coords0.
+__global__ void __launch_bounds__(256)
+flow_update_kernel(const float2* __restrict__ delta_pre, const float2* __restrict__ bias_p, const float2* __restrict__ coords0,
+                   float2* __restrict__ coords1, float2* __restrict__ flow, long long npix) {
+  const float2 bias = __ldg(bias_p);
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < npix; t += (long long)gridDim.x * blockDim.x) {
+    const float2 d = delta_pre[t], c0 = coords0[t];
+    float2 c1 = coords1[t];
+    c1.x = __fadd_rn(c1.x, __fadd_rn(d.x, bias.x));
+    c1.y = __fadd_rn(c1.y, __fadd_rn(d.y, bias.y));
+    coords1[t] = c1;
+    flow[t] = make_float2(__fadd_rn(c1.x, -c0.x), __fadd_rn(c1.y, -c0.y));
+  }
+}
+
 static int grid_for(long long total) {
   long long blocks = (total + 255) / 256;
   if (blocks > (long long)RAFTK_SM_COUNT * 16) blocks = (long long)RAFTK_SM_COUNT * 16;
@@ -143,5 +158,18 @@ extern "C" int raftk_motion_scatter(const float* cf_pre, const float* bias, cons
   if (((uintptr_t)cf_pre | (uintptr_t)bias | (uintptr_t)flow | (uintptr_t)dst_a | (uintptr_t)dst_b) & 7) return RAFTK_ERR_ALIGN;
   motion_scatter_kernel<<<grid_for(npix * (c_cf / 2 + 1)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       cf_pre, bias, flow, dst_a, dst_b, ld, npix, c_cf);
+  return launch_status();
+}
+
+extern "C" int raftk_flow_update(const float* delta_pre, const float* bias, const float* coords0, float* coords1,
+                                 float* flow, long long npix, void* stream) {
+  using namespace raftk;
+  if (npix < 0) return RAFTK_ERR_SHAPE;
+  if (npix == 0) return RAFTK_OK;
+  if (!delta_pre || !bias || !coords0 || !coords1 || !flow) return RAFTK_ERR_NULL;
+  if (((uintptr_t)delta_pre | (uintptr_t)bias | (uintptr_t)coords0 | (uintptr_t)coords1 | (uintptr_t)flow) & 7) return RAFTK_ERR_ALIGN;
+  flow_update_kernel<<<grid_for(npix), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float2*>(delta_pre), reinterpret_cast<const float2*>(bias),
+      reinterpret_cast<const float2*>(coords0), reinterpret_cast<float2*>(coords1), reinterpret_cast<float2*>(flow), npix);
   return launch_status();
 }

@@ -51,13 +51,18 @@ def resize_with_aligned_corners(image: torch.Tensor, shape, method: str = "bilin
     return out.permute(0, 2, 3, 1).contiguous()
 
 
-def upsample_flow(flow: torch.Tensor, up_mask: Optional[torch.Tensor] = None, factor: int = 8) -> torch.Tensor:
+def upsample_flow(flow: torch.Tensor, up_mask: Optional[torch.Tensor] = None, factor: int = 8, *,
+                  mask_bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Upsample flow (B, h, w, C) by ``factor`` (model.py:69-98).
 
     With ``up_mask`` (B, h, w, 9*factor*factor): convex combination of the 3x3 neighbours with
     softmax weights (model.py:85-98) — the CUDA kernel, which implements factor 8 and C = 2 (the
     only configuration the reference's models use).  Without: ``factor *`` align-corners bilinear
     resize (model.py:79-83).
+
+    Not in the reference's signature: ``mask_bias`` (576,) is added to ``up_mask`` inside the kernel
+    (the mask predictor's bias without a separate pass) and ``out`` is a preallocated contiguous
+    (B, 8h, 8w, 2) result buffer.
     """
     batch_size, h, w, num_channels = flow.shape
     if up_mask is None:
@@ -70,11 +75,21 @@ def upsample_flow(flow: torch.Tensor, up_mask: Optional[torch.Tensor] = None, fa
         raise NotImplementedError("the convex upsampling kernel implements factor=8, 2 flow channels")
     flow = _check_cuda_f32("flow", flow)
     up_mask = _check_cuda_f32("up_mask", up_mask)
-    out = torch.empty((batch_size, 8 * h, 8 * w, 2), dtype=torch.float32, device=flow.device)
+    if out is None:
+        out = torch.empty((batch_size, 8 * h, 8 * w, 2), dtype=torch.float32, device=flow.device)
+    else:
+        assert out.shape == (batch_size, 8 * h, 8 * w, 2) and out.dtype == torch.float32 and out.is_contiguous()
+        assert out.device == flow.device
     lib = _lib.load()
     with torch.cuda.device(flow.device):
-        rc = lib.raftk_convex_upsample(flow.data_ptr(), up_mask.data_ptr(), out.data_ptr(), batch_size, h, w,
-                                       _lib.current_stream_ptr(flow.device))
+        if mask_bias is None:
+            rc = lib.raftk_convex_upsample(flow.data_ptr(), up_mask.data_ptr(), out.data_ptr(), batch_size, h, w,
+                                           _lib.current_stream_ptr(flow.device))
+        else:
+            mask_bias = _check_cuda_f32("mask_bias", mask_bias)
+            assert mask_bias.shape == (9 * factor * factor,)
+            rc = lib.raftk_convex_upsample_bias(flow.data_ptr(), up_mask.data_ptr(), mask_bias.data_ptr(), out.data_ptr(),
+                                                batch_size, h, w, _lib.current_stream_ptr(flow.device))
     _lib.check("raftk_convex_upsample", rc)
     _lib.count_launch(1)
     return out

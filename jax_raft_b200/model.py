@@ -404,6 +404,7 @@ class _RecurrentState:
         self.B = torch.empty((n, self.ld, h, w), **opts)
         self.z = torch.empty((n, hid, h, w), **opts)
         self.h = torch.empty((n, hid, h, w), **opts)  # dense copy of the hidden state for the heads
+        self.flow = torch.zeros((n, h, w, 2), dtype=torch.float32, device=hidden.device)  # coords1 - coords0
         self.A[:, :hid] = hidden
         self.h.copy_(hidden)
         self.A[:, hid:hid + ctx] = context
@@ -423,6 +424,15 @@ class _RecurrentState:
                                           self.B.data_ptr() + off, self.ld, self.npix, self.c_cf,
                                           _lib.current_stream_ptr(cf_pre.device))
         _lib.check("raftk_motion_scatter", rc)
+        _lib.count_launch(1)
+
+    def update_flow(self, delta_pre, p, coords0, coords1):
+        """model.py:504-506: coords1 += conv + bias (in place); self.flow = coords1 - coords0."""
+        lib = _lib.load()
+        with torch.cuda.device(coords1.device):
+            rc = lib.raftk_flow_update(delta_pre.data_ptr(), p.b.data_ptr(), coords0.data_ptr(), coords1.data_ptr(),
+                                       self.flow.data_ptr(), self.npix, _lib.current_stream_ptr(coords1.device))
+        _lib.check("raftk_flow_update", rc)
         _lib.count_launch(1)
 
     def gru(self, P, path, padding):
@@ -511,19 +521,22 @@ class RAFT:
             coords1 = coords0.clone()
             state = _RecurrentState(cfg, hidden_state, context) if self.fused_update else None
 
-            flows = []
-            for _ in range(num_flow_updates):  # nn.scan(UpdateCell), model.py:589-603
-                coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context, state)
+            flows, out = [], None
+            if state is not None and cfg.use_mask_predictor:  # the upsampler writes the stacked result directly
+                out = torch.empty((num_flow_updates, batch_size, h, w, 2), dtype=torch.float32, device=image1.device)
+            for i in range(num_flow_updates):  # nn.scan(UpdateCell), model.py:589-603
+                coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context, state,
+                                                              out=None if out is None else out[i])
                 flows.append(up)
-            return torch.stack(flows, dim=0)
+            return out if out is not None else torch.stack(flows, dim=0)
         finally:
             torch.backends.cudnn.allow_tf32 = prev
 
     # -- model.py:494-510 ---------------------------------------------------------------
-    def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context, state=None):
+    def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context, state=None, out=None):
         cfg = self.config
         corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
-        flow_nhwc = coords1 - coords0
+        flow_nhwc = state.flow if state is not None else coords1 - coords0
         flow = flow_nhwc.permute(0, 3, 1, 2)
         if state is not None:
             cf_pre, p = _motion_encoder_pre(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
@@ -537,6 +550,15 @@ class RAFT:
             for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
                 hidden_state = _conv_gru(P, f"update_block/recurrent_block/convgru{gi}", hidden_state, x, pad)
         d = _conv(hidden_state, P["update_block/flow_head/conv1"], padding=1, act="relu")
+        if state is not None:
+            p = P["update_block/flow_head/conv2"]
+            state.update_flow(_cl(F.conv2d(d, p.w, None, padding=1)), p, coords0, coords1)
+            if cfg.use_mask_predictor:  # model.py:377-400; the upsampler adds the last bias itself
+                m = _cna(P, "mask_predictor/convrelu", hidden_state, None)
+                pm = P["mask_predictor/conv"]
+                up_mask = _cl(F.conv2d(m, pm.w, None)).permute(0, 2, 3, 1)
+                return coords1, hidden_state, upsample_flow(state.flow, up_mask, mask_bias=pm.b, out=out)
+            return coords1, hidden_state, upsample_flow(flow=state.flow)
         delta_flow = _conv(d, P["update_block/flow_head/conv2"], padding=1)
         coords1 = coords1 + delta_flow.permute(0, 2, 3, 1)
         up_mask = None

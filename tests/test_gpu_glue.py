@@ -115,3 +115,21 @@ def test_gru_glue_rejects_bad_shapes(cuda, lib):
     assert lib.raftk_motion_scatter(p, p, p, p, p, 8, 1, 8, None) == -2   # ld < c_cf + 2
     assert lib.raftk_gru_gate(None, p, p, 8, p, p, 8, 1, 4, None) == -1
     assert lib.raftk_gru_gate(None, None, None, 8, None, None, 8, 0, 4, None) == 0  # empty batch
+
+
+def test_flow_update(cuda, lib):
+    """UpdateCell tail (model.py:504-506), bit-exact against the same float32 sequence in torch."""
+    gen = torch.Generator(device=cuda).manual_seed(5)
+    npix = 2 * 13 * 17
+    delta = torch.randn((npix, 2), device=cuda, generator=gen)
+    bias = torch.randn((2,), device=cuda, generator=gen)
+    c0 = torch.rand((npix, 2), device=cuda, generator=gen) * 100
+    c1 = c0 + torch.randn((npix, 2), device=cuda, generator=gen) * 5
+    ref_c1 = c1 + (delta + bias)
+    ref_flow = ref_c1 - c0
+    flow = torch.empty_like(c1)
+    with torch.cuda.device(cuda):
+        rc = lib.raftk_flow_update(delta.data_ptr(), bias.data_ptr(), c0.data_ptr(), c1.data_ptr(), flow.data_ptr(), npix,
+                                   _stream(cuda))
+    _lib.check("raftk_flow_update", rc)
+    assert torch.equal(c1, ref_c1) and torch.equal(flow, ref_flow)

@@ -63,3 +63,19 @@ def test_convexity_properties_at_batch_size(cuda, lib):
 def test_empty_batch(cuda, lib):
     out = J.upsample_flow(torch.zeros((0, 4, 4, 2), device=cuda), torch.zeros((0, 4, 4, 576), device=cuda))
     assert out.shape == (0, 32, 32, 2)
+
+
+def test_bias_variant_and_out_buffer(cuda, lib):
+    """raftk_convex_upsample_bias: logits mask + bias[channel] give the bits of the plain entry on the
+    pre-added mask; ``out=`` writes into the caller's buffer."""
+    b, h, w = 2, 9, 14
+    gen = torch.Generator(device=cuda).manual_seed(7)
+    flow = torch.randn((b, h, w, 2), device=cuda, generator=gen) * 4
+    mask = torch.randn((b, h, w, 576), device=cuda, generator=gen) * 2
+    bias = torch.randn((576,), device=cuda, generator=gen)
+    ref = J.upsample_flow(flow, mask + bias)
+    buf = torch.full((3, b, 8 * h, 8 * w, 2), -1.0, device=cuda)
+    got = J.upsample_flow(flow, mask, mask_bias=bias, out=buf[1])
+    assert got.data_ptr() == buf[1].data_ptr()
+    assert torch.equal(buf[1], ref)
+    assert (buf[0] == -1).all() and (buf[2] == -1).all()
