@@ -280,12 +280,19 @@ def _prepare(cfg: RaftConfig, variables: Tree, device) -> Dict[str, _ConvP]:
 # Forward pieces (NCHW-shaped channels_last tensors == NHWC memory)
 # ---------------------------------------------------------------------------------------
 _ACT = {None: 0, "relu": 1, "sigmoid": 2, "tanh": 3}
+# conv + bias + relu as the library's fused convolution (one launch instead of conv + bias_act);
+# RAFTK_CUDNN_FUSED_RELU=0 restores the two-launch form for A/B timing
+_CUDNN_FUSED_RELU = bool(int(__import__("os").environ.get("RAFTK_CUDNN_FUSED_RELU", "1")))
 
 
 def _conv(x, p: _ConvP, stride=1, padding=0, act=None, bias=True):
     """Library convolution + (bias, activation) epilogue.  The bias is not given to the convolution:
     on channels_last tensors torch adds it with a strided broadcast kernel that costs more than the
     1x1 convolutions themselves; ``raftk_bias_act_nhwc`` applies bias and activation in one pass."""
+    if _CUDNN_FUSED_RELU and act == "relu" and bias:
+        pad = (padding, padding) if isinstance(padding, int) else tuple(padding)
+        st = (stride, stride) if isinstance(stride, int) else tuple(stride)
+        return torch.cudnn_convolution_relu(x, p.w, p.b, st, pad, (1, 1), 1)
     y = F.conv2d(x, p.w, None, stride=stride, padding=padding)
     if not bias and act is None:
         return y
