@@ -506,7 +506,9 @@ class RAFT:
         assert (h, w) == tuple(image2.shape[-3:-1]), "input images should have the same shape"
         assert (h % 8 == 0) and (w % 8 == 0), "input image H and W should be divisible by 8"
         prev = torch.backends.cudnn.allow_tf32
+        prev_bench = torch.backends.cudnn.benchmark
         torch.backends.cudnn.allow_tf32 = self.precision == "tf32"
+        torch.backends.cudnn.benchmark = True  # the library times its engines once per convolution shape
         try:
             x = torch.cat([image1, image2], dim=0).permute(0, 3, 1, 2)  # NHWC memory, NCHW view
             fmaps = _encoder(P, "feature_encoder", x, cfg.feature_encoder_layers, cfg.feature_encoder_block,
@@ -538,6 +540,7 @@ class RAFT:
             return out if out is not None else torch.stack(flows, dim=0)
         finally:
             torch.backends.cudnn.allow_tf32 = prev
+            torch.backends.cudnn.benchmark = prev_bench
 
     # -- model.py:494-510 ---------------------------------------------------------------
     def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context, state=None, out=None):
