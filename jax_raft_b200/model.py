@@ -377,20 +377,6 @@ def _motion_encoder(P, cfg, flow, corr_features):
     return torch.cat([cf, flow], dim=1)
 
 
-def _motion_encoder_pre(P, cfg, flow, corr_features):
-    """model.py:260-285 up to the last convolution, whose raw output (no bias, no relu) and parameters
-    are returned for ``raftk_motion_scatter``."""
-    me = "update_block/motion_encoder"
-    corr = _cna(P, f"{me}/convcorr1", corr_features, None)
-    if len(cfg.motion_encoder_corr_layers) == 2:
-        corr = _cna(P, f"{me}/convcorr2", corr, None)
-    fl = _cna(P, f"{me}/convflow1", flow, None)
-    fl = _cna(P, f"{me}/convflow2", fl, None)
-    p = P[f"{me}/conv/layers_0"]
-    pad = ((p.w.shape[2] - 1) // 2, (p.w.shape[3] - 1) // 2)
-    return _cl(F.conv2d(torch.cat([corr, fl], dim=1), p.w, None, padding=pad)), p
-
-
 def _cl(y):
     return y if y.is_contiguous(memory_format=torch.channels_last) else y.contiguous(memory_format=torch.channels_last)
 
@@ -472,11 +458,18 @@ def _conv_gru(P, path, h, x, padding):
 class RAFT:
     """Counterpart of the reference's ``RAFT`` module (model.py:513-605) + ``UpdateCell`` (484-510)."""
 
-    def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32", fused_update: bool = True):
+    def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32", fused_update: bool = True,
+                 concurrent: bool = True):
         assert precision in ("tf32", "fp32")
         # fused_update: UpdateCell's element-wise work through csrc/gru_glue.cu (same arithmetic as the
         # unfused path, which stays for configurations whose channel counts are odd and for A/B tests)
         self.fused_update = fused_update and _RecurrentState.supported(config)
+        # concurrent: independent branches (context || feature encoder, flow || correlation branch of the
+        # motion encoder, mask predictor + upsampler || flow head and the next iteration) are issued on
+        # side streams; captured into the CUDA graph they become parallel branches.  At batch 1 no single
+        # convolution fills 148 SMs, so the branches overlap almost for free.
+        self.concurrent = concurrent and self.fused_update
+        self._streams: Dict[str, Any] = {}
         self.config = config
         self.corr_block = corr_block or CorrBlock(config.corr_block_num_levels, config.corr_block_radius)
         expected = config.corr_block_num_levels * (2 * config.corr_block_radius + 1) ** 2
@@ -510,6 +503,21 @@ class RAFT:
         torch.backends.cudnn.allow_tf32 = self.precision == "tf32"
         torch.backends.cudnn.benchmark = True  # the library times its engines once per convolution shape
         try:
+            main = torch.cuda.current_stream(image1.device)
+            sa, sb = self._side_streams(image1.device) if self.concurrent else (None, None)
+            hid = cfg.recurrent_block_hidden_state_size
+
+            def context_branch():
+                context_out = _encoder(P, "context_encoder", image1.permute(0, 3, 1, 2), cfg.context_encoder_layers,
+                                       cfg.context_encoder_block, cfg.context_encoder_norm, cfg.encoder_strides)
+                assert context_out.shape[1] - hid > 0
+                return torch.tanh(context_out[:, :hid]), F.relu(context_out[:, hid:])
+
+            if sa is not None:
+                sa.wait_stream(main)
+                with torch.cuda.stream(sa):
+                    hidden_state, context = context_branch()
+
             x = torch.cat([image1, image2], dim=0).permute(0, 3, 1, 2)  # NHWC memory, NCHW view
             fmaps = _encoder(P, "feature_encoder", x, cfg.feature_encoder_layers, cfg.feature_encoder_block,
                              cfg.feature_encoder_norm, cfg.encoder_strides)
@@ -519,12 +527,10 @@ class RAFT:
 
             corr_pyramid = self.corr_block.build_pyramid(fmap1, fmap2)  # model.py:567
 
-            context_out = _encoder(P, "context_encoder", image1.permute(0, 3, 1, 2), cfg.context_encoder_layers,
-                                   cfg.context_encoder_block, cfg.context_encoder_norm, cfg.encoder_strides)
-            hid = cfg.recurrent_block_hidden_state_size
-            assert context_out.shape[1] - hid > 0
-            hidden_state = torch.tanh(context_out[:, :hid])
-            context = F.relu(context_out[:, hid:])
+            if sa is not None:
+                main.wait_stream(sa)
+            else:
+                hidden_state, context = context_branch()
 
             coords0 = make_coords_grid(batch_size, h // 8, w // 8, device=image1.device)
             coords1 = coords0.clone()
@@ -534,41 +540,36 @@ class RAFT:
             if state is not None and cfg.use_mask_predictor:  # the upsampler writes the stacked result directly
                 out = torch.empty((num_flow_updates, batch_size, h, w, 2), dtype=torch.float32, device=image1.device)
             for i in range(num_flow_updates):  # nn.scan(UpdateCell), model.py:589-603
-                coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context, state,
-                                                              out=None if out is None else out[i])
+                if state is not None:
+                    up = self._update_cell_fused(P, corr_pyramid, coords0, coords1, state, None if out is None else out[i],
+                                                 main, sa, sb, first=i == 0)
+                else:
+                    coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context)
                 flows.append(up)
+            if sa is not None:  # the last mask predictor + upsampler
+                main.wait_stream(sa)
             return out if out is not None else torch.stack(flows, dim=0)
         finally:
             torch.backends.cudnn.allow_tf32 = prev
             torch.backends.cudnn.benchmark = prev_bench
 
+    def _side_streams(self, device):
+        key = str(device)
+        if key not in self._streams:
+            self._streams[key] = (torch.cuda.Stream(device=device), torch.cuda.Stream(device=device))
+        return self._streams[key]
+
     # -- model.py:494-510 ---------------------------------------------------------------
-    def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context, state=None, out=None):
+    def _update_cell(self, P, corr_pyramid, coords0, coords1, hidden_state, context):
+        """UpdateCell as the reference composes it (concatenations, one op per line)."""
         cfg = self.config
         corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
-        flow_nhwc = state.flow if state is not None else coords1 - coords0
-        flow = flow_nhwc.permute(0, 3, 1, 2)
-        if state is not None:
-            cf_pre, p = _motion_encoder_pre(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
-            state.scatter_motion(cf_pre, p, flow_nhwc)
-            for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
-                state.gru(P, f"update_block/recurrent_block/convgru{gi}", pad)
-            hidden_state = state.h
-        else:
-            motion = _motion_encoder(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
-            x = torch.cat([context, motion], dim=1)
-            for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
-                hidden_state = _conv_gru(P, f"update_block/recurrent_block/convgru{gi}", hidden_state, x, pad)
+        flow = (coords1 - coords0).permute(0, 3, 1, 2)
+        motion = _motion_encoder(P, cfg, flow, corr_features.permute(0, 3, 1, 2))
+        x = torch.cat([context, motion], dim=1)
+        for gi, pad in enumerate(cfg.recurrent_block_padding, start=1):
+            hidden_state = _conv_gru(P, f"update_block/recurrent_block/convgru{gi}", hidden_state, x, pad)
         d = _conv(hidden_state, P["update_block/flow_head/conv1"], padding=1, act="relu")
-        if state is not None:
-            p = P["update_block/flow_head/conv2"]
-            state.update_flow(_cl(F.conv2d(d, p.w, None, padding=1)), p, coords0, coords1)
-            if cfg.use_mask_predictor:  # model.py:377-400; the upsampler adds the last bias itself
-                m = _cna(P, "mask_predictor/convrelu", hidden_state, None)
-                pm = P["mask_predictor/conv"]
-                up_mask = _cl(F.conv2d(m, pm.w, None)).permute(0, 2, 3, 1)
-                return coords1, hidden_state, upsample_flow(state.flow, up_mask, mask_bias=pm.b, out=out)
-            return coords1, hidden_state, upsample_flow(flow=state.flow)
         delta_flow = _conv(d, P["update_block/flow_head/conv2"], padding=1)
         coords1 = coords1 + delta_flow.permute(0, 2, 3, 1)
         up_mask = None
@@ -577,6 +578,59 @@ class RAFT:
             up_mask = _conv(m, P["mask_predictor/conv"]).permute(0, 2, 3, 1).contiguous()
         upsampled = upsample_flow(flow=(coords1 - coords0).contiguous(), up_mask=up_mask)
         return coords1, hidden_state, upsampled
+
+    def _update_cell_fused(self, P, corr_pyramid, coords0, coords1, state, out, main, sa, sb, first):
+        """The same cell on the channel-slice buffers (``_RecurrentState``); coords1 and state are
+        updated in place.  With side streams ``sa`` / ``sb``: the flow branch of the motion encoder runs
+        beside the correlation branch, and the mask predictor + upsampler run beside the flow head and
+        the next iteration's motion encoder (joined before the GRU overwrites the hidden state)."""
+        cfg = self.config
+        me = "update_block/motion_encoder"
+        flow = state.flow.permute(0, 3, 1, 2)
+
+        def flow_branch():
+            return _cna(P, f"{me}/convflow2", _cna(P, f"{me}/convflow1", flow, None), None)
+
+        corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
+        if sb is not None:  # forked after the lookup, which is HBM-bound and wants the machine to itself
+            sb.wait_stream(main)
+            with torch.cuda.stream(sb):
+                fl = flow_branch()
+        corr = _cna(P, f"{me}/convcorr1", corr_features.permute(0, 3, 1, 2), None)
+        if len(cfg.motion_encoder_corr_layers) == 2:
+            corr = _cna(P, f"{me}/convcorr2", corr, None)
+        if sb is not None:
+            main.wait_stream(sb)
+        else:
+            fl = flow_branch()
+        p = P[f"{me}/conv/layers_0"]
+        pad = ((p.w.shape[2] - 1) // 2, (p.w.shape[3] - 1) // 2)
+        cf_pre = _cl(F.conv2d(torch.cat([corr, fl], dim=1), p.w, None, padding=pad))
+        state.scatter_motion(cf_pre, p, state.flow)
+        if sa is not None and not first:
+            main.wait_stream(sa)  # the previous iteration's mask predictor / upsampler still read state.h, state.flow
+        for gi, gpad in enumerate(cfg.recurrent_block_padding, start=1):
+            state.gru(P, f"update_block/recurrent_block/convgru{gi}", gpad)
+
+        def mask_branch():  # model.py:377-400; the upsampler adds the last bias itself
+            m = _cna(P, "mask_predictor/convrelu", state.h, None)
+            return _cl(F.conv2d(m, P["mask_predictor/conv"].w, None)).permute(0, 2, 3, 1)
+
+        up_mask = None
+        if cfg.use_mask_predictor and sa is not None:
+            sa.wait_stream(main)
+            with torch.cuda.stream(sa):
+                up_mask = mask_branch()
+        d = _conv(state.h, P["update_block/flow_head/conv1"], padding=1, act="relu")
+        p = P["update_block/flow_head/conv2"]
+        state.update_flow(_cl(F.conv2d(d, p.w, None, padding=1)), p, coords0, coords1)
+        if not cfg.use_mask_predictor:
+            return upsample_flow(flow=state.flow)
+        if sa is None:
+            return upsample_flow(state.flow, mask_branch(), mask_bias=P["mask_predictor/conv"].b, out=out)
+        sa.wait_stream(main)
+        with torch.cuda.stream(sa):
+            return upsample_flow(state.flow, up_mask, mask_bias=P["mask_predictor/conv"].b, out=out)
 
     # -- public entry, mirrors flax Module.apply -------------------------------------------
     def apply(self, variables: Tree, image1, image2, train: bool = False, num_flow_updates: int = 12,
@@ -665,6 +719,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
     corr_block = kwargs.pop("corr_block", None)
     precision = kwargs.pop("precision", "tf32")
     fused_update = kwargs.pop("fused_update", True)
+    concurrent = kwargs.pop("concurrent", True)
     if kwargs:
         raise TypeError(
             f"unsupported keyword(s) {sorted(kwargs)}: this build replaces the correlation block "
@@ -673,14 +728,14 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
         # a local copy of the reference's released .msgpack (model.py:17-21) or of a converted one
         from .checkpoint import load_msgpack
 
-        model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update)
+        model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent)
         return model, load_msgpack(pretrained)
     if pretrained:
         # model.py:684-689 downloads a msgpack from GitHub; this environment has no network.
         raise RuntimeError(
             "pretrained=True needs network access (model.py:17-21, 684-689); pass pretrained='<file>.msgpack' "
             "(a local copy of the released checkpoint) or use variables_from_torch_state_dict(torch.load(path))")
-    model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update)
+    model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent)
     return model, model.init(seed)
 
 
