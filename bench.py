@@ -260,6 +260,42 @@ def time_hot_path_kernels(torch, J, model, variables, runner, flush, dev, passes
         return lk, bd, f"CUDA events around each launch in eager forwards behind a GPU backlog ({type(exc).__name__})"
 
 
+def lookup_back_to_back(torch, J, dev, hbm_gbs, batch):
+    """The lookup alone with no host or event between launches: one CUDA graph of 8 launches over 8
+    different coordinate sets (8 x 29 MB of footprints per pair, so a launch does not find its rows in
+    L2), replayed 4 times between two events; best of 5.  Kernel-to-kernel throughput, not latency."""
+    h, w, r, L = H // 8, W // 8, 4, 4
+    g = torch.Generator(device=dev).manual_seed(0)
+    q = batch * h * w
+    pyr = [torch.randn((q, h >> l, w >> l, 1), device=dev, generator=g) for l in range(L)]
+    coords = [J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
+              for _ in range(8)]
+    cb = J.CorrBlock(L, r)
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        for c in coords:
+            cb.index_pyramid(pyr, c)
+        torch.cuda.synchronize(dev)
+        with torch.cuda.graph(graph, stream=side):
+            for c in coords:
+                cb.index_pyramid(pyr, c)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = float("inf")
+    for _ in range(5):
+        e0.record()
+        for _ in range(4):
+            graph.replay()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        best = min(best, e0.elapsed_time(e1) / 32)
+    nbytes = q * (L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4)
+    gbs = nbytes / (best * 1e-3) / 1e9
+    return {"batch": batch, "ms_per_launch": best, "algorithmic_bytes": nbytes, "hbm_gbs": gbs, "frac_of_hbm_peak": gbs / hbm_gbs}
+
+
 def kernel_microbench(torch, J, dev, flush, hbm_gbs, batch, iters=10):
     """The three kernel families alone, at the Sintel 1/8 shape and `batch` pairs: CUDA events around
     each launch, L2 flushed before every launch.  Gives the roofline fractions at a size that
@@ -311,6 +347,11 @@ def kernel_microbench(torch, J, dev, flush, hbm_gbs, batch, iters=10):
                                                   "tflops_issued_bf16": 3 * flops / (pyr_ms * 1e-3) / 1e12}),
         "corr_lookup": entry(lk_ms, lk_bytes),
         "convex_upsample": entry(up_ms, up_bytes),
+        "corr_lookup_back_to_back": {
+            "how": "graph of 8 launches over 8 coordinate sets, no events or host between launches (throughput, not latency)",
+            "batch_1": lookup_back_to_back(torch, J, dev, hbm_gbs, 1),
+            f"batch_{batch}": lookup_back_to_back(torch, J, dev, hbm_gbs, batch),
+        },
     }
 
 
