@@ -84,18 +84,43 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons for one GPU while the timed region runs."""
+    """Samples SM clocks / throttle reasons of one GPU while the timed region runs: NVML in a thread
+    every 5 ms (the timed region of the default run is ~100 ms, too short for `nvidia-smi -lms`), with
+    the profiling recipe's nvidia-smi line as the fallback when NVML is not importable."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, uuid=None):
         self.index = index
+        self.uuid = uuid
         self.proc = None
         self.lines = []
+        self.nvml = None
+        self.samples = []
+        self._stop = threading.Event()
+
+    def _nvml_handle(self):
+        import pynvml
+
+        pynvml.nvmlInit()
+        if self.uuid is not None:
+            try:
+                return pynvml, pynvml.nvmlDeviceGetHandleByUUID(f"GPU-{self.uuid}")
+            except pynvml.NVMLError:
+                pass
+        return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index)
 
     def start(self):
+        try:
+            self.nvml, self.handle = self._nvml_handle()
+            self.smax = self.nvml.nvmlDeviceGetMaxClockInfo(self.handle, self.nvml.NVML_CLOCK_SM)
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return self
+        except Exception:  # noqa: BLE001 - any NVML problem: fall back to nvidia-smi
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
@@ -106,11 +131,31 @@ class ClockSampler:
             self.proc = None
         return self
 
+    def _poll(self):
+        n = self.nvml
+        while not self._stop.is_set():
+            try:
+                self.samples.append((n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM),
+                                     n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)))
+            except Exception:  # noqa: BLE001
+                break
+            self._stop.wait(0.005)
+
     def _pump(self):
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self._stop.set()
+            self.thread.join(timeout=2)
+            n = self.nvml
+            names = {"hw_slowdown": n.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": n.nvmlClocksEventReasonHwThermalSlowdown,
+                     "sw_thermal_slowdown": n.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": n.nvmlClocksEventReasonSwPowerCap}
+            reasons = sorted(k for k, bit in names.items() if any(r & bit for _, r in self.samples))
+            sm = [c for c, _ in self.samples]
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.smax, "samples": len(sm),
+                    "reasons": reasons, "source": "nvml, 5 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -133,7 +178,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons), "source": "nvidia-smi -lms 100"}
 
 
 # ---------------------------------------------------------------------------------------
@@ -421,7 +466,7 @@ def run_b200(args):
         runner.graph.replay()
         out_pin.copy_(runner.flows[-1], non_blocking=True)
 
-    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    sampler = ClockSampler(local_rank, str(getattr(torch.cuda.get_device_properties(dev), 'uuid', '')) or None).start() if rank == 0 else None
     total_ms = timed(step_resident, args.steps, args.warmup)
     clocks = sampler.stop() if sampler else None
     e2e_ms = timed(step_e2e, args.steps, max(1, args.warmup // 2))
