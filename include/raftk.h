@@ -176,15 +176,19 @@ int raftk_gru_gate(const float* zr_pre, const float* bias_zr, const float* h, in
                    float* rh_out, int ld_rh, long long npix, int hidden, void* stream);
 int raftk_gru_update(const float* q_pre, const float* bq, const float* z, float* h, int ldh, float* h_dense,
                      long long npix, int hidden, void* stream);
-/* MotionEncoder tail (model.py:286-290): relu(cf_pre + bias) (npix, c_cf) followed by the 2 flow
- * channels, written at dst_a and dst_b (pixel stride ld floats) — the motion slots of the two GRU
- * convolution input buffers.  c_cf and ld even, pointers 8-byte aligned. */
-/* UpdateCell tail (model.py:504-506) on (npix, 2) NHWC arrays: coords1 += delta_pre + bias (in place),
- * flow = coords1 - coords0.  bias: device, the flow head's two bias values, 8-byte aligned. */
-int raftk_flow_update(const float* delta_pre, const float* bias, const float* coords0, float* coords1,
-                      float* flow, long long npix, void* stream);
-int raftk_motion_scatter(const float* cf_pre, const float* bias, const float* flow, float* dst_a, float* dst_b,
-                         int ld, long long npix, int c_cf, void* stream);
+/* MotionEncoder tail (model.py:286-290): relu(cf_pre + bias) followed by the 2 flow channels, written
+ * at dst_a and dst_b (pixel stride ld floats) — the motion slots of the two GRU convolution input
+ * buffers.  cf_pre is (npix, c_cf) with pixel stride ld_src >= c_cf (the convolution may have been
+ * given zero filters up to a channel count the library does not have to pad).  c_cf, ld, ld_src even;
+ * pointers 8-byte aligned. */
+int raftk_motion_scatter(const float* cf_pre, int ld_src, const float* bias, const float* flow, float* dst_a,
+                         float* dst_b, int ld, long long npix, int c_cf, void* stream);
+/* UpdateCell tail (model.py:504-506): coords1 += delta_pre + bias (in place), flow = coords1 - coords0,
+ * on (npix, 2) arrays.  delta_pre has pixel stride ld_delta (>= 2, even: padded flow-head output);
+ * bias: device, the flow head's two bias values; flow_pitched (may be NULL): a second copy of the flow
+ * with pixel stride ld_flow (the zero-padded input of the next iteration's 7x7 flow convolution). */
+int raftk_flow_update(const float* delta_pre, int ld_delta, const float* bias, const float* coords0, float* coords1,
+                      float* flow, float* flow_pitched, int ld_flow, long long npix, void* stream);
 
 #ifdef __cplusplus
 }

@@ -52,9 +52,9 @@ SIGNATURES = {
     "raftk_instance_norm_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_size_t, c_void_p]),
     "raftk_gru_gate": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_int, c_void_p]),
     "raftk_gru_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, ctypes.c_longlong, c_int, c_void_p]),
-    "raftk_flow_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_void_p]),
+    "raftk_flow_update": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_void_p]),
     "raftk_convex_upsample_bias": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
-    "raftk_motion_scatter": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_int, c_void_p]),
+    "raftk_motion_scatter": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_int, c_void_p]),
     "raftk_convex_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
 }
 

@@ -72,7 +72,7 @@ gru_update_kernel(const float* __restrict__ q_pre, const float* __restrict__ bq,
 // c_cf conv channels (bias + relu) followed by the 2 flow channels, into two strided destinations.
 __global__ void __launch_bounds__(256)
 motion_scatter_kernel(const float* __restrict__ cf_pre, const float* __restrict__ bias, const float* __restrict__ flow,
-                      float* __restrict__ dst_a, float* __restrict__ dst_b, int ld, long long npix, int c_cf) {
+                      float* __restrict__ dst_a, float* __restrict__ dst_b, int ld, long long npix, int c_cf, int ld_src) {
   const int per_pix = c_cf / 2 + 1;
   const long long total = npix * per_pix;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
@@ -80,7 +80,7 @@ motion_scatter_kernel(const float* __restrict__ cf_pre, const float* __restrict_
     const int c = (int)(t - pix * per_pix) * 2;
     float2 v;
     if (c < c_cf) {
-      const float2 p = *reinterpret_cast<const float2*>(cf_pre + pix * c_cf + c);
+      const float2 p = *reinterpret_cast<const float2*>(cf_pre + pix * ld_src + c);
       const float2 b = *reinterpret_cast<const float2*>(bias + c);
       v.x = fmaxf(p.x + b.x, 0.0f);
       v.y = fmaxf(p.y + b.y, 0.0f);
@@ -94,16 +94,19 @@ motion_scatter_kernel(const float* __restrict__ cf_pre, const float* __restrict_
 
 // UpdateCell tail (model.py:504-506): coords1 += delta_pre + bias;  flow = coords1 - coords0.
 __global__ void __launch_bounds__(256)
-flow_update_kernel(const float2* __restrict__ delta_pre, const float2* __restrict__ bias_p, const float2* __restrict__ coords0,
-                   float2* __restrict__ coords1, float2* __restrict__ flow, long long npix) {
+flow_update_kernel(const float* __restrict__ delta_pre, int ld_delta, const float2* __restrict__ bias_p,
+                   const float2* __restrict__ coords0, float2* __restrict__ coords1, float2* __restrict__ flow,
+                   float* __restrict__ flow_pitched, int ld_flow, long long npix) {
   const float2 bias = __ldg(bias_p);
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < npix; t += (long long)gridDim.x * blockDim.x) {
-    const float2 d = delta_pre[t], c0 = coords0[t];
+    const float2 d = *reinterpret_cast<const float2*>(delta_pre + t * ld_delta), c0 = coords0[t];
     float2 c1 = coords1[t];
     c1.x = __fadd_rn(c1.x, __fadd_rn(d.x, bias.x));
     c1.y = __fadd_rn(c1.y, __fadd_rn(d.y, bias.y));
     coords1[t] = c1;
-    flow[t] = make_float2(__fadd_rn(c1.x, -c0.x), __fadd_rn(c1.y, -c0.y));
+    const float2 f = make_float2(__fadd_rn(c1.x, -c0.x), __fadd_rn(c1.y, -c0.y));
+    flow[t] = f;
+    if (flow_pitched) *reinterpret_cast<float2*>(flow_pitched + t * ld_flow) = f;
   }
 }
 
@@ -149,27 +152,30 @@ extern "C" int raftk_gru_update(const float* q_pre, const float* bq, const float
   return launch_status();
 }
 
-extern "C" int raftk_motion_scatter(const float* cf_pre, const float* bias, const float* flow, float* dst_a, float* dst_b,
-                                    int ld, long long npix, int c_cf, void* stream) {
+extern "C" int raftk_motion_scatter(const float* cf_pre, int ld_src, const float* bias, const float* flow, float* dst_a,
+                                    float* dst_b, int ld, long long npix, int c_cf, void* stream) {
   using namespace raftk;
-  if (npix < 0 || c_cf <= 0 || c_cf % 2 || ld % 2 || ld < c_cf + 2) return RAFTK_ERR_SHAPE;
+  if (npix < 0 || c_cf <= 0 || c_cf % 2 || ld % 2 || ld < c_cf + 2 || ld_src % 2 || ld_src < c_cf) return RAFTK_ERR_SHAPE;
   if (npix == 0) return RAFTK_OK;
   if (!cf_pre || !bias || !flow || !dst_a || !dst_b) return RAFTK_ERR_NULL;
   if (((uintptr_t)cf_pre | (uintptr_t)bias | (uintptr_t)flow | (uintptr_t)dst_a | (uintptr_t)dst_b) & 7) return RAFTK_ERR_ALIGN;
   motion_scatter_kernel<<<grid_for(npix * (c_cf / 2 + 1)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      cf_pre, bias, flow, dst_a, dst_b, ld, npix, c_cf);
+      cf_pre, bias, flow, dst_a, dst_b, ld, npix, c_cf, ld_src);
   return launch_status();
 }
 
-extern "C" int raftk_flow_update(const float* delta_pre, const float* bias, const float* coords0, float* coords1,
-                                 float* flow, long long npix, void* stream) {
+extern "C" int raftk_flow_update(const float* delta_pre, int ld_delta, const float* bias, const float* coords0,
+                                 float* coords1, float* flow, float* flow_pitched, int ld_flow, long long npix,
+                                 void* stream) {
   using namespace raftk;
-  if (npix < 0) return RAFTK_ERR_SHAPE;
+  if (npix < 0 || ld_delta < 2 || ld_delta % 2 || (flow_pitched && (ld_flow < 2 || ld_flow % 2))) return RAFTK_ERR_SHAPE;
   if (npix == 0) return RAFTK_OK;
   if (!delta_pre || !bias || !coords0 || !coords1 || !flow) return RAFTK_ERR_NULL;
-  if (((uintptr_t)delta_pre | (uintptr_t)bias | (uintptr_t)coords0 | (uintptr_t)coords1 | (uintptr_t)flow) & 7) return RAFTK_ERR_ALIGN;
+  if (((uintptr_t)delta_pre | (uintptr_t)bias | (uintptr_t)coords0 | (uintptr_t)coords1 | (uintptr_t)flow |
+       (uintptr_t)flow_pitched) & 7)
+    return RAFTK_ERR_ALIGN;
   flow_update_kernel<<<grid_for(npix), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const float2*>(delta_pre), reinterpret_cast<const float2*>(bias),
-      reinterpret_cast<const float2*>(coords0), reinterpret_cast<float2*>(coords1), reinterpret_cast<float2*>(flow), npix);
+      delta_pre, ld_delta, reinterpret_cast<const float2*>(bias), reinterpret_cast<const float2*>(coords0),
+      reinterpret_cast<float2*>(coords1), reinterpret_cast<float2*>(flow), flow_pitched, ld_flow, npix);
   return launch_status();
 }

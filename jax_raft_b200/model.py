@@ -267,6 +267,26 @@ def _prepare(cfg: RaftConfig, variables: Tree, device) -> Dict[str, _ConvP]:
             w.to(torch.float32).to(device).contiguous(memory_format=torch.channels_last),
             b.to(torch.float32).to(device),
         )
+    # Channel counts the library would pad with kernels of its own (nhwcAddPaddingKernel x2 + memset per
+    # call: 126 or 2 output channels; a non-tensor-core engine for 2 input channels) are padded here
+    # once, with zero filters, to the next multiple of 8 (profiles/conv_kernels.py: 21 -> 11 us, 16.5 -> 11 us,
+    # 16 -> 9.5 us per call at 55x128)
+    def pad8(n):
+        return (n + 7) // 8 * 8
+
+    def padded(p, cout=None, cin=None):
+        w, b = p.w, p.b
+        if cout is not None and cout > w.shape[0]:
+            w = torch.cat([w, w.new_zeros((cout - w.shape[0],) + tuple(w.shape[1:]))], dim=0)
+            b = torch.cat([b, b.new_zeros(cout - b.shape[0])])
+        if cin is not None and cin > w.shape[1]:
+            w = torch.cat([w, w.new_zeros((w.shape[0], cin - w.shape[1]) + tuple(w.shape[2:]))], dim=1)
+        return _ConvP(w.contiguous(memory_format=torch.channels_last), b.contiguous())
+
+    me = "update_block/motion_encoder"
+    out[f"{me}/conv/layers_0/padded"] = padded(out[f"{me}/conv/layers_0"], cout=pad8(cfg.motion_encoder_out_channels - 2))
+    out["update_block/flow_head/conv2/padded"] = padded(out["update_block/flow_head/conv2"], cout=8)
+    out[f"{me}/convflow1/layers_0/padded"] = padded(out[f"{me}/convflow1/layers_0"], cin=8)
     # ConvGRU: the z and r filters read the same input (model.py:306-307); stacked, they are one convolution
     for gi in range(1, len(cfg.recurrent_block_kernel_size) + 1):
         base = f"update_block/recurrent_block/convgru{gi}"
@@ -398,6 +418,8 @@ class _RecurrentState:
         self.z = torch.empty((n, hid, h, w), **opts)
         self.h = torch.empty((n, hid, h, w), **opts)  # dense copy of the hidden state for the heads
         self.flow = torch.zeros((n, h, w, 2), dtype=torch.float32, device=hidden.device)  # coords1 - coords0
+        # the same flow in channels 0-1 of an 8-channel tensor: input of the zero-padded 7x7 flow convolution
+        self.flow8 = torch.empty((n, 8, h, w), **opts).zero_()
         self.A[:, :hid] = hidden
         self.h.copy_(hidden)
         self.A[:, hid:hid + ctx] = context
@@ -413,8 +435,8 @@ class _RecurrentState:
         lib = _lib.load()
         off = 4 * (self.hid + self.ctx)
         with torch.cuda.device(cf_pre.device):
-            rc = lib.raftk_motion_scatter(cf_pre.data_ptr(), p.b.data_ptr(), flow_nhwc.data_ptr(), self.A.data_ptr() + off,
-                                          self.B.data_ptr() + off, self.ld, self.npix, self.c_cf,
+            rc = lib.raftk_motion_scatter(cf_pre.data_ptr(), cf_pre.shape[1], p.b.data_ptr(), flow_nhwc.data_ptr(),
+                                          self.A.data_ptr() + off, self.B.data_ptr() + off, self.ld, self.npix, self.c_cf,
                                           _lib.current_stream_ptr(cf_pre.device))
         _lib.check("raftk_motion_scatter", rc)
         _lib.count_launch(1)
@@ -423,8 +445,9 @@ class _RecurrentState:
         """model.py:504-506: coords1 += conv + bias (in place); self.flow = coords1 - coords0."""
         lib = _lib.load()
         with torch.cuda.device(coords1.device):
-            rc = lib.raftk_flow_update(delta_pre.data_ptr(), p.b.data_ptr(), coords0.data_ptr(), coords1.data_ptr(),
-                                       self.flow.data_ptr(), self.npix, _lib.current_stream_ptr(coords1.device))
+            rc = lib.raftk_flow_update(delta_pre.data_ptr(), delta_pre.shape[1], p.b.data_ptr(), coords0.data_ptr(),
+                                       coords1.data_ptr(), self.flow.data_ptr(), self.flow8.data_ptr(), 8, self.npix,
+                                       _lib.current_stream_ptr(coords1.device))
         _lib.check("raftk_flow_update", rc)
         _lib.count_launch(1)
 
@@ -586,10 +609,11 @@ class RAFT:
         the next iteration's motion encoder (joined before the GRU overwrites the hidden state)."""
         cfg = self.config
         me = "update_block/motion_encoder"
-        flow = state.flow.permute(0, 3, 1, 2)
 
         def flow_branch():
-            return _cna(P, f"{me}/convflow2", _cna(P, f"{me}/convflow1", flow, None), None)
+            pf = P[f"{me}/convflow1/layers_0/padded"]
+            pad = ((pf.w.shape[2] - 1) // 2, (pf.w.shape[3] - 1) // 2)
+            return _cna(P, f"{me}/convflow2", _conv(state.flow8, pf, padding=pad, act="relu"), None)
 
         corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
         if sb is not None:  # forked after the lookup, which is HBM-bound and wants the machine to itself
@@ -603,7 +627,7 @@ class RAFT:
             main.wait_stream(sb)
         else:
             fl = flow_branch()
-        p = P[f"{me}/conv/layers_0"]
+        p = P[f"{me}/conv/layers_0/padded"]
         pad = ((p.w.shape[2] - 1) // 2, (p.w.shape[3] - 1) // 2)
         cf_pre = _cl(F.conv2d(torch.cat([corr, fl], dim=1), p.w, None, padding=pad))
         state.scatter_motion(cf_pre, p, state.flow)
@@ -622,7 +646,7 @@ class RAFT:
             with torch.cuda.stream(sa):
                 up_mask = mask_branch()
         d = _conv(state.h, P["update_block/flow_head/conv1"], padding=1, act="relu")
-        p = P["update_block/flow_head/conv2"]
+        p = P["update_block/flow_head/conv2/padded"]
         state.update_flow(_cl(F.conv2d(d, p.w, None, padding=1)), p, coords0, coords1)
         if not cfg.use_mask_predictor:
             return upsample_flow(flow=state.flow)

@@ -86,18 +86,19 @@ def test_gru_gate_and_update(cuda, lib, hid, extra):
     assert torch.equal(A[:, :hid], hd) and torch.equal(A[:, hid:], A0[:, hid:])
 
 
-@pytest.mark.parametrize("c_cf,off,ld", [(126, 256, 384), (80, 160, 242)])
-def test_motion_scatter(cuda, lib, c_cf, off, ld):
+@pytest.mark.parametrize("c_cf,ld_src,off,ld", [(126, 126, 256, 384), (126, 128, 256, 384), (80, 80, 160, 242)])
+def test_motion_scatter(cuda, lib, c_cf, ld_src, off, ld):
     """MotionEncoder tail (model.py:286-290): relu(conv + bias) ++ flow into both GRU input buffers."""
     gen = torch.Generator(device=cuda).manual_seed(c_cf)
     npix = 3 * 5 * 11
-    cf_pre = torch.randn((npix, c_cf), device=cuda, generator=gen)
-    bias = torch.randn((c_cf,), device=cuda, generator=gen)
+    cf_full = torch.randn((npix, ld_src), device=cuda, generator=gen)  # channels >= c_cf: zero-filter padding
+    cf_pre = cf_full[:, :c_cf]
+    bias = torch.randn((ld_src,), device=cuda, generator=gen)[:c_cf]
     flow = torch.randn((npix, 2), device=cuda, generator=gen)
     A = torch.full((npix, ld), 7.0, device=cuda)
     B = torch.full((npix, ld), 9.0, device=cuda)
     with torch.cuda.device(cuda):
-        rc = lib.raftk_motion_scatter(cf_pre.data_ptr(), bias.data_ptr(), flow.data_ptr(), A.data_ptr() + 4 * off,
+        rc = lib.raftk_motion_scatter(cf_full.data_ptr(), ld_src, bias.data_ptr(), flow.data_ptr(), A.data_ptr() + 4 * off,
                                       B.data_ptr() + 4 * off, ld, npix, c_cf, _stream(cuda))
     _lib.check("raftk_motion_scatter", rc)
     ref = torch.cat([F.relu(cf_pre + bias), flow], dim=1)
@@ -112,24 +113,32 @@ def test_gru_glue_rejects_bad_shapes(cuda, lib):
     assert lib.raftk_gru_gate(p, p, p, 7, p, p, 8, 1, 4, None) == -2      # odd stride
     assert lib.raftk_gru_gate(p, p, p, 2, p, p, 8, 1, 4, None) == -2      # stride < hidden
     assert lib.raftk_gru_update(p, p, p, p + 4, 8, p, 1, 4, None) == -6   # 4-byte aligned pointer
-    assert lib.raftk_motion_scatter(p, p, p, p, p, 8, 1, 8, None) == -2   # ld < c_cf + 2
+    assert lib.raftk_motion_scatter(p, 8, p, p, p, p, 8, 1, 8, None) == -2   # ld < c_cf + 2
+    assert lib.raftk_motion_scatter(p, 6, p, p, p, p, 16, 1, 8, None) == -2  # source pitch < c_cf
+    assert lib.raftk_flow_update(p, 3, p, p, p, p, None, 0, 1, None) == -2   # odd delta pitch
     assert lib.raftk_gru_gate(None, p, p, 8, p, p, 8, 1, 4, None) == -1
     assert lib.raftk_gru_gate(None, None, None, 8, None, None, 8, 0, 4, None) == 0  # empty batch
 
 
-def test_flow_update(cuda, lib):
-    """UpdateCell tail (model.py:504-506), bit-exact against the same float32 sequence in torch."""
+@pytest.mark.parametrize("ld_delta,ld_flow", [(2, 0), (8, 8)])
+def test_flow_update(cuda, lib, ld_delta, ld_flow):
+    """UpdateCell tail (model.py:504-506), bit-exact against the same float32 sequence in torch; with a
+    padded flow-head output and the second, pitched copy of the flow."""
     gen = torch.Generator(device=cuda).manual_seed(5)
     npix = 2 * 13 * 17
-    delta = torch.randn((npix, 2), device=cuda, generator=gen)
-    bias = torch.randn((2,), device=cuda, generator=gen)
+    delta_full = torch.randn((npix, ld_delta), device=cuda, generator=gen)
+    delta = delta_full[:, :2]
+    bias = torch.randn((8,), device=cuda, generator=gen)[:2]
     c0 = torch.rand((npix, 2), device=cuda, generator=gen) * 100
     c1 = c0 + torch.randn((npix, 2), device=cuda, generator=gen) * 5
     ref_c1 = c1 + (delta + bias)
     ref_flow = ref_c1 - c0
     flow = torch.empty_like(c1)
+    pitched = torch.full((npix, max(ld_flow, 1)), 3.0, device=cuda)
     with torch.cuda.device(cuda):
-        rc = lib.raftk_flow_update(delta.data_ptr(), bias.data_ptr(), c0.data_ptr(), c1.data_ptr(), flow.data_ptr(), npix,
-                                   _stream(cuda))
+        rc = lib.raftk_flow_update(delta_full.data_ptr(), ld_delta, bias.data_ptr(), c0.data_ptr(), c1.data_ptr(), flow.data_ptr(),
+                                   pitched.data_ptr() if ld_flow else None, ld_flow, npix, _stream(cuda))
     _lib.check("raftk_flow_update", rc)
     assert torch.equal(c1, ref_c1) and torch.equal(flow, ref_flow)
+    if ld_flow:
+        assert torch.equal(pitched[:, :2], ref_flow) and (pitched[:, 2:] == 3.0).all()
