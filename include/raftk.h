@@ -152,6 +152,26 @@ int raftk_convex_upsample(const float* flow, const float* mask, float* out, int 
 int raftk_convex_upsample_bias(const float* flow, const float* mask, const float* mask_bias, float* out, int B,
                                int h, int w, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Next row f1: raftk_corr_lookup fused with the 1x1 convolution that consumes it
+ * (MotionEncoder.convcorr1 + ReLU, model.py:275-276), so the L*(2r+1)^2 correlation features stay
+ * on the SM:   out[q, n] = act( sum_c weight[n, c] * lookup(q)[c] + bias[n] ),  act = ReLU if relu.
+ * The product is TF32 (tcgen05.mma.kind::tf32: 10-bit-mantissa operands, float32 accumulation),
+ * as the library convolution it replaces in the default precision mode.
+ *
+ *   levels, coords     as raftk_corr_lookup; num_levels == 4 and radius in {3, 4} only
+ *                      (else RAFTK_ERR_UNSUPPORTED: use raftk_corr_lookup + a convolution)
+ *   weight  device, (N, K') float32 row-major, 16-byte aligned, K' = raftk_lookup_conv_weight_cols():
+ *           each level's (2r+1)^2 filter columns followed by zeros up to a multiple of 32, i.e.
+ *           weight[n, l*KL + t] = W[n, l*(2r+1)^2 + t], KL = K'/4 (96 for r = 4, 64 for r = 3)
+ *   bias    device, (N), 16-byte aligned;  N a multiple of 16, 16 <= N <= 256
+ *   out     device, (Q, N)
+ * ---------------------------------------------------------------------------------- */
+int raftk_lookup_conv_weight_cols(int num_levels, int radius);
+int raftk_corr_lookup_conv1x1(const float* const* levels, int num_levels, const float* coords, const float* weight,
+                              const float* bias, float* out, int Q, int h, int w, int radius, int N, int relu,
+                              void* stream);
+
 /* Host-model glue, not a hot-path row: in place y = act(x + bias[c]) on an NHWC conv output
  * (npix, c); act 0 none, 1 relu, 2 sigmoid, 3 tanh.  Used by jax_raft_b200/model.py after the
  * library convolutions (ConvNormActivation / ConvGRU / FlowHead epilogues, model.py:120-159,

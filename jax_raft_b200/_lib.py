@@ -55,6 +55,8 @@ SIGNATURES = {
     "raftk_flow_update": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_void_p]),
     "raftk_convex_upsample_bias": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "raftk_motion_scatter": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_int, c_void_p]),
+    "raftk_lookup_conv_weight_cols": (c_int, [c_int, c_int]),
+    "raftk_corr_lookup_conv1x1": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_convex_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
 }
 

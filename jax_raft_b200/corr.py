@@ -124,6 +124,53 @@ class CorrBlock:
         return out
 
 
+    # -- lookup fused with the 1x1 convolution that consumes it ----------------
+    @property
+    def fused_conv_supported(self) -> bool:
+        return self.num_levels == 4 and self.radius in (3, 4)
+
+    def pack_conv_weight(self, weight: torch.Tensor) -> torch.Tensor:
+        """(N, L*(2r+1)^2[, 1, 1]) filters of the convolution that follows the lookup (convcorr1,
+        model.py:275) -> the (N, K') layout ``raftk_corr_lookup_conv1x1`` reads: each level's columns
+        padded with zeros to a multiple of 32."""
+        assert self.fused_conv_supported
+        n = weight.shape[0]
+        ss = (2 * self.radius + 1) ** 2
+        w = weight.reshape(n, self.num_levels, ss).to(torch.float32)
+        kl = _lib.load().raftk_lookup_conv_weight_cols(self.num_levels, self.radius) // self.num_levels
+        packed = w.new_zeros((n, self.num_levels, kl))
+        packed[:, :, :ss] = w
+        return packed.reshape(n, self.num_levels * kl).contiguous()
+
+    def index_pyramid_conv(self, corr_pyramid: Sequence[torch.Tensor], centroids_coords: torch.Tensor,
+                           packed_weight: torch.Tensor, bias: torch.Tensor, relu: bool = True) -> torch.Tensor:
+        """``act(conv1x1(index_pyramid(corr_pyramid, coords)) + bias)`` in one kernel, (B, h, w, N); TF32
+        products.  N a multiple of 16, at most 256."""
+        assert self.fused_conv_supported
+        assert centroids_coords.shape[-1] == 2
+        coords = _check_cuda_f32("centroids_coords", centroids_coords)
+        b, hq, wq, _ = coords.shape
+        q = b * hq * wq
+        assert len(corr_pyramid) == self.num_levels
+        lv0 = corr_pyramid[0]
+        assert lv0.shape[0] == q, "pyramid and coords disagree on the number of query pixels"
+        h, w = int(lv0.shape[1]), int(lv0.shape[2])
+        levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(corr_pyramid)]
+        weight = _check_cuda_f32("packed_weight", packed_weight)
+        bias = _check_cuda_f32("bias", bias)
+        n = weight.shape[0]
+        lib = _lib.load()
+        assert weight.shape[1] == lib.raftk_lookup_conv_weight_cols(self.num_levels, self.radius) and bias.shape == (n,)
+        out = torch.empty((b, hq, wq, n), dtype=torch.float32, device=coords.device)
+        with torch.cuda.device(coords.device):
+            rc = lib.raftk_corr_lookup_conv1x1(_lib.ptr_array(levels), self.num_levels, coords.data_ptr(), weight.data_ptr(),
+                                               bias.data_ptr(), out.data_ptr(), q, h, w, self.radius, n, 1 if relu else 0,
+                                               _lib.current_stream_ptr(coords.device))
+        _lib.check("raftk_corr_lookup_conv1x1", rc)
+        _lib.count_launch(1)
+        return out
+
+
 class AltCorrBlock:
     """On-the-fly lookup that never materialises the volume ("alt_corr").
 

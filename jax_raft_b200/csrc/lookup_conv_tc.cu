@@ -1,0 +1,465 @@
+// the window lookup (CorrBlock.index_pyramid, model.py:448-470) fused with
+// MotionEncoder.convcorr1 (1x1 convolution 324 -> 256 + ReLU, model.py:275-276), so the 324-channel
+// correlation features never leave the SM.
+//
+//   out[q, n] = act( sum_c W[n, c] * lookup(q)[c] + bias[n] )
+//
+// One CTA = 64 query pixels (UMMA M = 64, cta_group::1), all N <= 256 output channels:
+//   warps 0-15 lookup: the software-pipelined per-query routine of corr_lookup.cu (same float32 tap
+//              arithmetic, bit-identical values), four queries per warp, but the taps are written into a
+//              K-major, 128-byte-swizzled A tile in shared memory (12 K-blocks of 64 rows x 32 floats for
+//              r = 4; each level's 81 channels are padded to 96 so that a K-block never straddles two levels);
+//   warp 16    TMA producer: the prepared weights W' (N rows x K' floats) stream through a 2-stage ring,
+//              one 32-float K-block (N x 128 B) per stage;
+//   warp 17    one thread issues tcgen05.mma.kind::tf32 (K = 8 per instruction) once the A tile is
+//              complete; the accumulator (64 x N float32) lives in TMEM;
+//   warps 0-3  epilogue: tcgen05.ld, + bias, ReLU, 128-byte row segments to global memory.
+// The multiplication is TF32 (10-bit mantissa operands, float32 accumulation) — what the library
+// convolution it replaces uses in the default precision mode.
+//
+// Status: parity-green, but SLOWER than the two-kernel path at every batch size measured
+// (batch 1: 28 us against 15.4 us for raftk_corr_lookup + the library's 1x1 convolution back to back), so the
+// host model does not use it by default.  The three phases of a CTA run one after the other, each of the
+// 110 CTAs streams all 384 KB of weights from L2 (42 MB per launch), and with one CTA per SM (220 KB of
+// shared memory) nothing overlaps across CTAs.  What it would take: weight multicast across a cluster and a
+// level-major tap order so that the MMAs of level l run under the taps of level l+1.
+
+#include <cuda.h>
+
+#include <cstring>
+
+#include "raftk_common.cuh"
+#include "lookup_taps.cuh"
+
+namespace raftk {
+namespace lc {
+
+constexpr int TM = 64;  // queries per CTA
+constexpr int LOOKUP_WARPS = 16;
+constexpr int NUM_THREADS = (LOOKUP_WARPS + 2) * 32;
+constexpr int STAGES = 2;
+constexpr int PITCH = 20;
+constexpr int A_BLOCK_BYTES = TM * 128;  // one K-block of the A tile: 64 rows x 32 floats
+constexpr int SMEM_LIMIT = 232448;       // 227 KB
+
+struct Params {
+  const float* level[4];
+  int lh[4], lw[4], aligned[4];
+  const float* coords;
+  const float* bias;
+  float* out;
+  int Q, N, relu;
+};
+
+// ---- PTX wrappers (same forms as corr_volume_tc.cu) --------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* tm, uint64_t* bar, void* dst, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+                   "r"(smem_u32(dst)),
+               "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// K-major operand tile, 128-byte swizzle: rows of 128 B (32 floats), 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::tf32 instruction descriptor: D = f32 (bits 4-5 = 1), A = B = tf32 (bits 7-9, 10-12 = 2), both
+// K-major, N >> 3 at bit 17, M >> 4 at bit 24.
+__device__ __forceinline__ uint32_t make_idesc(int m, int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+// One footprint chunk (see corr_lookup.cu): floats [gx, gx+4) of row gy, zeros outside the level.
+__device__ __forceinline__ float4 load_chunk(const float* slab, int lh, int lw, int gy, int gx, bool aligned, uint64_t pol) {
+  float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  if ((unsigned)gy >= (unsigned)lh) return v;
+  const float* row = slab + (size_t)gy * lw;
+  if (aligned) {
+    if ((unsigned)gx < (unsigned)lw) v = ldg_f4_l2hint(reinterpret_cast<const float4*>(row + gx), pol);
+  } else {
+    if ((unsigned)gx < (unsigned)lw) v.x = __ldg(row + gx);
+    if ((unsigned)(gx + 1) < (unsigned)lw) v.y = __ldg(row + gx + 1);
+    if ((unsigned)(gx + 2) < (unsigned)lw) v.z = __ldg(row + gx + 2);
+    if ((unsigned)(gx + 3) < (unsigned)lw) v.w = __ldg(row + gx + 3);
+  }
+  return v;
+}
+
+template <int R>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+lookup_conv_kernel(const __grid_constant__ CUtensorMap tmW, const Params p) {
+  constexpr int S = 2 * R + 1, SS = S * S, FP = 2 * R + 2, ROWS = FP + 1, TILE = ROWS * PITCH;
+  constexpr int NTAP = (SS + 31) / 32;
+  constexpr int KL = NTAP * 32;     // channels per level in the A tile: 96 (r = 4), 64 (r = 3)
+  constexpr int KB = 4 * KL / 32;   // K-blocks: 12 / 8
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const int b_stage_bytes = p.N * 128;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + KB * A_BLOCK_BYTES;
+  float* smem_f = reinterpret_cast<float*>(smem_b + STAGES * b_stage_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_f + LOOKUP_WARPS * 4 * TILE);
+  uint64_t* b_full = bars;             // [STAGES]
+  uint64_t* b_empty = bars + STAGES;   // [STAGES]
+  uint64_t* a_ready = bars + 2 * STAGES;
+  uint64_t* acc_full = a_ready + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * TM;
+  const uint32_t tmem_cols = p.N <= 32 ? 32u : p.N <= 64 ? 64u : p.N <= 128 ? 128u : 256u;
+
+  if (warp == LOOKUP_WARPS && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    mbar_init(a_ready, LOOKUP_WARPS);
+    mbar_init(acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == LOOKUP_WARPS + 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(tmem_cols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < LOOKUP_WARPS) {
+    // ===================== lookup: taps -> A tile =====================
+    float* F = smem_f + warp * (4 * TILE);
+    for (int e = lane; e < 4 * PITCH; e += 32) F[(e / PITCH) * TILE + FP * PITCH + (e % PITCH)] = 0.0f;  // guard rows
+    // padding columns of the A tile (channels SS..KL-1 of every level) are zero: rows warp, warp+8, ...
+    for (int e = lane; e < (TM / LOOKUP_WARPS) * 4 * (KL - SS); e += 32) {
+      const int rr = e / (4 * (KL - SS)), rem = e % (4 * (KL - SS));
+      const int l = rem / (KL - SS), c = l * KL + SS + rem % (KL - SS);
+      const int r = warp + LOOKUP_WARPS * rr;
+      *reinterpret_cast<float*>(smem_a + (c >> 5) * A_BLOCK_BYTES + r * 128 + ((((c & 31) >> 2) ^ (r & 7)) << 4) + (c & 3) * 4) = 0.0f;
+    }
+    __syncwarp();
+
+    float di[NTAP], dj[NTAP];
+#pragma unroll
+    for (int k = 0; k < NTAP; ++k) {
+      const int t = lane + 32 * k < SS ? lane + 32 * k : 0;
+      const int i = t / S, j = t - i * S;
+      di[k] = (float)(i - R);
+      dj[k] = (float)(j - R);
+    }
+    const bool last_tap_valid = lane + 32 * (NTAP - 1) < SS;
+    const int row_u = lane >> 2, chunk = lane & 3;
+    const int lvx = lane >> 3, rowx = 8 + ((lane >> 2) & 1);
+    const float* levelx = lvx == 0 ? p.level[0] : lvx == 1 ? p.level[1] : lvx == 2 ? p.level[2] : p.level[3];
+    const int lhx = lvx == 0 ? p.lh[0] : lvx == 1 ? p.lh[1] : lvx == 2 ? p.lh[2] : p.lh[3];
+    const int lwx = lvx == 0 ? p.lw[0] : lvx == 1 ? p.lw[1] : lvx == 2 ? p.lw[2] : p.lw[3];
+    const bool alignedx = (lvx == 0 ? p.aligned[0] : lvx == 1 ? p.aligned[1] : lvx == 2 ? p.aligned[2] : p.aligned[3]) != 0;
+    const uint64_t pol = l2_policy_evict_last();
+
+    float4 v[5];
+    auto fetch = [&](int q, float cx, float cy) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        v[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        const float sc = __int_as_float((127 - k) << 23);
+        const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
+        const int lh = p.lh[k], lw = p.lw[k];
+        const int gy = by + row_u, gx = (bx & ~3) + 4 * chunk;
+        if (row_u < FP && gx <= bx + FP - 1)
+          v[k] = load_chunk(p.level[k] + (size_t)q * lh * lw, lh, lw, gy, gx, p.aligned[k] != 0, pol);
+      }
+      v[4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      if (FP > 8) {
+        const float sc = __int_as_float((127 - lvx) << 23);
+        const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
+        const int gy = by + rowx, gx = (bx & ~3) + 4 * chunk;
+        if (gx <= bx + FP - 1) v[4] = load_chunk(levelx + (size_t)q * lhx * lwx, lhx, lwx, gy, gx, alignedx, pol);
+      }
+    };
+    auto near = [](float cx, float cy) { return fabsf(cx) <= 1.0e6f && fabsf(cy) <= 1.0e6f; };
+
+    int r = warp;  // row of the A tile = query q0 + r
+    float cx = 0.0f, cy = 0.0f;
+    if (q0 + r < p.Q) {
+      cx = __ldg(p.coords + 2 * (size_t)(q0 + r));
+      cy = __ldg(p.coords + 2 * (size_t)(q0 + r) + 1);
+      if (near(cx, cy)) fetch(q0 + r, cx, cy);
+    }
+    for (; r < TM; r += LOOKUP_WARPS) {
+      const int q = q0 + r, rn = r + LOOKUP_WARPS;
+      const bool valid = q < p.Q;
+      const bool fast = valid && near(cx, cy);
+      if (fast) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (row_u < FP) *reinterpret_cast<float4*>(F + k * TILE + row_u * PITCH + chunk * 4) = v[k];
+        if (FP > 8) *reinterpret_cast<float4*>(F + lvx * TILE + rowx * PITCH + chunk * 4) = v[4];
+        __syncwarp();
+      }
+      float ncx = 0.0f, ncy = 0.0f;
+      if (rn < TM && q0 + rn < p.Q) {
+        ncx = __ldg(p.coords + 2 * (size_t)(q0 + rn));
+        ncy = __ldg(p.coords + 2 * (size_t)(q0 + rn) + 1);
+        if (near(ncx, ncy)) fetch(q0 + rn, ncx, ncy);
+      }
+      uint8_t* arow = smem_a + r * 128;
+      const int sw = r & 7;
+#pragma unroll
+      for (int l = 0; l < 4; ++l) {
+        const float sc = __int_as_float((127 - l) << 23);
+        const float cxl = cx * sc, cyl = cy * sc;
+        const float fbxa = (float)(((int)floorf(cxl) - R) & ~3);
+        const float fby = floorf(cyl) - (float)R;
+        const float* Fl = F + l * TILE;
+#pragma unroll
+        for (int k = 0; k < NTAP; ++k) {
+          float acc;
+          if (fast) {
+            const float sx = __fadd_rn(cxl, di[k]), sy = __fadd_rn(cyl, dj[k]);
+            const float fx0 = floorf(sx), fy0 = floorf(sy);
+            const float wx1 = __fadd_rn(sx, -fx0), wy1 = __fadd_rn(sy, -fy0);
+            const float wx0 = __fadd_rn(1.0f, -wx1), wy0 = __fadd_rn(1.0f, -wy1);
+            const int off = __float2int_rn(fmaf(fy0 - fby, (float)PITCH, fx0 - fbxa));
+            const float* f = Fl + off;
+            acc = __fmul_rn(__fmul_rn(wy0, wx0), f[0]);
+            acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy0, wx1), f[1]));
+            acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx0), f[PITCH]));
+            acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx1), f[PITCH + 1]));
+          } else {
+            // row past the end of the batch: zeros.  Query farther than 1e6 from the map: every corner
+            // of every tap is outside every level -> 0, or NaN when a coordinate is not finite
+            // (0 * weight, as the reference's arithmetic gives)
+            acc = valid ? __fadd_rn(__fadd_rn(cx, -cx), __fadd_rn(cy, -cy)) : 0.0f;
+          }
+          if (k < NTAP - 1 || last_tap_valid) {
+            const int c = l * KL + lane + 32 * k;  // channel in the padded K order
+            *reinterpret_cast<float*>(arow + (c >> 5) * A_BLOCK_BYTES + ((((c & 31) >> 2) ^ sw) << 4) + (c & 3) * 4) = acc;
+          }
+        }
+      }
+      __syncwarp();
+      cx = ncx;
+      cy = ncy;
+    }
+    fence_async_smem();  // generic-proxy writes of the A tile -> visible to the tensor core's async proxy
+    __syncwarp();
+    if (lane == 0) mbar_arrive(a_ready);
+
+    // ===================== epilogue (warps 0-3: TMEM lane quarter = warp) =====================
+    if (warp < 4) {
+      mbar_wait(acc_full, 0);
+      tc_fence_after();
+      // M = 64: accumulator row m lives in TMEM lane (m % 16) + 32 * (m / 16) — lanes 0-15 of each quarter
+      const int m = 16 * warp + lane;
+      const long long q = (long long)q0 + m;
+      const bool store = lane < 16 && q < p.Q;
+      for (int n0 = 0; n0 < p.N; n0 += 32) {
+        float acc[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)n0, acc);
+        tmem_ld_wait();
+        if (store) {
+          float* orow = p.out + q * p.N + n0;
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            if (n0 + c < p.N) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c));
+              float4 o = make_float4(acc[c] + b.x, acc[c + 1] + b.y, acc[c + 2] + b.z, acc[c + 3] + b.w);
+              if (p.relu) {
+                o.x = fmaxf(o.x, 0.0f);
+                o.y = fmaxf(o.y, 0.0f);
+                o.z = fmaxf(o.z, 0.0f);
+                o.w = fmaxf(o.w, 0.0f);
+              }
+              *reinterpret_cast<float4*>(orow + c) = o;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == LOOKUP_WARPS) {
+    // ===================== TMA producer: weight K-blocks =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < KB; ++kb) {
+        mbar_wait(&b_empty[stage], phase ^ 1);
+        mbar_expect_tx(&b_full[stage], (uint32_t)b_stage_bytes);
+        tma_load_2d(&tmW, &b_full[stage], smem_b + stage * b_stage_bytes, kb * 32, 0);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(TM, p.N);
+      mbar_wait(a_ready, 0);
+      tc_fence_after();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < KB; ++kb) {
+        mbar_wait(&b_full[stage], phase);
+        tc_fence_after();
+        const uint32_t as = smem_u32(smem_a + kb * A_BLOCK_BYTES);
+        const uint32_t bs = smem_u32(smem_b + stage * b_stage_bytes);
+#pragma unroll
+        for (int k8 = 0; k8 < 4; ++k8)  // 8 floats = 32 bytes of K per instruction
+          tc_mma_tf32(tmem_base, umma_desc(as + 32 * k8), umma_desc(bs + 32 * k8), idesc, (kb | k8) != 0);
+        tc_commit(&b_empty[stage]);  // the stage is free once these MMAs have read it
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      tc_commit(acc_full);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == LOOKUP_WARPS + 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols));
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+static int padded_level_channels(int radius) {
+  const int ss = (2 * radius + 1) * (2 * radius + 1);
+  return (ss + 31) / 32 * 32;
+}
+
+}  // namespace lc
+}  // namespace raftk
+
+extern "C" int raftk_lookup_conv_weight_cols(int num_levels, int radius) {
+  if (num_levels != 4 || (radius != 3 && radius != 4)) return 0;
+  return 4 * raftk::lc::padded_level_channels(radius);
+}
+
+extern "C" int raftk_corr_lookup_conv1x1(const float* const* levels, int num_levels, const float* coords,
+                                         const float* weight, const float* bias, float* out, int Q, int h, int w,
+                                         int radius, int N, int relu, void* stream) {
+  using namespace raftk;
+  using namespace raftk::lc;
+  if (Q < 0 || h <= 0 || w <= 0 || num_levels < 1 || num_levels > RAFTK_MAX_LEVELS) return RAFTK_ERR_SHAPE;
+  if (num_levels != 4 || (radius != 3 && radius != 4) || N < 16 || N > 256 || N % 16) return RAFTK_ERR_UNSUPPORTED;
+  if ((h >> (num_levels - 1)) < 1 || (w >> (num_levels - 1)) < 1) return RAFTK_ERR_TOO_SMALL;
+  if (Q == 0) return RAFTK_OK;
+  if (!levels || !coords || !weight || !bias || !out) return RAFTK_ERR_NULL;
+  if (((uintptr_t)weight & 15) || ((uintptr_t)bias & 15) || ((uintptr_t)out & 15) || ((uintptr_t)coords & 7)) return RAFTK_ERR_ALIGN;
+  Params p{};
+  for (int l = 0; l < 4; ++l) {
+    if (!levels[l]) return RAFTK_ERR_NULL;
+    p.level[l] = levels[l];
+    p.lh[l] = h >> l;
+    p.lw[l] = w >> l;
+    p.aligned[l] = (p.lw[l] % 4 == 0) && (((uintptr_t)levels[l] & 15) == 0);
+  }
+  p.coords = coords;
+  p.bias = bias;
+  p.out = out;
+  p.Q = Q;
+  p.N = N;
+  p.relu = relu;
+  const int KL = padded_level_channels(radius), K = 4 * KL, KB = K / 32;
+  EncodeTiledFn encode = get_encode_fn();
+  if (!encode) return RAFTK_ERR_UNSUPPORTED;
+  CUtensorMap tmW;
+  {
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)N};
+    const cuuint64_t strides[1] = {(cuuint64_t)K * 4};
+    const cuuint32_t box[2] = {32, (cuuint32_t)N};
+    const cuuint32_t estr[2] = {1, 1};
+    if (encode(&tmW, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(weight), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return RAFTK_ERR_UNSUPPORTED;
+  }
+  const int tile = (2 * radius + 3) * PITCH;
+  const size_t smem = 1024 + (size_t)KB * A_BLOCK_BYTES + (size_t)STAGES * N * 128 + (size_t)LOOKUP_WARPS * 4 * tile * 4 + 128;
+  if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
+  const int blocks = (Q + TM - 1) / TM;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e;
+  if (radius == 4) {
+    e = cudaFuncSetAttribute(lookup_conv_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    lookup_conv_kernel<4><<<blocks, NUM_THREADS, smem, s>>>(tmW, p);
+  } else {
+    e = cudaFuncSetAttribute(lookup_conv_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    lookup_conv_kernel<3><<<blocks, NUM_THREADS, smem, s>>>(tmW, p);
+  }
+  return launch_status();
+}

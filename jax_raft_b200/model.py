@@ -482,7 +482,7 @@ class RAFT:
     """Counterpart of the reference's ``RAFT`` module (model.py:513-605) + ``UpdateCell`` (484-510)."""
 
     def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32", fused_update: bool = True,
-                 concurrent: bool = True):
+                 concurrent: bool = True, fused_lookup_conv: bool = False):
         assert precision in ("tf32", "fp32")
         # fused_update: UpdateCell's element-wise work through csrc/gru_glue.cu (same arithmetic as the
         # unfused path, which stays for configurations whose channel counts are odd and for A/B tests)
@@ -501,6 +501,11 @@ class RAFT:
         # "tf32": cuDNN may use TF32 for the float32 convolutions — what XLA's GPU backend does
         # by default for the reference.  "fp32": full-precision library convolutions.
         self.precision = precision
+        # fused_lookup_conv: the lookup and MotionEncoder.convcorr1 as one kernel (raftk_corr_lookup_conv1x1,
+        # SURVEY §8 f1).  Off by default: measured slower than the two kernels it replaces.
+        self.fused_lookup_conv = (fused_lookup_conv and self.fused_update and precision == "tf32"
+                                  and getattr(self.corr_block, "fused_conv_supported", False)
+                                  and config.motion_encoder_corr_layers[0] % 16 == 0 and config.motion_encoder_corr_layers[0] <= 256)
         self._prepared: Dict[Tuple[int, str], Any] = {}
         self._graphs: Dict[Any, "_GraphRunner"] = {}
 
@@ -615,12 +620,21 @@ class RAFT:
             pad = ((pf.w.shape[2] - 1) // 2, (pf.w.shape[3] - 1) // 2)
             return _cna(P, f"{me}/convflow2", _conv(state.flow8, pf, padding=pad, act="relu"), None)
 
-        corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
+        fuse = self.fused_lookup_conv
+        if fuse:  # lookup + convcorr1 + ReLU in one kernel (TF32 product)
+            pc = P[f"{me}/convcorr1/layers_0"]
+            packed = getattr(pc, "_packed", None)
+            if packed is None:
+                packed = pc._packed = self.corr_block.pack_conv_weight(pc.w)
+            corr = self.corr_block.index_pyramid_conv(corr_pyramid, coords1, packed, pc.b, relu=True).permute(0, 3, 1, 2)
+        else:
+            corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
         if sb is not None:  # forked after the lookup, which is HBM-bound and wants the machine to itself
             sb.wait_stream(main)
             with torch.cuda.stream(sb):
                 fl = flow_branch()
-        corr = _cna(P, f"{me}/convcorr1", corr_features.permute(0, 3, 1, 2), None)
+        if not fuse:
+            corr = _cna(P, f"{me}/convcorr1", corr_features.permute(0, 3, 1, 2), None)
         if len(cfg.motion_encoder_corr_layers) == 2:
             corr = _cna(P, f"{me}/convcorr2", corr, None)
         if sb is not None:
@@ -744,6 +758,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
     precision = kwargs.pop("precision", "tf32")
     fused_update = kwargs.pop("fused_update", True)
     concurrent = kwargs.pop("concurrent", True)
+    fused_lookup_conv = kwargs.pop("fused_lookup_conv", False)
     if kwargs:
         raise TypeError(
             f"unsupported keyword(s) {sorted(kwargs)}: this build replaces the correlation block "
@@ -752,14 +767,16 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
         # a local copy of the reference's released .msgpack (model.py:17-21) or of a converted one
         from .checkpoint import load_msgpack
 
-        model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent)
+        model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent,
+                     fused_lookup_conv=fused_lookup_conv)
         return model, load_msgpack(pretrained)
     if pretrained:
         # model.py:684-689 downloads a msgpack from GitHub; this environment has no network.
         raise RuntimeError(
             "pretrained=True needs network access (model.py:17-21, 684-689); pass pretrained='<file>.msgpack' "
             "(a local copy of the released checkpoint) or use variables_from_torch_state_dict(torch.load(path))")
-    model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent)
+    model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent,
+                     fused_lookup_conv=fused_lookup_conv)
     return model, model.init(seed)
 
 

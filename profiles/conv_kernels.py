@@ -15,7 +15,8 @@ torch.backends.cudnn.allow_tf32 = True
 B, h, w = int(sys.argv[1]) if len(sys.argv) > 1 else 1, 55, 128
 cases = [  # name, cin, cout, kh, kw, pad, fused relu
     ("convcorr1 1x1 324->256", 324, 256, 1, 1, (0, 0), True), ("convcorr1 1x1 328->256", 328, 256, 1, 1, (0, 0), True),
-    ("convcorr2 3x3 256->192", 256, 192, 3, 3, (1, 1), True),
+    ("convcorr2 3x3 256->192", 256, 192, 3, 3, (1, 1), True), ("convcorr2 3x3 256->256", 256, 256, 3, 3, (1, 1), True),
+    ("convcorr2 3x3 256->192 nofuse", 256, 192, 3, 3, (1, 1), False), ("convcorr2 3x3 256->128", 256, 128, 3, 3, (1, 1), True),
     ("convflow1 7x7 2->128", 2, 128, 7, 7, (3, 3), True), ("convflow1 7x7 8->128", 8, 128, 7, 7, (3, 3), True),
     ("convflow1 7x7 4->128", 4, 128, 7, 7, (3, 3), True),
     ("convflow2 3x3 128->64", 128, 64, 3, 3, (1, 1), True),

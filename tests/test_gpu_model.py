@@ -63,6 +63,45 @@ def test_fused_update_block_matches_unfused(cuda, lib, golden, name):
     assert _epe(a[-1], b[-1]) <= 1e-3
 
 
+@pytest.mark.parametrize("name", ["raft_small", "raft_large"])
+def test_graph_replay_with_new_inputs_and_serial_schedule(cuda, lib, golden, name):
+    """The captured forward re-initialises its state on every replay (a second, different pair through
+    the same graph equals the eager result on that pair, and replaying the first pair again restores the
+    first result), and the side-stream schedule gives the result of the serial one."""
+    g = golden(f"e2e_{name}")
+    img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
+    rng = np.random.default_rng(11)
+    other1 = rng.uniform(-1, 1, img1.shape).astype(np.float32)
+    other2 = np.roll(other1, (-2, 4), axis=(1, 2))
+    model, variables = getattr(J, name)(precision="fp32", seed=5)
+    serial, _ = getattr(J, name)(precision="fp32", concurrent=False)
+    assert model.concurrent and not serial.concurrent
+    first = model.apply(variables, img1, img2, num_flow_updates=iters).clone()
+    second = model.apply(variables, other1, other2, num_flow_updates=iters).clone()
+    again = model.apply(variables, img1, img2, num_flow_updates=iters).clone()
+    assert torch.equal(first, again)
+    assert _epe(first.cpu().numpy()[-1], second.cpu().numpy()[-1]) > 0.1  # different inputs, different flows
+    for a, (x1, x2) in ((first, (img1, img2)), (second, (other1, other2))):
+        eager = model.apply(variables, x1, x2, num_flow_updates=iters, use_cuda_graph=False)
+        plain = serial.apply(variables, x1, x2, num_flow_updates=iters, use_cuda_graph=False)
+        assert _epe(a.cpu().numpy()[-1], eager.cpu().numpy()[-1]) <= 1e-3
+        assert _epe(eager.cpu().numpy()[-1], plain.cpu().numpy()[-1]) <= 1e-3
+
+
+@pytest.mark.parametrize("name", ["raft_small", "raft_large"])
+def test_fused_lookup_conv_in_the_model(cuda, lib, golden, name):
+    """SURVEY §8(f) f1 end to end: the flow with raftk_corr_lookup_conv1x1 in place of lookup + convcorr1
+    stays within the 0.01 px bar of the CPU reference (TF32 products on both GPU paths)."""
+    g = golden(f"e2e_{name}")
+    img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
+    net, ref_flows = _torchvision_cpu(name, img1, img2, iters)
+    variables = J.variables_from_torch_state_dict(net.state_dict())
+    model, _ = getattr(J, name)(fused_lookup_conv=True)
+    assert model.fused_lookup_conv
+    flows = model.apply(variables, img1, img2, num_flow_updates=iters).cpu().numpy()
+    assert _epe(flows[-1], ref_flows[-1]) <= 0.01
+
+
 def test_alt_corr_block_drops_in(cuda, lib, golden):
     g = golden("e2e_raft_large")
     img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
