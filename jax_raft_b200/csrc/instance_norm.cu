@@ -23,16 +23,24 @@ instnorm_stats_kernel(const float* __restrict__ x, double* __restrict__ stats, i
   if (tr < rows) {
     float fs[4] = {0, 0, 0, 0}, fq[4] = {0, 0, 0, 0};
     int cnt = 0;
-    for (int p = p0 + tr; p < p1; p += rows) {
-      const float4 v = __ldg(x4 + (size_t)p * c4 + tc);
+    auto add = [&](const float4 v) {
       fs[0] += v.x; fs[1] += v.y; fs[2] += v.z; fs[3] += v.w;
       fq[0] += v.x * v.x; fq[1] += v.y * v.y; fq[2] += v.z * v.z; fq[3] += v.w * v.w;
-      if (++cnt == 64) {  // spill the float partials into the double accumulators
+    };
+    int p = p0 + tr;
+    for (; p + 3 * rows < p1; p += 4 * rows) {  // four independent loads in flight per thread
+      const float4 v0 = __ldg(x4 + (size_t)p * c4 + tc);
+      const float4 v1 = __ldg(x4 + (size_t)(p + rows) * c4 + tc);
+      const float4 v2 = __ldg(x4 + (size_t)(p + 2 * rows) * c4 + tc);
+      const float4 v3 = __ldg(x4 + (size_t)(p + 3 * rows) * c4 + tc);
+      add(v0); add(v1); add(v2); add(v3);
+      if (++cnt == 16) {  // spill the float partials (64 pixels) into the double accumulators
 #pragma unroll
         for (int i = 0; i < 4; ++i) { s[i] += fs[i]; q[i] += fq[i]; fs[i] = 0; fq[i] = 0; }
         cnt = 0;
       }
     }
+    for (; p < p1; p += rows) add(__ldg(x4 + (size_t)p * c4 + tc));
 #pragma unroll
     for (int i = 0; i < 4; ++i) { s[i] += fs[i]; q[i] += fq[i]; }
   }
@@ -68,24 +76,39 @@ __global__ void __launch_bounds__(256) instnorm_finalize_kernel(double* __restri
   *reinterpret_cast<float2*>(stats + 2 * i) = mi;
 }
 
+// Thread (tr, tc) owns channel group tc (4 channels) of pixel rows tr, tr + rows, ... of one slice of
+// image n: its four (mean, 1/std) pairs are read once, and the loop has no index arithmetic beyond adds.
 template <bool RELU>
 __global__ void __launch_bounds__(256)
-instnorm_apply_kernel(float* __restrict__ x, const double* __restrict__ stats, int npix, int c4, long long total4) {
-  float4* x4 = reinterpret_cast<float4*>(x);
-  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total4; t += (long long)gridDim.x * blockDim.x) {
-    const int cc = (int)(t % c4);
-    const long long n = t / ((long long)npix * c4);
-    const double* st = stats + ((size_t)n * c4 * 4 + cc * 4) * 2;
-    float4 v = x4[t];
-    float* pv = reinterpret_cast<float*>(&v);
+instnorm_apply_kernel(float* __restrict__ x, const double* __restrict__ stats, int npix, int c4, int slices) {
+  const int n = blockIdx.y, slice = blockIdx.x;
+  const int rows = 256 / c4;
+  const int tc = threadIdx.x % c4, tr = threadIdx.x / c4;
+  if (tr >= rows) return;
+  float4* x4 = reinterpret_cast<float4*>(x) + (size_t)n * npix * c4 + tc;
+  const double* st = stats + ((size_t)n * c4 * 4 + tc * 4) * 2;
+  float2 mi[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float2 mi = __ldg(reinterpret_cast<const float2*>(st + 2 * i));
-      const float y = (pv[i] - mi.x) * mi.y;
-      pv[i] = RELU ? fmaxf(y, 0.0f) : y;
+  for (int i = 0; i < 4; ++i) mi[i] = __ldg(reinterpret_cast<const float2*>(st + 2 * i));
+  const int p0 = (int)((long long)npix * slice / slices), p1 = (int)((long long)npix * (slice + 1) / slices);
+  auto norm = [&](float4 v) {
+    v.x = (v.x - mi[0].x) * mi[0].y;
+    v.y = (v.y - mi[1].x) * mi[1].y;
+    v.z = (v.z - mi[2].x) * mi[2].y;
+    v.w = (v.w - mi[3].x) * mi[3].y;
+    if (RELU) {
+      v.x = fmaxf(v.x, 0.0f); v.y = fmaxf(v.y, 0.0f); v.z = fmaxf(v.z, 0.0f); v.w = fmaxf(v.w, 0.0f);
     }
-    x4[t] = v;
+    return v;
+  };
+  int p = p0 + tr;
+  for (; p + 3 * rows < p1; p += 4 * rows) {
+    float4* a = x4 + (size_t)p * c4;
+    const size_t step = (size_t)rows * c4;
+    const float4 v0 = a[0], v1 = a[step], v2 = a[2 * step], v3 = a[3 * step];
+    a[0] = norm(v0); a[step] = norm(v1); a[2 * step] = norm(v2); a[3 * step] = norm(v3);
   }
+  for (; p < p1; p += rows) x4[(size_t)p * c4] = norm(x4[(size_t)p * c4]);
 }
 
 }  // namespace raftk
@@ -107,13 +130,12 @@ extern "C" int raftk_instance_norm_nhwc(float* x, int n, int npix, int c, float 
   int slices = (RAFTK_SM_COUNT * 4 + n - 1) / n;
   if (slices > npix) slices = npix;
   instnorm_stats_kernel<<<dim3(slices, n), 256, 0, s>>>(x, static_cast<double*>(scratch), npix, c / 4, slices);
-  const long long total4 = (long long)n * npix * (c / 4);
-  long long blocks = (total4 + 255) / 256;
-  if (blocks > (long long)RAFTK_SM_COUNT * 16) blocks = (long long)RAFTK_SM_COUNT * 16;
+  int aslices = (RAFTK_SM_COUNT * 16 + n - 1) / n;
+  if (aslices > npix) aslices = npix;
   instnorm_finalize_kernel<<<(n * c + 255) / 256, 256, 0, s>>>(static_cast<double*>(scratch), n * c, npix, eps);
   if (relu)
-    instnorm_apply_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, total4);
+    instnorm_apply_kernel<true><<<dim3(aslices, n), 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, aslices);
   else
-    instnorm_apply_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, total4);
+    instnorm_apply_kernel<false><<<dim3(aslices, n), 256, 0, s>>>(x, static_cast<const double*>(scratch), npix, c / 4, aslices);
   return launch_status();
 }
