@@ -185,6 +185,13 @@ int raftk_bias_act_nhwc(float* x, const float* bias, long long npix, int c, int 
 size_t raftk_instance_norm_scratch_bytes(int n, int c);
 int raftk_instance_norm_nhwc(float* x, int n, int npix, int c, float eps, int relu, void* scratch,
                              size_t scratch_bytes, void* stream);
+/* Same, followed by the residual block's tail (model.py:183-184): x = relu(residual + y), y the
+ * normalised (and, if relu, rectified) value; residual (n, npix, c), 16-byte aligned. */
+int raftk_instance_norm_residual_nhwc(float* x, const float* residual, int n, int npix, int c, float eps, int relu,
+                                      void* scratch, size_t scratch_bytes, void* stream);
+/* Host-model glue: x = relu(x + y) over count floats (count % 4 == 0, 16-byte aligned): the residual
+ * tail of blocks whose norm layer is folded into the convolution (model.py:183-184, 215-216). */
+int raftk_add_relu(float* x, const float* y, long long count, void* stream);
 
 /* Host-model glue, not hot-path rows: the element-wise parts of ConvGRU (model.py:293-312) on NHWC
  * tensors.  `h` points at the hidden-state channel slice inside the z/r-convolution input buffer

@@ -50,6 +50,8 @@ SIGNATURES = {
     "raftk_bias_act_nhwc": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_int, c_void_p]),
     "raftk_instance_norm_scratch_bytes": (c_size_t, [c_int, c_int]),
     "raftk_instance_norm_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_size_t, c_void_p]),
+    "raftk_instance_norm_residual_nhwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, ctypes.c_float, c_int, c_void_p, ctypes.c_size_t, c_void_p]),
+    "raftk_add_relu": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_void_p]),
     "raftk_gru_gate": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_int, c_void_p]),
     "raftk_gru_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, ctypes.c_longlong, c_int, c_void_p]),
     "raftk_flow_update": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_void_p]),

@@ -335,34 +335,55 @@ def _conv(x, p: _ConvP, stride=1, padding=0, act=None, bias=True):
     return y
 
 
-def _instance_norm_(y, relu: bool, eps: float = 1e-5):
-    """In-place InstanceNorm(+ReLU) of a conv output through the glue kernel; shapes it does not
-    cover (channel counts not a multiple of 4) use the library op."""
+def _instance_norm_(y, relu: bool, eps: float = 1e-5, residual=None):
+    """In-place InstanceNorm(+ReLU) of a conv output through the glue kernel; with ``residual`` also the
+    residual block's tail ``relu(residual + .)``.  Shapes it does not cover (channel counts not a
+    multiple of 4) use the library ops."""
     n, c, h, w = y.shape
     if c % 4 or c > 1024:
         y = F.instance_norm(y, eps=eps)
-        return F.relu(y) if relu else y
-    if not y.is_contiguous(memory_format=torch.channels_last):
-        y = y.contiguous(memory_format=torch.channels_last)
+        y = F.relu(y) if relu else y
+        return y if residual is None else F.relu(residual + y)
+    y = _cl(y)
     lib = _lib.load()
     nbytes = lib.raftk_instance_norm_scratch_bytes(n, c)
     scratch = torch.empty((nbytes,), dtype=torch.uint8, device=y.device)
     with torch.cuda.device(y.device):
-        rc = lib.raftk_instance_norm_nhwc(y.data_ptr(), n, h * w, c, eps, 1 if relu else 0, scratch.data_ptr(), nbytes,
-                                          _lib.current_stream_ptr(y.device))
+        if residual is None:
+            rc = lib.raftk_instance_norm_nhwc(y.data_ptr(), n, h * w, c, eps, 1 if relu else 0, scratch.data_ptr(), nbytes,
+                                              _lib.current_stream_ptr(y.device))
+        else:
+            residual = _cl(residual)
+            assert residual.shape == y.shape
+            rc = lib.raftk_instance_norm_residual_nhwc(y.data_ptr(), residual.data_ptr(), n, h * w, c, eps, 1 if relu else 0,
+                                                       scratch.data_ptr(), nbytes, _lib.current_stream_ptr(y.device))
     _lib.check("raftk_instance_norm_nhwc", rc)
     _lib.count_launch(3)
     return y
 
 
-def _cna(P, path, x, norm, stride=1, padding=None, act=True):
-    """ConvNormActivation (model.py:120-159): conv (+bias), norm, relu."""
+def _add_relu_(x, y):
+    """relu(x + y) in one pass, into ``x`` when it is a dense channels_last tensor this call may overwrite."""
+    if x.numel() % 4 or not x.is_contiguous(memory_format=torch.channels_last) or not y.is_contiguous(memory_format=torch.channels_last):
+        return F.relu(x + y)
+    lib = _lib.load()
+    with torch.cuda.device(x.device):
+        rc = lib.raftk_add_relu(x.data_ptr(), y.data_ptr(), x.numel(), _lib.current_stream_ptr(x.device))
+    _lib.check("raftk_add_relu", rc)
+    _lib.count_launch(1)
+    return x
+
+
+def _cna(P, path, x, norm, stride=1, padding=None, act=True, residual=None):
+    """ConvNormActivation (model.py:120-159): conv (+bias), norm, relu; with ``residual`` (instance norm
+    only) also the enclosing block's ``relu(residual + .)``."""
     p = P[f"{path}/layers_0"]
     if padding is None:
         padding = ((p.w.shape[2] - 1) // 2, (p.w.shape[3] - 1) // 2)
     if norm == "instance":  # nn.InstanceNorm(epsilon=1e-5, no scale/bias), model.py:706-707
         # a per-channel bias cancels in (x - mean) / std, so the conv bias is not applied at all
-        return _instance_norm_(_conv(x, p, stride, padding, bias=False), relu=act)
+        return _instance_norm_(_conv(x, p, stride, padding, bias=False), relu=act, residual=residual)
+    assert residual is None
     return _conv(x, p, stride, padding, act="relu" if act else None)
 
 
@@ -372,16 +393,20 @@ def _encoder(P, prefix, x, layers, block, norm, strides):
         for bi in range(2):
             s = stride if bi == 0 else 1
             base = f"{prefix}/layer{li}/layers_{bi}"
+            last = "convnormrelu2" if block == "residual" else "convnormrelu3"
+            if s != 1:  # the shortcut first, so that the block's last norm can absorb the residual tail
+                shortcut = _cna(P, f"{base}/downsample", x, norm, stride=s, act=False)
+            else:
+                shortcut = x
+            fuse_tail = norm == "instance"
             if block == "residual":  # model.py:162-184
                 y = _cna(P, f"{base}/convnormrelu1", x, norm, stride=s)
-                y = _cna(P, f"{base}/convnormrelu2", y, norm)
             else:  # model.py:187-216
                 y = _cna(P, f"{base}/convnormrelu1", x, norm)
                 y = _cna(P, f"{base}/convnormrelu2", y, norm, stride=s)
-                y = _cna(P, f"{base}/convnormrelu3", y, norm)
-            if s != 1:
-                x = _cna(P, f"{base}/downsample", x, norm, stride=s, act=False)
-            x = F.relu(x + y)
+            y = _cna(P, f"{base}/{last}", y, norm, residual=shortcut if fuse_tail else None)
+            # relu(shortcut + y): inside the norm kernel above, else one pass into y (a fresh conv output)
+            x = y if fuse_tail else _add_relu_(y, shortcut)
     return _conv(x, P[f"{prefix}/conv"])
 
 

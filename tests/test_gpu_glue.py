@@ -142,3 +142,37 @@ def test_flow_update(cuda, lib, ld_delta, ld_flow):
     assert torch.equal(c1, ref_c1) and torch.equal(flow, ref_flow)
     if ld_flow:
         assert torch.equal(pitched[:, :2], ref_flow) and (pitched[:, 2:] == 3.0).all()
+
+
+@pytest.mark.parametrize("shape", [(2, 55, 128, 128), (1, 23, 31, 8)])
+@pytest.mark.parametrize("relu", [0, 1])
+def test_instance_norm_with_residual_tail(cuda, lib, shape, relu):
+    """raftk_instance_norm_residual_nhwc: relu(residual + [relu](instance_norm(x))) (model.py:183-184)."""
+    n, h, w, c = shape
+    gen = torch.Generator(device=cuda).manual_seed(c + relu)
+    x = torch.randn(shape, device=cuda, generator=gen) * 2.5 + 10.0
+    res = torch.randn(shape, device=cuda, generator=gen)
+    y = F.instance_norm(x.permute(0, 3, 1, 2).double(), eps=1e-5).permute(0, 2, 3, 1)
+    if relu:
+        y = F.relu(y)
+    ref = F.relu(res.double() + y)
+    got = x.clone()
+    nbytes = lib.raftk_instance_norm_scratch_bytes(n, c)
+    scratch = torch.empty((nbytes,), dtype=torch.uint8, device=cuda)
+    with torch.cuda.device(cuda):
+        rc = lib.raftk_instance_norm_residual_nhwc(got.data_ptr(), res.data_ptr(), n, h * w, c, 1e-5, relu, scratch.data_ptr(),
+                                                   nbytes, _stream(cuda))
+    _lib.check("raftk_instance_norm_residual_nhwc", rc)
+    assert torch.allclose(got.double(), ref, rtol=1e-4, atol=1e-4)
+
+
+def test_add_relu(cuda, lib):
+    gen = torch.Generator(device=cuda).manual_seed(1)
+    x = torch.randn((3, 17, 19, 8), device=cuda, generator=gen)
+    y = torch.randn((3, 17, 19, 8), device=cuda, generator=gen)
+    ref = F.relu(x + y)
+    with torch.cuda.device(cuda):
+        rc = lib.raftk_add_relu(x.data_ptr(), y.data_ptr(), x.numel(), _stream(cuda))
+    _lib.check("raftk_add_relu", rc)
+    assert torch.equal(x, ref)
+    assert lib.raftk_add_relu(x.data_ptr(), y.data_ptr(), 6, None) == -2
