@@ -192,6 +192,9 @@ def cpu_oracle_pairs_per_s(steps: int, warmup: int, budget_s: float):
     from oracle import corr_oracle_c, raft_cpu
 
     corr_oracle_c.build()
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if torch.get_num_threads() < avail:  # torchrun exports OMP_NUM_THREADS=1; this arm runs on rank 0 alone
+        torch.set_num_threads(avail)
     cores = torch.get_num_threads()
     net = raft_cpu.build_modules("raft_large", seed=0)
     img1, img2 = synthetic_pairs(1, seed=1)
@@ -221,6 +224,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # rank 0 alone runs the CPU arm
+    # all host threads for the one working rank (torchrun pins OMP_NUM_THREADS to 1 per rank); set before
+    # torch and the OpenMP C oracle are loaded
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    os.environ["OMP_NUM_THREADS"] = str(avail)
     value, per_pair, cores, sample, phases = cpu_oracle_pairs_per_s(args.steps, args.warmup, budget_s=150.0)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
