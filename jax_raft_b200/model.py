@@ -592,13 +592,16 @@ class RAFT:
             flows, out = [], None
             if state is not None and cfg.use_mask_predictor:  # the upsampler writes the stacked result directly
                 out = torch.empty((num_flow_updates, batch_size, h, w, 2), dtype=torch.float32, device=image1.device)
+            pending = None  # the previous iteration's upsampler launch, deferred past this iteration's lookup
             for i in range(num_flow_updates):  # nn.scan(UpdateCell), model.py:589-603
                 if state is not None:
-                    up = self._update_cell_fused(P, corr_pyramid, coords0, coords1, state, None if out is None else out[i],
-                                                 main, sa, sb, first=i == 0)
+                    up, pending = self._update_cell_fused(P, corr_pyramid, coords0, coords1, state,
+                                                          None if out is None else out[i], main, sa, sb, i == 0, pending)
                 else:
                     coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context)
                 flows.append(up)
+            if pending is not None:
+                pending()
             if sa is not None:  # the last mask predictor + upsampler
                 main.wait_stream(sa)
             return out if out is not None else torch.stack(flows, dim=0)
@@ -632,11 +635,13 @@ class RAFT:
         upsampled = upsample_flow(flow=(coords1 - coords0).contiguous(), up_mask=up_mask)
         return coords1, hidden_state, upsampled
 
-    def _update_cell_fused(self, P, corr_pyramid, coords0, coords1, state, out, main, sa, sb, first):
+    def _update_cell_fused(self, P, corr_pyramid, coords0, coords1, state, out, main, sa, sb, first, pending=None):
         """The same cell on the channel-slice buffers (``_RecurrentState``); coords1 and state are
         updated in place.  With side streams ``sa`` / ``sb``: the flow branch of the motion encoder runs
-        beside the correlation branch, and the mask predictor + upsampler run beside the flow head and
-        the next iteration's motion encoder (joined before the GRU overwrites the hidden state)."""
+        beside the correlation branch, the mask predictor beside the flow head, and the upsampler beside
+        the NEXT iteration's motion-encoder convolutions: its launch is returned as ``pending`` and issued
+        by the next call right after the lookup, so the two HBM-bound kernels never share the machine
+        (joined before the GRU overwrites the hidden state and the flow).  Returns (upsampled, pending)."""
         cfg = self.config
         me = "update_block/motion_encoder"
 
@@ -658,6 +663,8 @@ class RAFT:
             sb.wait_stream(main)
             with torch.cuda.stream(sb):
                 fl = flow_branch()
+        if pending is not None:
+            pending()
         if not fuse:
             corr = _cna(P, f"{me}/convcorr1", corr_features.permute(0, 3, 1, 2), None)
         if len(cfg.motion_encoder_corr_layers) == 2:
@@ -688,12 +695,16 @@ class RAFT:
         p = P["update_block/flow_head/conv2/padded"]
         state.update_flow(_cl(F.conv2d(d, p.w, None, padding=1)), p, coords0, coords1)
         if not cfg.use_mask_predictor:
-            return upsample_flow(flow=state.flow)
+            return upsample_flow(flow=state.flow), None
         if sa is None:
-            return upsample_flow(state.flow, mask_branch(), mask_bias=P["mask_predictor/conv"].b, out=out)
-        sa.wait_stream(main)
-        with torch.cuda.stream(sa):
-            return upsample_flow(state.flow, up_mask, mask_bias=P["mask_predictor/conv"].b, out=out)
+            return upsample_flow(state.flow, mask_branch(), mask_bias=P["mask_predictor/conv"].b, out=out), None
+
+        def deferred_upsample():
+            sa.wait_stream(main)
+            with torch.cuda.stream(sa):
+                upsample_flow(state.flow, up_mask, mask_bias=P["mask_predictor/conv"].b, out=out)
+
+        return out, deferred_upsample
 
     # -- public entry, mirrors flax Module.apply -------------------------------------------
     def apply(self, variables: Tree, image1, image2, train: bool = False, num_flow_updates: int = 12,
