@@ -5,24 +5,27 @@
 //   out[q, n] = act( sum_c W[n, c] * lookup(q)[c] + bias[n] )
 //
 // One CTA = 64 query pixels (UMMA M = 64, cta_group::1), all N <= 256 output channels:
-//   warps 0-15 lookup: the software-pipelined per-query routine of corr_lookup.cu (same float32 tap
-//              arithmetic, bit-identical values), four queries per warp, but the taps are written into a
-//              K-major, 128-byte-swizzled A tile in shared memory (12 K-blocks of 64 rows x 32 floats for
-//              r = 4; each level's 81 channels are padded to 96 so that a K-block never straddles two levels);
-//   warp 16    TMA producer: the prepared weights W' (N rows x K' floats) stream through a 2-stage ring,
+//   warps 0-15 lookup, four queries per warp, LEVEL-MAJOR: the float32 tap arithmetic of corr_lookup.cu
+//              (bit-identical values), one level of all four queries at a time, with the next level's
+//              footprint chunks in flight; the taps go into a K-major, 128-byte-swizzled A tile in shared
+//              memory (12 K-blocks of 64 rows x 32 floats for r = 4; each level's 81 channels are padded to
+//              96, so level l is exactly K-blocks 3l..3l+2 and its MMAs can start when its taps are done);
+//   warp 16    TMA producer: the prepared weights W' (N rows x K' floats) stream through a 3-stage ring,
 //              one 32-float K-block (N x 128 B) per stage;
-//   warp 17    one thread issues tcgen05.mma.kind::tf32 (K = 8 per instruction) once the A tile is
-//              complete; the accumulator (64 x N float32) lives in TMEM;
-//   warps 0-3  epilogue: tcgen05.ld, + bias, ReLU, 128-byte row segments to global memory.
+//   warp 17    one thread issues tcgen05.mma.kind::tf32 (K = 8 per instruction), level by level, into a
+//              64 x N float32 accumulator in TMEM — the MMAs of level l run under the taps of level l + 1;
+//   warps 0-15 epilogue: tcgen05.ld (lane quarter = warp % 4, N columns split over the four warps of a
+//              quarter), + bias (staged in shared memory), ReLU, 128-byte row segments to global memory.
 // The multiplication is TF32 (10-bit mantissa operands, float32 accumulation) — what the library
 // convolution it replaces uses in the default precision mode.
 //
-// Status: parity-green, but SLOWER than the two-kernel path at every batch size measured
-// (batch 1: 28 us against 15.4 us for raftk_corr_lookup + the library's 1x1 convolution back to back), so the
-// host model does not use it by default.  The three phases of a CTA run one after the other, each of the
-// 110 CTAs streams all 384 KB of weights from L2 (42 MB per launch), and with one CTA per SM (220 KB of
-// shared memory) nothing overlaps across CTAs.  What it would take: weight multicast across a cluster and a
-// level-major tap order so that the MMAs of level l run under the taps of level l+1.
+// Status: parity-green, but still slower than the two-kernel path (batch 1: 21.4 us against
+// 15.4 us for raftk_corr_lookup + the library's 1x1 convolution back to back), so the host model does not use
+// it by default.  Phase elimination at batch 1: launch + TMEM + epilogue skeleton 8.2 us, + taps 10.8 us,
+// + weights and MMAs 3.2 us (mostly hidden).  The taps are the problem: 64 queries per SM on 16 warps issue at
+// 40 % (ncu: 1073 instructions per query against 779 in the stand-alone kernel, 89 KB of unrolled code with
+// instruction-fetch stalls, four warps per scheduler), where the stand-alone kernel spreads the same
+// arithmetic over 148 SMs x 48 warps.
 
 #include <cuda.h>
 
@@ -37,7 +40,7 @@ namespace lc {
 constexpr int TM = 64;  // queries per CTA
 constexpr int LOOKUP_WARPS = 16;
 constexpr int NUM_THREADS = (LOOKUP_WARPS + 2) * 32;
-constexpr int STAGES = 2;
+constexpr int STAGES = 3;
 constexpr int PITCH = 20;
 constexpr int A_BLOCK_BYTES = TM * 128;  // one K-block of the A tile: 64 rows x 32 floats
 constexpr int SMEM_LIMIT = 232448;       // 227 KB
@@ -150,12 +153,13 @@ lookup_conv_kernel(const __grid_constant__ CUtensorMap tmW, const Params p) {
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + KB * A_BLOCK_BYTES;
   float* smem_f = reinterpret_cast<float*>(smem_b + STAGES * b_stage_bytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_f + LOOKUP_WARPS * 4 * TILE);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_f + LOOKUP_WARPS * TILE);
   uint64_t* b_full = bars;             // [STAGES]
   uint64_t* b_empty = bars + STAGES;   // [STAGES]
-  uint64_t* a_ready = bars + 2 * STAGES;
-  uint64_t* acc_full = a_ready + 1;
+  uint64_t* a_ready = bars + 2 * STAGES;  // [4]: level l's K-blocks of the A tile are written
+  uint64_t* acc_full = a_ready + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  float* smem_bias = reinterpret_cast<float*>(bars + 16);  // [N], 128 bytes past the barriers
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * TM;
@@ -166,7 +170,7 @@ lookup_conv_kernel(const __grid_constant__ CUtensorMap tmW, const Params p) {
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 1);
     }
-    mbar_init(a_ready, LOOKUP_WARPS);
+    for (int l = 0; l < 4; ++l) mbar_init(&a_ready[l], LOOKUP_WARPS);
     mbar_init(acc_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -174,17 +178,22 @@ lookup_conv_kernel(const __grid_constant__ CUtensorMap tmW, const Params p) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(tmem_cols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
+  for (int i = threadIdx.x; i < p.N; i += NUM_THREADS) smem_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp < LOOKUP_WARPS) {
-    // ===================== lookup: taps -> A tile =====================
-    float* F = smem_f + warp * (4 * TILE);
-    for (int e = lane; e < 4 * PITCH; e += 32) F[(e / PITCH) * TILE + FP * PITCH + (e % PITCH)] = 0.0f;  // guard rows
-    // padding columns of the A tile (channels SS..KL-1 of every level) are zero: rows warp, warp+8, ...
-    for (int e = lane; e < (TM / LOOKUP_WARPS) * 4 * (KL - SS); e += 32) {
+    // ===================== lookup: taps -> A tile, level-major =====================
+    // Each warp owns QPW rows of the tile (queries q0 + warp + LOOKUP_WARPS * j) and walks them level by
+    // level, so that level l's K-blocks are complete — and their MMAs can run — while the taps of level
+    // l + 1 are evaluated.  One (query, level) footprint is in flight ahead of the one being evaluated.
+    constexpr int QPW = TM / LOOKUP_WARPS;
+    float* F = smem_f + warp * TILE;  // one level's footprint tile
+    for (int e = lane; e < PITCH; e += 32) F[FP * PITCH + e] = 0.0f;  // guard row
+    // padding columns of the A tile (channels SS..KL-1 of every level) are zero
+    for (int e = lane; e < QPW * 4 * (KL - SS); e += 32) {
       const int rr = e / (4 * (KL - SS)), rem = e % (4 * (KL - SS));
       const int l = rem / (KL - SS), c = l * KL + SS + rem % (KL - SS);
       const int r = warp + LOOKUP_WARPS * rr;
@@ -202,78 +211,70 @@ lookup_conv_kernel(const __grid_constant__ CUtensorMap tmW, const Params p) {
     }
     const bool last_tap_valid = lane + 32 * (NTAP - 1) < SS;
     const int row_u = lane >> 2, chunk = lane & 3;
-    const int lvx = lane >> 3, rowx = 8 + ((lane >> 2) & 1);
-    const float* levelx = lvx == 0 ? p.level[0] : lvx == 1 ? p.level[1] : lvx == 2 ? p.level[2] : p.level[3];
-    const int lhx = lvx == 0 ? p.lh[0] : lvx == 1 ? p.lh[1] : lvx == 2 ? p.lh[2] : p.lh[3];
-    const int lwx = lvx == 0 ? p.lw[0] : lvx == 1 ? p.lw[1] : lvx == 2 ? p.lw[2] : p.lw[3];
-    const bool alignedx = (lvx == 0 ? p.aligned[0] : lvx == 1 ? p.aligned[1] : lvx == 2 ? p.aligned[2] : p.aligned[3]) != 0;
     const uint64_t pol = l2_policy_evict_last();
 
-    float4 v[5];
-    auto fetch = [&](int q, float cx, float cy) {
+    float cx[QPW], cy[QPW];
+    bool fastq[QPW], validq[QPW];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        v[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        const float sc = __int_as_float((127 - k) << 23);
-        const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
-        const int lh = p.lh[k], lw = p.lw[k];
-        const int gy = by + row_u, gx = (bx & ~3) + 4 * chunk;
-        if (row_u < FP && gx <= bx + FP - 1)
-          v[k] = load_chunk(p.level[k] + (size_t)q * lh * lw, lh, lw, gy, gx, p.aligned[k] != 0, pol);
-      }
-      v[4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-      if (FP > 8) {
-        const float sc = __int_as_float((127 - lvx) << 23);
-        const int bx = (int)floorf(cx * sc) - R, by = (int)floorf(cy * sc) - R;
-        const int gy = by + rowx, gx = (bx & ~3) + 4 * chunk;
-        if (gx <= bx + FP - 1) v[4] = load_chunk(levelx + (size_t)q * lhx * lwx, lhx, lwx, gy, gx, alignedx, pol);
+    for (int j = 0; j < QPW; ++j) {
+      const int q = q0 + warp + LOOKUP_WARPS * j;
+      validq[j] = q < p.Q;
+      cx[j] = validq[j] ? __ldg(p.coords + 2 * (size_t)q) : 0.0f;
+      cy[j] = validq[j] ? __ldg(p.coords + 2 * (size_t)q + 1) : 0.0f;
+      fastq[j] = validq[j] && fabsf(cx[j]) <= 1.0e6f && fabsf(cy[j]) <= 1.0e6f;
+    }
+
+    // the chunks of one level's footprints of all QPW queries (rows 0-7 by all lanes, rows 8.. by lanes 0-7),
+    // fetched one level ahead of the taps: DRAM latency hides behind a whole level of tap arithmetic
+    float4 cur0[QPW], cur1[QPW], nxt0[QPW], nxt1[QPW];
+    auto fetch_level = [&](int l, float4* a0, float4* a1) {
+      const float sc = __int_as_float((127 - l) << 23);
+      const int lh = p.lh[l], lw = p.lw[l];
+      const bool al = p.aligned[l] != 0;
+#pragma unroll
+      for (int j = 0; j < QPW; ++j) {
+        a0[j] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        a1[j] = a0[j];
+        if (!fastq[j]) continue;
+        const int q = q0 + warp + LOOKUP_WARPS * j;
+        const int bx = (int)floorf(cx[j] * sc) - R, by = (int)floorf(cy[j] * sc) - R;
+        const float* slab = p.level[l] + (size_t)q * lh * lw;
+        const int gx = (bx & ~3) + 4 * chunk;
+        if (gx <= bx + FP - 1) {
+          a0[j] = load_chunk(slab, lh, lw, by + row_u, gx, al, pol);
+          if (FP > 8 && row_u < FP - 8) a1[j] = load_chunk(slab, lh, lw, by + 8 + row_u, gx, al, pol);
+        }
       }
     };
-    auto near = [](float cx, float cy) { return fabsf(cx) <= 1.0e6f && fabsf(cy) <= 1.0e6f; };
 
-    int r = warp;  // row of the A tile = query q0 + r
-    float cx = 0.0f, cy = 0.0f;
-    if (q0 + r < p.Q) {
-      cx = __ldg(p.coords + 2 * (size_t)(q0 + r));
-      cy = __ldg(p.coords + 2 * (size_t)(q0 + r) + 1);
-      if (near(cx, cy)) fetch(q0 + r, cx, cy);
-    }
-    for (; r < TM; r += LOOKUP_WARPS) {
-      const int q = q0 + r, rn = r + LOOKUP_WARPS;
-      const bool valid = q < p.Q;
-      const bool fast = valid && near(cx, cy);
-      if (fast) {
+    fetch_level(0, cur0, cur1);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (row_u < FP) *reinterpret_cast<float4*>(F + k * TILE + row_u * PITCH + chunk * 4) = v[k];
-        if (FP > 8) *reinterpret_cast<float4*>(F + lvx * TILE + rowx * PITCH + chunk * 4) = v[4];
+    for (int l = 0; l < 4; ++l) {
+      const float sc = __int_as_float((127 - l) << 23);
+      if (l + 1 < 4) fetch_level(l + 1, nxt0, nxt1);
+#pragma unroll
+      for (int j = 0; j < QPW; ++j) {
+        const int r = warp + LOOKUP_WARPS * j;
+        if (fastq[j]) {
+          *reinterpret_cast<float4*>(F + row_u * PITCH + chunk * 4) = cur0[j];
+          if (FP > 8 && row_u < FP - 8) *reinterpret_cast<float4*>(F + (8 + row_u) * PITCH + chunk * 4) = cur1[j];
+        }
         __syncwarp();
-      }
-      float ncx = 0.0f, ncy = 0.0f;
-      if (rn < TM && q0 + rn < p.Q) {
-        ncx = __ldg(p.coords + 2 * (size_t)(q0 + rn));
-        ncy = __ldg(p.coords + 2 * (size_t)(q0 + rn) + 1);
-        if (near(ncx, ncy)) fetch(q0 + rn, ncx, ncy);
-      }
-      uint8_t* arow = smem_a + r * 128;
-      const int sw = r & 7;
-#pragma unroll
-      for (int l = 0; l < 4; ++l) {
-        const float sc = __int_as_float((127 - l) << 23);
-        const float cxl = cx * sc, cyl = cy * sc;
+        uint8_t* arow = smem_a + r * 128;
+        const int sw = r & 7;
+        const float cxl = cx[j] * sc, cyl = cy[j] * sc;
         const float fbxa = (float)(((int)floorf(cxl) - R) & ~3);
         const float fby = floorf(cyl) - (float)R;
-        const float* Fl = F + l * TILE;
 #pragma unroll
         for (int k = 0; k < NTAP; ++k) {
           float acc;
-          if (fast) {
+          if (fastq[j]) {
             const float sx = __fadd_rn(cxl, di[k]), sy = __fadd_rn(cyl, dj[k]);
             const float fx0 = floorf(sx), fy0 = floorf(sy);
             const float wx1 = __fadd_rn(sx, -fx0), wy1 = __fadd_rn(sy, -fy0);
             const float wx0 = __fadd_rn(1.0f, -wx1), wy0 = __fadd_rn(1.0f, -wy1);
             const int off = __float2int_rn(fmaf(fy0 - fby, (float)PITCH, fx0 - fbxa));
-            const float* f = Fl + off;
+            const float* f = F + off;
             acc = __fmul_rn(__fmul_rn(wy0, wx0), f[0]);
             acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy0, wx1), f[1]));
             acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx0), f[PITCH]));
@@ -282,40 +283,44 @@ lookup_conv_kernel(const __grid_constant__ CUtensorMap tmW, const Params p) {
             // row past the end of the batch: zeros.  Query farther than 1e6 from the map: every corner
             // of every tap is outside every level -> 0, or NaN when a coordinate is not finite
             // (0 * weight, as the reference's arithmetic gives)
-            acc = valid ? __fadd_rn(__fadd_rn(cx, -cx), __fadd_rn(cy, -cy)) : 0.0f;
+            acc = validq[j] ? __fadd_rn(__fadd_rn(cx[j], -cx[j]), __fadd_rn(cy[j], -cy[j])) : 0.0f;
           }
-          if (k < NTAP - 1 || last_tap_valid) {
-            const int c = l * KL + lane + 32 * k;  // channel in the padded K order
-            *reinterpret_cast<float*>(arow + (c >> 5) * A_BLOCK_BYTES + ((((c & 31) >> 2) ^ sw) << 4) + (c & 3) * 4) = acc;
-          }
+          if (k < NTAP - 1 || last_tap_valid)  // channel l*KL + 32*k + lane of the padded K order: K-block l*KL/32 + k
+            *reinterpret_cast<float*>(arow + (l * (KL / 32) + k) * A_BLOCK_BYTES + (((lane >> 2) ^ sw) << 4) + (lane & 3) * 4) = acc;
         }
+        __syncwarp();
       }
+      fence_async_smem();  // generic-proxy writes of level l's K-blocks -> visible to the tensor core's async proxy
       __syncwarp();
-      cx = ncx;
-      cy = ncy;
+      if (lane == 0) mbar_arrive(&a_ready[l]);
+#pragma unroll
+      for (int j = 0; j < QPW; ++j) {
+        cur0[j] = nxt0[j];
+        cur1[j] = nxt1[j];
+      }
     }
-    fence_async_smem();  // generic-proxy writes of the A tile -> visible to the tensor core's async proxy
-    __syncwarp();
-    if (lane == 0) mbar_arrive(a_ready);
 
-    // ===================== epilogue (warps 0-3: TMEM lane quarter = warp) =====================
-    if (warp < 4) {
+    // ===================== epilogue (all lookup warps) =====================
+    // TMEM lane quarter = warp % 4 (M = 64: accumulator row m lives in lane (m % 16) + 32 * (m / 16), lanes
+    // 0-15 of each quarter); the N columns are split over the LOOKUP_WARPS / 4 warps that share a quarter
+    {
       mbar_wait(acc_full, 0);
       tc_fence_after();
-      // M = 64: accumulator row m lives in TMEM lane (m % 16) + 32 * (m / 16) — lanes 0-15 of each quarter
-      const int m = 16 * warp + lane;
+      const int quarter = warp & 3, part = warp >> 2;
+      constexpr int PARTS = LOOKUP_WARPS / 4;
+      const int m = 16 * quarter + lane;
       const long long q = (long long)q0 + m;
       const bool store = lane < 16 && q < p.Q;
-      for (int n0 = 0; n0 < p.N; n0 += 32) {
+      for (int n0 = 32 * part; n0 < p.N; n0 += 32 * PARTS) {
         float acc[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)n0, acc);
+        tmem_ld_32x32(tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)n0, acc);
         tmem_ld_wait();
         if (store) {
           float* orow = p.out + q * p.N + n0;
 #pragma unroll
           for (int c = 0; c < 32; c += 4) {
             if (n0 + c < p.N) {
-              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c));
+              const float4 b = *reinterpret_cast<const float4*>(smem_bias + n0 + c);
               float4 o = make_float4(acc[c] + b.x, acc[c + 1] + b.y, acc[c + 2] + b.z, acc[c + 3] + b.w);
               if (p.relu) {
                 o.x = fmaxf(o.x, 0.0f);
@@ -348,11 +353,13 @@ lookup_conv_kernel(const __grid_constant__ CUtensorMap tmW, const Params p) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       const uint32_t idesc = make_idesc(TM, p.N);
-      mbar_wait(a_ready, 0);
-      tc_fence_after();
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = 0; kb < KB; ++kb) {
+        if (kb % (KL / 32) == 0) {  // first K-block of a level: its taps must be in the A tile
+          mbar_wait(&a_ready[kb / (KL / 32)], 0);
+          tc_fence_after();
+        }
         mbar_wait(&b_full[stage], phase);
         tc_fence_after();
         const uint32_t as = smem_u32(smem_a + kb * A_BLOCK_BYTES);
@@ -447,7 +454,7 @@ extern "C" int raftk_corr_lookup_conv1x1(const float* const* levels, int num_lev
       return RAFTK_ERR_UNSUPPORTED;
   }
   const int tile = (2 * radius + 3) * PITCH;
-  const size_t smem = 1024 + (size_t)KB * A_BLOCK_BYTES + (size_t)STAGES * N * 128 + (size_t)LOOKUP_WARPS * 4 * tile * 4 + 128;
+  const size_t smem = 1024 + (size_t)KB * A_BLOCK_BYTES + (size_t)STAGES * N * 128 + (size_t)LOOKUP_WARPS * tile * 4 + 128 + (size_t)N * 4;
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   const int blocks = (Q + TM - 1) / TM;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
