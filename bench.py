@@ -255,7 +255,7 @@ class _TimedCorr:
     def __init__(self, inner, torch, external: bool):
         self.inner, self.torch, self.external = inner, torch, external
         self.out_channels = inner.out_channels
-        self.lookup_events, self.build_events = [], []
+        self.lookup_events, self.build_events, self.empty_events = [], [], []
 
     def _pair(self):
         kw = {"external": True} if self.external else {}
@@ -270,6 +270,10 @@ class _TimedCorr:
         return out
 
     def index_pyramid(self, pyr, coords):
+        e0, e1 = self._pair()  # nothing between them: what an event pair costs by itself at this point of the graph
+        e0.record()
+        e1.record()
+        self.empty_events.append((e0, e1))
         a, b = self._pair()
         a.record()
         out = self.inner.index_pyramid(pyr, coords)
@@ -279,7 +283,11 @@ class _TimedCorr:
 
 
 def time_hot_path_kernels(torch, J, model, variables, runner, flush, dev, passes):
-    """Mean launch duration (ms) of the lookup and of build_pyramid inside full forwards."""
+    """Mean launch duration (ms) of the lookup and of build_pyramid inside full forwards.  Also leaves the
+    mean duration of an EMPTY event pair (two event nodes with nothing between) in
+    ``time_hot_path_kernels.event_overhead_ms``: the part of every event-bracketed figure that is the
+    events themselves."""
+    time_hot_path_kernels.event_overhead_ms = None
     P = model.prepare(variables, dev)
     try:
         tcorr = _TimedCorr(model.corr_block, torch, external=True)
@@ -287,13 +295,15 @@ def time_hot_path_kernels(torch, J, model, variables, runner, flush, dev, passes
         g = torch.cuda.CUDAGraph()
         with torch.no_grad(), torch.cuda.graph(g):
             model_t.forward(P, runner.image1, runner.image2, ITERS)
-        lk, bd = [], []
+        lk, bd, ov = [], [], []
         for _ in range(passes):
             flush.fill_(1)
             g.replay()
             torch.cuda.synchronize(dev)
             lk += [a.elapsed_time(b) for a, b in tcorr.lookup_events]
             bd += [a.elapsed_time(b) for a, b in tcorr.build_events]
+            ov += [a.elapsed_time(b) for a, b in tcorr.empty_events]
+        time_hot_path_kernels.event_overhead_ms = sum(ov) / len(ov) if ov else None
         return lk, bd, "CUDA events recorded as graph nodes around each launch, graph replay of the full forward"
     except Exception as exc:  # older torch without external events: eager pass behind a GPU backlog
         tcorr = _TimedCorr(model.corr_block, torch, external=False)
@@ -494,6 +504,7 @@ def run_b200(args):
     nq = B * (H // 8) * (W // 8)
     lookup_bytes = nq * (L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4)  # 2904 B/query
     lk_mean_ms = sum(lk_ms) / len(lk_ms)
+    ev_ov = time_hot_path_kernels.event_overhead_ms
     achieved = lookup_bytes / (lk_mean_ms * 1e-3) / 1e9
     N = (H // 8) * (W // 8)
     P_l = sum((H // 8 >> l) * (W // 8 >> l) for l in range(L))
@@ -527,6 +538,11 @@ def run_b200(args):
             "peak_source": peak_src, "algorithmic_bytes_per_launch": lookup_bytes,
             "mean_launch_ms": lk_mean_ms, "launches_timed": len(lk_ms),
             "how": how,
+            # what the bracketing events cost by themselves (an empty pair at the same place in the graph);
+            # `achieved` and `frac` above are NOT corrected for it — these two are
+            "event_pair_overhead_ms": ev_ov,
+            "frac_net_of_event_overhead": (lookup_bytes / (max(lk_mean_ms - ev_ov, 1e-6) * 1e-3) / 1e9 / hbm_gbs
+                                           if ev_ov is not None else None),
         },
         "kernels_in_step": {
             "corr_pyramid": {"mean_ms": pyr_ms, "algorithmic_bytes": pyr_bytes,
