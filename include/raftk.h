@@ -217,6 +217,14 @@ int raftk_motion_scatter(const float* cf_pre, int ld_src, const float* bias, con
 int raftk_flow_update(const float* delta_pre, int ld_delta, const float* bias, const float* coords0, float* coords1,
                       float* flow, float* flow_pitched, int ld_flow, long long npix, void* stream);
 
+/* Tuning knob, no counterpart in the reference: the short kernels (lookup, update-block glue) are launched
+ * with programmatic stream serialization, so that each may be scheduled while its predecessor drains and
+ * waits in its first instruction (griddepcontrol.wait) — this hides most of the node-to-node launch
+ * latency inside the forward's CUDA graph.  raftk_set_pdl(0) launches them the ordinary way (initial value:
+ * on, or off if the environment has RAFTK_PDL=0); returns the previous setting.  Process-wide, not
+ * synchronised: set it before launching. */
+int raftk_set_pdl(int on);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,3 +21,20 @@ extern "C" const char* raftk_error_string(int code) {
       return "raftk: unknown error code";
   }
 }
+
+namespace raftk {
+int& pdl_flag() {
+  static int flag = [] {
+    const char* e = getenv("RAFTK_PDL");
+    return (e && e[0] == '0') ? 0 : 1;
+  }();
+  return flag;
+}
+}  // namespace raftk
+
+extern "C" int raftk_set_pdl(int on) {
+  int& f = raftk::pdl_flag();
+  const int prev = f;
+  f = on ? 1 : 0;
+  return prev;
+}

@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
   extern __shared__ float smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* F = smem + warp * (4 * TILE);
+  pdl_wait();  // the coordinates come from the kernel before this one
   // guard row of each level tile (never written again); all other cells are rewritten per query
   for (int e = lane; e < 4 * PITCH; e += 32) F[(e / PITCH) * TILE + FP * PITCH + (e % PITCH)] = 0.0f;
   __syncwarp();
@@ -286,9 +287,9 @@ extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, con
     int blocks = (Q + 2 * kFastWarps - 1) / (2 * kFastWarps);
     if (blocks > RAFTK_SM_COUNT * 8) blocks = RAFTK_SM_COUNT * 8;
     if (radius == 4)
-      corr_lookup_fast_kernel<4><<<blocks, kFastWarps * 32, smem, s>>>(p);
+      launch_pdl(corr_lookup_fast_kernel<4>, blocks, kFastWarps * 32, smem, s, p);
     else
-      corr_lookup_fast_kernel<3><<<blocks, kFastWarps * 32, smem, s>>>(p);
+      launch_pdl(corr_lookup_fast_kernel<3>, blocks, kFastWarps * 32, smem, s, p);
     return launch_status();
   }
   const int FP = 2 * radius + 2;

@@ -26,6 +26,7 @@ template <int V>
 __global__ void __launch_bounds__(256)
 gru_gate_kernel(const float* __restrict__ zr_pre, const float* __restrict__ bias_zr, const float* __restrict__ h, int ldh,
                 float* __restrict__ z_out, float* __restrict__ rh_out, int ld_rh, long long npix, int H) {
+  pdl_wait();
   using T = Vec<V>;
   const int HV = H / V;
   const long long total = npix * HV;
@@ -52,6 +53,7 @@ template <int V>
 __global__ void __launch_bounds__(256)
 gru_update_kernel(const float* __restrict__ q_pre, const float* __restrict__ bq, const float* __restrict__ z,
                   float* __restrict__ h, int ldh, float* __restrict__ h_dense, long long npix, int H) {
+  pdl_wait();
   using T = Vec<V>;
   const int HV = H / V;
   const long long total = npix * HV;
@@ -73,6 +75,7 @@ gru_update_kernel(const float* __restrict__ q_pre, const float* __restrict__ bq,
 __global__ void __launch_bounds__(256)
 motion_scatter_kernel(const float* __restrict__ cf_pre, const float* __restrict__ bias, const float* __restrict__ flow,
                       float* __restrict__ dst_a, float* __restrict__ dst_b, int ld, long long npix, int c_cf, int ld_src) {
+  pdl_wait();
   const int per_pix = c_cf / 2 + 1;
   const long long total = npix * per_pix;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
@@ -97,6 +100,10 @@ __global__ void __launch_bounds__(256)
 flow_update_kernel(const float* __restrict__ delta_pre, int ld_delta, const float2* __restrict__ bias_p,
                    const float2* __restrict__ coords0, float2* __restrict__ coords1, float2* __restrict__ flow,
                    float* __restrict__ flow_pitched, int ld_flow, long long npix) {
+  pdl_wait();
+  // the kernel after this one in the step is the lookup, which waits for this grid in its first instruction:
+  // let it be scheduled now
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const float2 bias = __ldg(bias_p);
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < npix; t += (long long)gridDim.x * blockDim.x) {
     const float2 d = *reinterpret_cast<const float2*>(delta_pre + t * ld_delta), c0 = coords0[t];
@@ -129,9 +136,9 @@ extern "C" int raftk_gru_gate(const float* zr_pre, const float* bias_zr, const f
   const bool v4 = !(bits & 15) && hidden % 4 == 0 && ldh % 4 == 0 && ld_rh % 4 == 0;
   auto s = static_cast<cudaStream_t>(stream);
   if (v4)
-    gru_gate_kernel<4><<<grid_for(npix * (hidden / 4)), 256, 0, s>>>(zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
+    launch_pdl(gru_gate_kernel<4>, grid_for(npix * (hidden / 4)), 256, 0, s, zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
   else
-    gru_gate_kernel<2><<<grid_for(npix * (hidden / 2)), 256, 0, s>>>(zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
+    launch_pdl(gru_gate_kernel<2>, grid_for(npix * (hidden / 2)), 256, 0, s, zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
   return launch_status();
 }
 
@@ -146,9 +153,9 @@ extern "C" int raftk_gru_update(const float* q_pre, const float* bq, const float
   const bool v4 = !(bits & 15) && hidden % 4 == 0 && ldh % 4 == 0;
   auto s = static_cast<cudaStream_t>(stream);
   if (v4)
-    gru_update_kernel<4><<<grid_for(npix * (hidden / 4)), 256, 0, s>>>(q_pre, bq, z, h, ldh, h_dense, npix, hidden);
+    launch_pdl(gru_update_kernel<4>, grid_for(npix * (hidden / 4)), 256, 0, s, q_pre, bq, z, h, ldh, h_dense, npix, hidden);
   else
-    gru_update_kernel<2><<<grid_for(npix * (hidden / 2)), 256, 0, s>>>(q_pre, bq, z, h, ldh, h_dense, npix, hidden);
+    launch_pdl(gru_update_kernel<2>, grid_for(npix * (hidden / 2)), 256, 0, s, q_pre, bq, z, h, ldh, h_dense, npix, hidden);
   return launch_status();
 }
 
@@ -159,8 +166,8 @@ extern "C" int raftk_motion_scatter(const float* cf_pre, int ld_src, const float
   if (npix == 0) return RAFTK_OK;
   if (!cf_pre || !bias || !flow || !dst_a || !dst_b) return RAFTK_ERR_NULL;
   if (((uintptr_t)cf_pre | (uintptr_t)bias | (uintptr_t)flow | (uintptr_t)dst_a | (uintptr_t)dst_b) & 7) return RAFTK_ERR_ALIGN;
-  motion_scatter_kernel<<<grid_for(npix * (c_cf / 2 + 1)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      cf_pre, bias, flow, dst_a, dst_b, ld, npix, c_cf, ld_src);
+  launch_pdl(motion_scatter_kernel, grid_for(npix * (c_cf / 2 + 1)), 256, 0, static_cast<cudaStream_t>(stream), cf_pre, bias,
+             flow, dst_a, dst_b, ld, npix, c_cf, ld_src);
   return launch_status();
 }
 
@@ -174,8 +181,8 @@ extern "C" int raftk_flow_update(const float* delta_pre, int ld_delta, const flo
   if (((uintptr_t)delta_pre | (uintptr_t)bias | (uintptr_t)coords0 | (uintptr_t)coords1 | (uintptr_t)flow |
        (uintptr_t)flow_pitched) & 7)
     return RAFTK_ERR_ALIGN;
-  flow_update_kernel<<<grid_for(npix), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      delta_pre, ld_delta, reinterpret_cast<const float2*>(bias), reinterpret_cast<const float2*>(coords0),
-      reinterpret_cast<float2*>(coords1), reinterpret_cast<float2*>(flow), flow_pitched, ld_flow, npix);
+  launch_pdl(flow_update_kernel, grid_for(npix), 256, 0, static_cast<cudaStream_t>(stream), delta_pre, ld_delta,
+             reinterpret_cast<const float2*>(bias), reinterpret_cast<const float2*>(coords0),
+             reinterpret_cast<float2*>(coords1), reinterpret_cast<float2*>(flow), flow_pitched, ld_flow, npix);
   return launch_status();
 }

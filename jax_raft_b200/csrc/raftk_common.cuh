@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 #include "raftk.h"
 
 #define RAFTK_SM_COUNT 148  // B200: 2 dies x 74 SMs
@@ -23,6 +25,33 @@ static inline bool levels_fit(int h, int w, int num_levels) {
 }
 
 __device__ __forceinline__ float ldg_f32(const float* p) { return __ldg(p); }
+
+// Programmatic dependent launch: a kernel launched through launch_pdl may be scheduled while its
+// predecessor in the stream (or graph) is still draining; pdl_wait() — the first thing such a kernel
+// does — blocks until the predecessor has completed and its writes are visible.  Hides most of the
+// ~2 us node-to-node launch latency of the short kernels between the library convolutions.  A no-op
+// in a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// process-wide switch (capi.cu: raftk_set_pdl); initial value from RAFTK_PDL (default on)
+int& pdl_flag();
+static inline bool pdl_enabled() { return pdl_flag() != 0; }
+
+template <typename... KArgs, typename... Args>
+static inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // Streaming 128-bit store / load: the volume is written once and read much later,
 // the lookup output is consumed by a different kernel — neither wants L1 residency.
