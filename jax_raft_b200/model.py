@@ -765,6 +765,9 @@ class _GraphRunner:
 
     def __init__(self, model: RAFT, P, shape, device, num_flow_updates: int):
         self.device = device
+        # the captured kernels read the prepared weights and use the model's side streams: keep both alive
+        # for as long as the graph can be replayed, even if the caller drops the model
+        self._model, self._params = model, P
         self.image1 = torch.zeros(shape, dtype=torch.float32, device=device)
         self.image2 = torch.zeros(shape, dtype=torch.float32, device=device)
         with torch.cuda.device(device), torch.no_grad():
