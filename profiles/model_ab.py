@@ -2,7 +2,7 @@
 (the library's convolution engines are chosen once per shape per process, so variants share them wherever
 their convolutions coincide), replayed alternately with an L2 flush in between.
 
-    python profiles/model_ab.py split_motion_conv=False split_motion_conv=True
+    [BATCH=8] python profiles/model_ab.py concurrent=False concurrent=True
 """
 import os
 import sys
@@ -15,7 +15,7 @@ from bench import ITERS, synthetic_pairs  # noqa: E402
 
 dev = torch.device("cuda", 0)
 variants = sys.argv[1:] or ["", "split_motion_conv=False"]
-img1, img2 = synthetic_pairs(1, seed=1)
+img1, img2 = synthetic_pairs(int(os.environ.get("BATCH", "1")), seed=1)
 i1, i2 = torch.from_numpy(img1).to(dev), torch.from_numpy(img2).to(dev)
 _, variables = J.raft_large(seed=0)
 graphs = []
