@@ -94,5 +94,24 @@ for b in (1, 16):
         lines.append(f"| `{name}` | " + " | ".join(vals) + " |")
     lines.append("")
 
+# ---- f1 (lookup fused with convcorr1) ----
+rep = os.path.join(GO, f"{tag}_f1_b1.ncu-rep")
+raw_path = os.path.join(OUT, f"{tag}_f1_b1_raw.csv")
+if os.path.exists(rep):
+    with open(raw_path, "w") as f:
+        f.write(subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout)
+if os.path.exists(raw_path):
+    rows = list(csv.reader(open(raw_path)))
+    hdr, units, r = rows[0], rows[1], rows[-1]
+    more = ["smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio"]
+    lines += [f"## `ncu --set full`, f1 `lookup_conv_kernel<4>` at batch 1 (`{tag}_f1_b1_raw.csv`; `profiles/lookup_conv_time.py 1`)\n",
+              "| metric | value |", "|---|---|"]
+    for w in WANT + more:
+        if w in hdr:
+            lines.append(f"| `{w}` | {r[hdr.index(w)]} {units[hdr.index(w)]} |")
+    lines.append("")
+
 open(os.path.join(OUT, f"{tag}_summary.md"), "w").write("\n".join(lines) + "\n")
 print("\n".join(lines))
