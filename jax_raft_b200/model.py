@@ -538,6 +538,13 @@ class RAFT:
     def init(self, seed: int = 0) -> Tree:
         return init_variables(self.config, seed)
 
+    def invalidate(self) -> None:
+        """Forget prepared weights and captured graphs.  ``prepare`` and the graph cache key on the identity
+        of the ``variables`` tree, so call this after changing a tree's arrays IN PLACE (a new tree object
+        needs nothing)."""
+        self._prepared.clear()
+        self._graphs.clear()
+
     def prepare(self, variables: Tree, device) -> Dict[str, _ConvP]:
         key = (id(variables), str(device))
         if key not in self._prepared:

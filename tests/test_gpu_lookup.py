@@ -112,3 +112,37 @@ def test_grid_sample_standalone(cuda, lib, c):
     grid[0, 0, :4] = [[-1.0, 0.0], [w - 1.0, h - 1.0], [w - 0.5, 2.0], [1e6, -1e6]]
     got = J.grid_sample(torch.from_numpy(img).to(cuda), torch.from_numpy(grid).to(cuda)).cpu().numpy()
     _assert_bit_exact(got, O.grid_sample(img, grid))
+
+
+def test_programmatic_dependent_launch_switch(cuda, lib):
+    """raftk_set_pdl: the lookup launched behind another kernel with and without programmatic stream
+    serialization gives the same bits, eagerly and from a captured graph; the call returns the old setting."""
+    b, h, w, r = 1, 24, 40, 4
+    gen = torch.Generator(device=cuda).manual_seed(2)
+    q = b * h * w
+    pyr = [torch.randn((q, h >> l, w >> l, 1), device=cuda, generator=gen) for l in range(4)]
+    base = J.make_coords_grid(b, h, w, device=cuda)
+    noise = (torch.rand((b, h, w, 2), device=cuda, generator=gen) - 0.5) * 12
+    cb = J.CorrBlock(4, r)
+    prev = lib.raftk_set_pdl(1)
+    try:
+        outs = {}
+        for on in (0, 1):
+            assert lib.raftk_set_pdl(on) in (0, 1)
+            coords = base + noise          # produced by the kernel right before the lookup
+            eager = cb.index_pyramid(pyr, coords)
+            g = torch.cuda.CUDAGraph()
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                with torch.cuda.graph(g, stream=s):
+                    c2 = base + noise
+                    captured = cb.index_pyramid(pyr, c2)
+            g.replay()
+            torch.cuda.synchronize()
+            assert torch.equal(eager, captured)
+            outs[on] = eager
+        assert torch.equal(outs[0], outs[1])
+        assert lib.raftk_set_pdl(0) == 1 and lib.raftk_set_pdl(1) == 0
+    finally:
+        lib.raftk_set_pdl(prev)

@@ -49,6 +49,15 @@ def test_factories_keep_reference_signature():
         J.raft_large(corr_block=J.CorrBlock(4, 3))  # out_channels must match the motion encoder
     with pytest.raises(NotImplementedError):
         model.apply(variables, np.zeros((1, 64, 64, 3), np.float32), np.zeros((1, 64, 64, 3), np.float32), train=True)
+    # host-side options (not in the reference): scheduling / fusion switches, all consistent with each other
+    assert model.fused_update and model.concurrent and not model.fused_lookup_conv
+    plain, _ = J.raft_large(fused_update=False, fused_lookup_conv=True)
+    assert not plain.concurrent and not plain.fused_lookup_conv  # both need the fused update cell
+    fp32, _ = J.raft_large(precision="fp32", fused_lookup_conv=True)
+    assert not fp32.fused_lookup_conv                           # the fused kernel multiplies in TF32
+    model._prepared["x"] = model._graphs["y"] = object()
+    model.invalidate()
+    assert not model._prepared and not model._graphs
 
 
 def test_corr_block_asserts_like_reference_and_has_no_cpu_fallback():
