@@ -172,6 +172,20 @@ int raftk_corr_lookup_conv1x1(const float* const* levels, int num_levels, const 
                               const float* bias, float* out, int Q, int h, int w, int radius, int N, int relu,
                               void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Next row f2: MaskPredictor's last 1x1 convolution (model.py:394-400, with its 0.25
+ * factor folded into weight and bias) fused with raftk_convex_upsample, so the 576-channel mask is
+ * never written:  mask[p, ch] = sum_c W[ch, c] * m[p, c] + bias[ch]  (TF32 product), then the convex
+ * combination of model.py:85-98.
+ *   m       device, (B*h*w, K) float32 (the 3x3 convolution + ReLU before it), 16-byte aligned;
+ *           K a multiple of 32, K <= 256 (else RAFTK_ERR_UNSUPPORTED)
+ *   weight  device, (576, K) float32, rows in PASS order: row g*144 + k*16 + t holds the filter of mask
+ *           channel k*64 + 16*g + t  (g = 0..3, k = 0..8, t = 0..15);  bias (576) in the same order
+ *   flow    device, (B, h, w, 2);   out  device, (B, 8h, 8w, 2)
+ * ---------------------------------------------------------------------------------- */
+int raftk_mask_upsample(const float* m, const float* weight, const float* bias, const float* flow, float* out, int B,
+                        int h, int w, int K, void* stream);
+
 /* Host-model glue, not a hot-path row: in place y = act(x + bias[c]) on an NHWC conv output
  * (npix, c); act 0 none, 1 relu, 2 sigmoid, 3 tanh.  Used by jax_raft_b200/model.py after the
  * library convolutions (ConvNormActivation / ConvGRU / FlowHead epilogues, model.py:120-159,

@@ -6,12 +6,13 @@ raises if ``lib/libraftk.so`` has not been built (there is no CPU or eager fallb
 """
 
 from .corr import AltCorrBlock, CorrBlock
-from .functional import grid_sample, make_coords_grid, resize_with_aligned_corners, upsample_flow
+from .functional import (grid_sample, make_coords_grid, mask_upsample, pack_mask_predictor, resize_with_aligned_corners,
+                         upsample_flow)
 from .model import (RAFT, RAFT_LARGE, RAFT_SMALL, RaftConfig, init_variables, raft_large, raft_small,
                     torch_state_dict_from_variables, variables_from_torch_state_dict)
 
 __all__ = [
-    "RAFT", "raft_large", "raft_small", "CorrBlock", "AltCorrBlock", "upsample_flow", "make_coords_grid", "grid_sample", "resize_with_aligned_corners",
+    "RAFT", "raft_large", "raft_small", "CorrBlock", "AltCorrBlock", "upsample_flow", "mask_upsample", "pack_mask_predictor", "make_coords_grid", "grid_sample", "resize_with_aligned_corners",
     "RaftConfig", "RAFT_LARGE", "RAFT_SMALL", "init_variables", "variables_from_torch_state_dict",
     "torch_state_dict_from_variables",
 ]

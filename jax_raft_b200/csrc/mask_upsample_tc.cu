@@ -1,0 +1,284 @@
+// MaskPredictor's last 1x1 convolution (256 -> 576, with the 0.25 factor folded
+// into its weights; model.py:394-400) fused with the convex 8x upsampler (model.py:85-98), so the
+// 576-channel mask (16.2 MB per 440x1024 pair and iteration) is never written to memory:
+//
+//   mask[p, k*64 + s] = sum_c W[k*64 + s, c] * m[p, c] + bias[k*64 + s]        (TF32 product)
+//   out[b, 8y+fy, 8x+fx, :] = sum_k softmax_k(mask[p, k, s]) * 8*flow[b, y+dy, x+dx, :],  s = fy*8 + fx
+//
+// One CTA = 128 coarse pixels (UMMA M = 128, cta_group::1; accumulator row = TMEM lane = pixel).  The 576
+// output channels are produced in four passes of 144 columns: pass g holds, for the 16 sub-pixels
+// s in [16g, 16g+16), all nine neighbour planes k (column k*16 + s - 16g), so the softmax over k of a
+// sub-pixel is complete inside one pass.  The host permutes the weight rows and the bias into that order.
+//   warp 4   TMA producer: the A tile (128 pixels x K floats, K <= 256, 8 K-blocks, resident) once, then
+//            the weights, one (pass, K-block) slab of 144 rows x 128 B per stage of a 4-stage ring;
+//   warp 5   one thread issues tcgen05.mma.kind::tf32 (K = 8 each) into one of two TMEM accumulators
+//            (columns 0 and 256), so the MMAs of pass g+1 run under the epilogue of pass g;
+//   warps 0-3 epilogue, thread = pixel: two sweeps of tcgen05.ld.32x32b.x16 over the nine planes (max, then
+//            exp / sum / convex combination, the arithmetic of convex_upsample.cu), two 64-byte output
+//            row segments per pass.
+// Status: DESIGN.md §4.7.
+
+#include <cuda.h>
+
+#include <cstring>
+
+#include "raftk_common.cuh"
+#include "tc_ptx.cuh"
+
+namespace raftk {
+namespace mu {
+
+using namespace raftk::ptx;
+
+constexpr int TM = 128;             // pixels per CTA
+constexpr int NP = 144;             // columns per pass: 9 planes x 16 sub-pixels
+constexpr int PASSES = 4;
+constexpr int STAGES = 4;
+constexpr int A_BLOCK_BYTES = TM * 128;   // 16 KB: 128 rows x 32 floats
+constexpr int B_STAGE_BYTES = NP * 128;   // 18 KB: 144 rows x 32 floats
+constexpr int NUM_THREADS = 6 * 32;
+constexpr int SMEM_LIMIT = 232448;
+
+struct Params {
+  const float* bias;  // [576], pass order
+  const float* flow;  // (B, h, w, 2)
+  float* out;         // (B, 8h, 8w, 2)
+  int B, h, w, K;
+  long long Q;
+};
+
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const int KB = p.K / 32;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + KB * A_BLOCK_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + STAGES * B_STAGE_BYTES);
+  uint64_t* a_full = bars;               // [1]
+  uint64_t* b_full = bars + 1;           // [STAGES]
+  uint64_t* b_empty = b_full + STAGES;   // [STAGES]
+  uint64_t* acc_full = b_empty + STAGES; // [2]
+  uint64_t* acc_empty = acc_full + 2;    // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  float* smem_bias = reinterpret_cast<float*>(bars + 16);  // [576]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long q0 = (long long)blockIdx.x * TM;
+
+  if (warp == 4 && lane == 0) {
+    mbar_init(a_full, 1);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 5) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  for (int i = threadIdx.x; i < PASSES * NP; i += NUM_THREADS) smem_bias[i] = __ldg(p.bias + i);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      mbar_expect_tx(a_full, (uint32_t)(KB * A_BLOCK_BYTES));  // rows past Q are zero-filled and still counted
+      for (int kb = 0; kb < KB; ++kb) tma_load_2d(&tmA, a_full, smem_a + kb * A_BLOCK_BYTES, kb * 32, (int)q0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int g = 0; g < PASSES; ++g)
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&b_empty[stage], phase ^ 1);
+          mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);
+          tma_load_2d(&tmW, &b_full[stage], smem_b + stage * B_STAGE_BYTES, kb * 32, g * NP);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      // kind::tf32, D = f32, A = B = tf32, K-major, N = 144, M = 128
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NP >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+      mbar_wait(a_full, 0);
+      tc_fence_after();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int g = 0; g < PASSES; ++g) {
+        const int buf = g & 1;
+        mbar_wait(&acc_empty[buf], ((g >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)buf * 256;
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&b_full[stage], phase);
+          tc_fence_after();
+          const uint32_t as = smem_u32(smem_a + kb * A_BLOCK_BYTES);
+          const uint32_t bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
+#pragma unroll
+          for (int k8 = 0; k8 < 4; ++k8)
+            tc_mma_tf32(tmem_d, umma_desc(as + 32 * k8), umma_desc(bs + 32 * k8), idesc, (kb | k8) != 0);
+          tc_commit(&b_empty[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        tc_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    // ===================== epilogue: thread = pixel =====================
+    const long long pix = q0 + 32 * warp + lane;
+    const bool valid = pix < p.Q;
+    const int x = valid ? (int)(pix % p.w) : 0;
+    const int y = valid ? (int)((pix / p.w) % p.h) : 0;
+    const int b = valid ? (int)(pix / ((long long)p.w * p.h)) : 0;
+    // 8 * flow of the nine neighbours, zero outside the image (SAME padding, model.py:91-92)
+    float fxk[9], fyk[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const int yy = y + k / 3 - 1, xx = x + k % 3 - 1;
+      float2 f = make_float2(0.0f, 0.0f);
+      if (valid && (unsigned)yy < (unsigned)p.h && (unsigned)xx < (unsigned)p.w)
+        f = __ldg(reinterpret_cast<const float2*>(p.flow) + ((long long)b * p.h + yy) * p.w + xx);
+      fxk[k] = 8.0f * f.x;
+      fyk[k] = 8.0f * f.y;
+    }
+    const long long W8 = 8LL * p.w;
+    for (int g = 0; g < PASSES; ++g) {
+      const int buf = g & 1;
+      mbar_wait(&acc_full[buf], (g >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * 256;
+      const float* sb = smem_bias + g * NP;
+      float mx[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) mx[i] = -INFINITY;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        float v[16];
+        tmem_ld_32x16(taddr + k * 16, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) mx[i] = fmaxf(mx[i], v[i] + sb[k * 16 + i]);
+      }
+      float s[16], ax[16], ay[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) s[i] = ax[i] = ay[i] = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        float v[16];
+        tmem_ld_32x16(taddr + k * 16, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float e = __expf((v[i] + sb[k * 16 + i]) - mx[i]);
+          s[i] += e;
+          ax[i] = fmaf(e, fxk[k], ax[i]);
+          ay[i] = fmaf(e, fyk[k], ay[i]);
+        }
+      }
+      // both sweeps have read the accumulator: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      if (valid) {
+        // sub-pixel 16g + i -> (fy, fx) = (2g + i / 8, i % 8): two output rows of 8 pixels x 2 channels
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float* orow = p.out + (((long long)b * 8 * p.h + 8 * y + 2 * g + half) * W8 + 8 * x) * 2;
+#pragma unroll
+          for (int j = 0; j < 8; j += 2) {
+            const int i0 = 8 * half + j;
+            const float r0 = 1.0f / s[i0], r1 = 1.0f / s[i0 + 1];
+            st_na_f4(orow + 2 * j, make_float4(ax[i0] * r0, ay[i0] * r0, ax[i0 + 1] * r1, ay[i0 + 1] * r1));
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
+}  // namespace mu
+}  // namespace raftk
+
+extern "C" int raftk_mask_upsample(const float* m, const float* weight, const float* bias, const float* flow, float* out,
+                                   int B, int h, int w, int K, void* stream) {
+  using namespace raftk;
+  using namespace raftk::mu;
+  if (B < 0 || h <= 0 || w <= 0 || K <= 0) return RAFTK_ERR_SHAPE;
+  if (K % 32 || K > 256) return RAFTK_ERR_UNSUPPORTED;
+  if (B == 0) return RAFTK_OK;
+  if (!m || !weight || !bias || !flow || !out) return RAFTK_ERR_NULL;
+  if (((uintptr_t)m & 15) || ((uintptr_t)weight & 15) || ((uintptr_t)bias & 3) || ((uintptr_t)flow & 7) || ((uintptr_t)out & 15))
+    return RAFTK_ERR_ALIGN;
+  const long long Q = (long long)B * h * w;
+  if (Q > 0x7fffffffLL - TM) return RAFTK_ERR_SHAPE;
+  EncodeTiledFn encode = get_encode_fn();
+  if (!encode) return RAFTK_ERR_UNSUPPORTED;
+  CUtensorMap tmA, tmW;
+  {
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Q};
+    const cuuint64_t strides[1] = {(cuuint64_t)K * 4};
+    const cuuint32_t box[2] = {32, TM};
+    const cuuint32_t estr[2] = {1, 1};
+    if (encode(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(m), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return RAFTK_ERR_UNSUPPORTED;
+  }
+  {
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)(PASSES * NP)};
+    const cuuint64_t strides[1] = {(cuuint64_t)K * 4};
+    const cuuint32_t box[2] = {32, NP};
+    const cuuint32_t estr[2] = {1, 1};
+    if (encode(&tmW, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(weight), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return RAFTK_ERR_UNSUPPORTED;
+  }
+  Params p{};
+  p.bias = bias;
+  p.flow = flow;
+  p.out = out;
+  p.B = B;
+  p.h = h;
+  p.w = w;
+  p.K = K;
+  p.Q = Q;
+  const size_t smem = 1024 + (size_t)(K / 32) * A_BLOCK_BYTES + (size_t)STAGES * B_STAGE_BYTES + 128 + PASSES * NP * 4;
+  if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
+  cudaError_t e = cudaFuncSetAttribute(mask_upsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  const long long blocks = (Q + TM - 1) / TM;
+  mask_upsample_kernel<<<(unsigned)blocks, NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmW, p);
+  return launch_status();
+}

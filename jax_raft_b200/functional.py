@@ -93,3 +93,40 @@ def upsample_flow(flow: torch.Tensor, up_mask: Optional[torch.Tensor] = None, fa
     _lib.check("raftk_convex_upsample", rc)
     _lib.count_launch(1)
     return out
+
+
+def pack_mask_predictor(weight: torch.Tensor, bias: torch.Tensor):
+    """Filters (576, K[, 1, 1]) and bias (576) of MaskPredictor's last convolution (model.py:394-400, any
+    constant factor already folded in) -> the pass order ``raftk_mask_upsample`` reads: row
+    ``g*144 + k*16 + t`` is mask channel ``k*64 + 16*g + t``."""
+    n = weight.shape[0]
+    assert n == 576 and bias.shape == (576,)
+    w = weight.reshape(9, 4, 16, -1).permute(1, 0, 2, 3).reshape(576, -1)  # (k, g, t) -> (g, k, t)
+    b = bias.reshape(9, 4, 16).permute(1, 0, 2).reshape(576)
+    return w.to(torch.float32).contiguous(), b.to(torch.float32).contiguous()
+
+
+def mask_upsample(flow: torch.Tensor, features: torch.Tensor, packed_weight: torch.Tensor, packed_bias: torch.Tensor,
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``upsample_flow(flow, conv1x1(features) + bias)`` in one kernel (TF32 product),
+    with ``features`` (B, h, w, K) the mask predictor's hidden activation and the weights from
+    ``pack_mask_predictor``.  Not in the reference's API."""
+    flow = _check_cuda_f32("flow", flow)
+    features = _check_cuda_f32("features", features)
+    w = _check_cuda_f32("packed_weight", packed_weight)
+    bvec = _check_cuda_f32("packed_bias", packed_bias)
+    b, h, wd, c = flow.shape
+    assert c == 2 and features.shape[:3] == (b, h, wd)
+    k = features.shape[3]
+    assert w.shape == (576, k) and bvec.shape == (576,)
+    if out is None:
+        out = torch.empty((b, 8 * h, 8 * wd, 2), dtype=torch.float32, device=flow.device)
+    else:
+        assert out.shape == (b, 8 * h, 8 * wd, 2) and out.dtype == torch.float32 and out.is_contiguous()
+    lib = _lib.load()
+    with torch.cuda.device(flow.device):
+        rc = lib.raftk_mask_upsample(features.data_ptr(), w.data_ptr(), bvec.data_ptr(), flow.data_ptr(), out.data_ptr(), b, h, wd,
+                                     k, _lib.current_stream_ptr(flow.device))
+    _lib.check("raftk_mask_upsample", rc)
+    _lib.count_launch(1)
+    return out
