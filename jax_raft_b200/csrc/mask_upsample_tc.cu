@@ -9,13 +9,14 @@
 // output channels are produced in four passes of 144 columns: pass g holds, for the 16 sub-pixels
 // s in [16g, 16g+16), all nine neighbour planes k (column k*16 + s - 16g), so the softmax over k of a
 // sub-pixel is complete inside one pass.  The host permutes the weight rows and the bias into that order.
-//   warp 4   TMA producer: the A tile (128 pixels x K floats, K <= 256, 8 K-blocks, resident) once, then
+//   warp 8   TMA producer: the A tile (128 pixels x K floats, K <= 256, 8 K-blocks, resident) once, then
 //            the weights, one (pass, K-block) slab of 144 rows x 128 B per stage of a 4-stage ring;
-//   warp 5   one thread issues tcgen05.mma.kind::tf32 (K = 8 each) into one of two TMEM accumulators
+//   warp 9   one thread issues tcgen05.mma.kind::tf32 (K = 8 each) into one of two TMEM accumulators
 //            (columns 0 and 256), so the MMAs of pass g+1 run under the epilogue of pass g;
-//   warps 0-3 epilogue, thread = pixel: two sweeps of tcgen05.ld.32x32b.x16 over the nine planes (max, then
-//            exp / sum / convex combination, the arithmetic of convex_upsample.cu), two 64-byte output
-//            row segments per pass.
+//   warps 0-7 epilogue, thread = (pixel, 8 of the pass's 16 sub-pixels; TMEM lane quarter = warp % 4): nine
+//            tcgen05.ld.32x32b.x8 bring all planes of its sub-pixels into registers, the accumulator is
+//            released at once, then max / exp / sum / convex combination (the arithmetic of
+//            convex_upsample.cu) and one 64-byte output row segment per pass.
 // Status: DESIGN.md §4.7.
 
 #include <cuda.h>
@@ -36,7 +37,8 @@ constexpr int PASSES = 4;
 constexpr int STAGES = 4;
 constexpr int A_BLOCK_BYTES = TM * 128;   // 16 KB: 128 rows x 32 floats
 constexpr int B_STAGE_BYTES = NP * 128;   // 18 KB: 144 rows x 32 floats
-constexpr int NUM_THREADS = 6 * 32;
+constexpr int EPI_WARPS = 8;         // two per TMEM lane quarter: sub-pixels 0-7 and 8-15 of a pass
+constexpr int NUM_THREADS = (EPI_WARPS + 2) * 32;
 constexpr int SMEM_LIMIT = 232448;
 
 struct Params {
@@ -47,14 +49,11 @@ struct Params {
   long long Q;
 };
 
-__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, float* v) {
+__device__ __forceinline__ void tmem_ld_32x8(uint32_t taddr, float* v) {
   uint32_t* r = reinterpret_cast<uint32_t*>(v);
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
 }
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -76,7 +75,7 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long q0 = (long long)blockIdx.x * TM;
 
-  if (warp == 4 && lane == 0) {
+  if (warp == EPI_WARPS && lane == 0) {
     mbar_init(a_full, 1);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&b_full[s], 1);
@@ -84,11 +83,11 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[i], EPI_WARPS);  // one arrival per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 5) {
+  if (warp == EPI_WARPS + 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
@@ -98,7 +97,7 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 4) {
+  if (warp == EPI_WARPS) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       mbar_expect_tx(a_full, (uint32_t)(KB * A_BLOCK_BYTES));  // rows past Q are zero-filled and still counted
@@ -116,7 +115,7 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           }
         }
     }
-  } else if (warp == 5) {
+  } else if (warp == EPI_WARPS + 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       // kind::tf32, D = f32, A = B = tf32, K-major, N = 144, M = 128
@@ -148,8 +147,9 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       }
     }
   } else {
-    // ===================== epilogue: thread = pixel =====================
-    const long long pix = q0 + 32 * warp + lane;
+    // ===================== epilogue: thread = (pixel, half of the pass's 16 sub-pixels) =====================
+    const int quarter = warp & 3, half = warp >> 2;
+    const long long pix = q0 + 32 * quarter + lane;
     const bool valid = pix < p.Q;
     const int x = valid ? (int)(pix % p.w) : 0;
     const int y = valid ? (int)((pix / p.w) % p.h) : 0;
@@ -170,58 +170,50 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const int buf = g & 1;
       mbar_wait(&acc_full[buf], (g >> 1) & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * 256;
-      const float* sb = smem_bias + g * NP;
-      float mx[16];
+      const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * 256 + 8 * half;
+      const float* sb = smem_bias + g * NP + 8 * half;
+      // all nine planes of this thread's eight sub-pixels: 72 registers, one wait
+      float v[9][8];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) mx[i] = -INFINITY;
-#pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        float v[16];
-        tmem_ld_32x16(taddr + k * 16, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 16; ++i) mx[i] = fmaxf(mx[i], v[i] + sb[k * 16 + i]);
-      }
-      float s[16], ax[16], ay[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) s[i] = ax[i] = ay[i] = 0.0f;
-#pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        float v[16];
-        tmem_ld_32x16(taddr + k * 16, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const float e = __expf((v[i] + sb[k * 16 + i]) - mx[i]);
-          s[i] += e;
-          ax[i] = fmaf(e, fxk[k], ax[i]);
-          ay[i] = fmaf(e, fyk[k], ay[i]);
-        }
-      }
-      // both sweeps have read the accumulator: hand it back to the MMA warp
+      for (int k = 0; k < 9; ++k) tmem_ld_32x8(taddr + k * 16, v[k]);
+      tmem_ld_wait();
+      // the accumulator has been read: hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
-      if (valid) {
-        // sub-pixel 16g + i -> (fy, fx) = (2g + i / 8, i % 8): two output rows of 8 pixels x 2 channels
+      float o[16];
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          float* orow = p.out + (((long long)b * 8 * p.h + 8 * y + 2 * g + half) * W8 + 8 * x) * 2;
+      for (int i = 0; i < 8; ++i) {
+        float mx = -INFINITY;
 #pragma unroll
-          for (int j = 0; j < 8; j += 2) {
-            const int i0 = 8 * half + j;
-            const float r0 = 1.0f / s[i0], r1 = 1.0f / s[i0 + 1];
-            st_na_f4(orow + 2 * j, make_float4(ax[i0] * r0, ay[i0] * r0, ax[i0 + 1] * r1, ay[i0 + 1] * r1));
-          }
+        for (int k = 0; k < 9; ++k) {
+          v[k][i] += sb[k * 16 + i];
+          mx = fmaxf(mx, v[k][i]);
         }
+        float s = 0.0f, ax = 0.0f, ay = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+          const float e = __expf(v[k][i] - mx);
+          s += e;
+          ax = fmaf(e, fxk[k], ax);
+          ay = fmaf(e, fyk[k], ay);
+        }
+        const float inv = 1.0f / s;
+        o[2 * i] = ax * inv;
+        o[2 * i + 1] = ay * inv;
+      }
+      if (valid) {
+        // sub-pixels 16g + 8*half + i -> output row fy = 2g + half, fx = i: 8 pixels x 2 channels = 64 bytes
+        float* orow = p.out + (((long long)b * 8 * p.h + 8 * y + 2 * g + half) * W8 + 8 * x) * 2;
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) st_na_f4(orow + j, make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]));
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == EPI_WARPS + 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
   }

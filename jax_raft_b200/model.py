@@ -28,7 +28,7 @@ import torch.nn.functional as F
 
 from . import _lib
 from .corr import CorrBlock
-from .functional import make_coords_grid, upsample_flow
+from .functional import make_coords_grid, mask_upsample, pack_mask_predictor, upsample_flow
 
 Tree = Dict[str, Any]
 
@@ -507,7 +507,7 @@ class RAFT:
     """Counterpart of the reference's ``RAFT`` module (model.py:513-605) + ``UpdateCell`` (484-510)."""
 
     def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32", fused_update: bool = True,
-                 concurrent: bool = True, fused_lookup_conv: bool = False):
+                 concurrent: bool = True, fused_lookup_conv: bool = False, fused_mask_upsample: bool = True):
         assert precision in ("tf32", "fp32")
         # fused_update: UpdateCell's element-wise work through csrc/gru_glue.cu (same arithmetic as the
         # unfused path, which stays for configurations whose channel counts are odd and for A/B tests)
@@ -528,6 +528,11 @@ class RAFT:
         self.precision = precision
         # fused_lookup_conv: the lookup and MotionEncoder.convcorr1 as one kernel (raftk_corr_lookup_conv1x1,
         # SURVEY §8 f1).  Off by default: measured slower than the two kernels it replaces.
+        # fused_mask_upsample: MaskPredictor's last 1x1 convolution inside the upsampler (raftk_mask_upsample,
+        # SURVEY §8 f2): parity at batch 1, 40 % faster than convolution + upsampler from batch 4 up
+        hidden_mask = 256  # MaskPredictor's hidden size (model.py:383)
+        self.fused_mask_upsample = (fused_mask_upsample and self.fused_update and precision == "tf32"
+                                    and config.use_mask_predictor and hidden_mask % 32 == 0 and hidden_mask <= 256)
         self.fused_lookup_conv = (fused_lookup_conv and self.fused_update and precision == "tf32"
                                   and getattr(self.corr_block, "fused_conv_supported", False)
                                   and config.motion_encoder_corr_layers[0] % 16 == 0 and config.motion_encoder_corr_layers[0] <= 256)
@@ -689,9 +694,23 @@ class RAFT:
         for gi, gpad in enumerate(cfg.recurrent_block_padding, start=1):
             state.gru(P, f"update_block/recurrent_block/convgru{gi}", gpad)
 
+        fuse_mask = self.fused_mask_upsample
+        if fuse_mask:  # the last 1x1 convolution inside the upsampler (TF32 product)
+            pm = P["mask_predictor/conv"]
+            packed = getattr(pm, "_packed", None)
+            if packed is None:
+                packed = pm._packed = pack_mask_predictor(pm.w, pm.b)
+
         def mask_branch():  # model.py:377-400; the upsampler adds the last bias itself
             m = _cna(P, "mask_predictor/convrelu", state.h, None)
+            if fuse_mask:
+                return m.permute(0, 2, 3, 1)  # the hidden activation: the fused kernel applies the last convolution
             return _cl(F.conv2d(m, P["mask_predictor/conv"].w, None)).permute(0, 2, 3, 1)
+
+        def upsample(mask_or_features):
+            if fuse_mask:
+                return mask_upsample(state.flow, mask_or_features, packed[0], packed[1], out=out)
+            return upsample_flow(state.flow, mask_or_features, mask_bias=P["mask_predictor/conv"].b, out=out)
 
         up_mask = None
         if cfg.use_mask_predictor and sa is not None:
@@ -704,12 +723,12 @@ class RAFT:
         if not cfg.use_mask_predictor:
             return upsample_flow(flow=state.flow), None
         if sa is None:
-            return upsample_flow(state.flow, mask_branch(), mask_bias=P["mask_predictor/conv"].b, out=out), None
+            return upsample(mask_branch()), None
 
         def deferred_upsample():
             sa.wait_stream(main)
             with torch.cuda.stream(sa):
-                upsample_flow(state.flow, up_mask, mask_bias=P["mask_predictor/conv"].b, out=out)
+                upsample(up_mask)
 
         return out, deferred_upsample
 
@@ -805,6 +824,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
     fused_update = kwargs.pop("fused_update", True)
     concurrent = kwargs.pop("concurrent", True)
     fused_lookup_conv = kwargs.pop("fused_lookup_conv", False)
+    fused_mask_upsample = kwargs.pop("fused_mask_upsample", True)
     if kwargs:
         raise TypeError(
             f"unsupported keyword(s) {sorted(kwargs)}: this build replaces the correlation block "
@@ -814,7 +834,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
         from .checkpoint import load_msgpack
 
         model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent,
-                     fused_lookup_conv=fused_lookup_conv)
+                     fused_lookup_conv=fused_lookup_conv, fused_mask_upsample=fused_mask_upsample)
         return model, load_msgpack(pretrained)
     if pretrained:
         # model.py:684-689 downloads a msgpack from GitHub; this environment has no network.
@@ -822,7 +842,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
             "pretrained=True needs network access (model.py:17-21, 684-689); pass pretrained='<file>.msgpack' "
             "(a local copy of the released checkpoint) or use variables_from_torch_state_dict(torch.load(path))")
     model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent,
-                     fused_lookup_conv=fused_lookup_conv)
+                     fused_lookup_conv=fused_lookup_conv, fused_mask_upsample=fused_mask_upsample)
     return model, model.init(seed)
 
 

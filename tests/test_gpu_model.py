@@ -102,6 +102,23 @@ def test_fused_lookup_conv_in_the_model(cuda, lib, golden, name):
     assert _epe(flows[-1], ref_flows[-1]) <= 0.01
 
 
+def test_fused_mask_upsample_in_the_model(cuda, lib, golden):
+    """SURVEY §8(f) f2 end to end (the default path): the flow with raftk_mask_upsample stays within the
+    0.01 px bar of the CPU reference, and close to the convolution + upsampler composition."""
+    g = golden("e2e_raft_large")
+    img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
+    net, ref_flows = _torchvision_cpu("raft_large", img1, img2, iters)
+    variables = J.variables_from_torch_state_dict(net.state_dict())
+    fused, _ = J.raft_large()
+    plain, _ = J.raft_large(fused_mask_upsample=False)
+    assert fused.fused_mask_upsample and not plain.fused_mask_upsample
+    a = fused.apply(variables, img1, img2, num_flow_updates=iters).cpu().numpy()
+    b = plain.apply(variables, img1, img2, num_flow_updates=iters).cpu().numpy()
+    for i in (0, iters - 1):
+        assert _epe(a[i], ref_flows[i]) <= 0.01
+    assert _epe(a[-1], b[-1]) <= 5e-3
+
+
 def test_alt_corr_block_drops_in(cuda, lib, golden):
     g = golden("e2e_raft_large")
     img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
