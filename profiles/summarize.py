@@ -28,7 +28,7 @@ if os.path.exists(fn):
         k = re.sub(r"<.*", "", k)[:70]
         agg[k][0] += 1
         agg[k][1] += v
-    mine = sum(t for k, (n, t) in agg.items() if "raftk" in k or "tc::" in k)
+    mine = sum(t for k, (n, t) in agg.items() if any(t in k for t in ("raftk", "tc::", "mu::", "lc::")))
     lines += [f"## One raft_large 440x1024 x32-iteration step, eager, every launch (`{os.path.basename(fn)}`)\n",
               f"`ncu --metrics gpu__time_duration.sum --clock-control none` (cold-cache, serialised: compare shares).",
               f"{len(recs)} launches, {tot / 1e6:.2f} ms summed; raftk kernels: {mine / 1e3:.1f} us = {100 * mine / tot:.1f} % of the step.\n",
@@ -36,7 +36,7 @@ if os.path.exists(fn):
     for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:18]:
         lines.append(f"| {100 * t / tot:.1f} % | {n} | {t / n / 1e3:.1f} | `{k}` |")
     for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        if ("raftk" in k or "tc::" in k) and all(k not in l for l in lines):
+        if (any(t in k for t in ("raftk", "tc::", "mu::", "lc::"))) and all(k not in l for l in lines):
             lines.append(f"| {100 * t / tot:.2f} % | {n} | {t / n / 1e3:.1f} | `{k}` |")
     with open(os.path.join(OUT, f"{tag}_step_launches.csv"), "w") as f:
         f.writelines(rows)
@@ -58,7 +58,7 @@ if os.path.exists(fn):
         f.write("kernel,launches,total_ns,mean_ns,share\n")
         for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
             f.write(f'"{k}",{n},{t:.0f},{t / n:.0f},{t / tot:.5f}\n')
-    mine = sum(t for k, (n, t) in agg.items() if "raftk" in k or "tc::" in k)
+    mine = sum(t for k, (n, t) in agg.items() if any(t in k for t in ("raftk", "tc::", "mu::", "lc::")))
     lines += [f"## `python bench.py --steps 2 --warmup 3 --skip-cpu-baseline --micro-batch 0` under the same ncu pass "
               f"(`{tag}_bench_launches_summary.csv`)\n",
               f"{len(recs)} launches over the whole command (eager warm-ups, graph capture, replays, event-timed pass); "
