@@ -1,7 +1,7 @@
 // Host-model glue, NOT a row of SURVEY.md §8: InstanceNorm (+ ReLU) on an NHWC tensor, the norm
 // layer of the feature encoder (model.py:706-707: nn.InstanceNorm(epsilon=1e-5, no scale / bias);
 // applied inside ConvNormActivation, model.py:146-158).  torch runs it as two batch-norm kernels
-// (~100 us per call at 220x512x64); this is one statistics pass, a tiny finalise and one normalise pass.
+// (~100 us per call at 220x512x64); this is one statistics pass and one normalise pass.
 //
 //   y[n, p, c] = (x[n, p, c] - mean[n, c]) / sqrt(var[n, c] + eps),  var = E[x^2] - mean^2 (biased),
 // statistics accumulated in float64 so the one-pass variance does not cancel.
@@ -65,24 +65,14 @@ instnorm_stats_kernel(const float* __restrict__ x, double* __restrict__ stats, i
   }
 }
 
-// (sum, sum of squares) in float64 -> (mean, 1/sqrt(var + eps)) in float32, in place: slot i keeps
-// its 16 bytes, the first 8 now hold the float pair.
-__global__ void __launch_bounds__(256) instnorm_finalize_kernel(double* __restrict__ stats, int count, int npix, float eps) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= count) return;
-  const double mean = stats[2 * i] / npix;
-  const double var = stats[2 * i + 1] / npix - mean * mean;
-  const float2 mi = make_float2((float)mean, rsqrtf((float)var + eps));
-  *reinterpret_cast<float2*>(stats + 2 * i) = mi;
-}
-
 // Thread (tr, tc) owns channel group tc (4 channels) of pixel rows tr, tr + rows, ... of one slice of
-// image n: its four (mean, 1/std) pairs are read once, and the loop has no index arithmetic beyond adds.
+// image n: it turns its four (sum, sum of squares) float64 pairs into (mean, 1/std) once — no separate
+// finalise launch — and the loop has no index arithmetic beyond adds.
 // RES: out = relu(residual + y) on top (the residual block's tail, model.py:183-184).
 template <bool RELU, bool RES>
 __global__ void __launch_bounds__(256)
 instnorm_apply_kernel(float* __restrict__ x, const float* __restrict__ residual, const double* __restrict__ stats, int npix,
-                      int c4, int slices) {
+                      int c4, int slices, float eps) {
   const int n = blockIdx.y, slice = blockIdx.x;
   const int rows = 256 / c4;
   const int tc = threadIdx.x % c4, tr = threadIdx.x / c4;
@@ -92,7 +82,11 @@ instnorm_apply_kernel(float* __restrict__ x, const float* __restrict__ residual,
   const double* st = stats + ((size_t)n * c4 * 4 + tc * 4) * 2;
   float2 mi[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) mi[i] = __ldg(reinterpret_cast<const float2*>(st + 2 * i));
+  for (int i = 0; i < 4; ++i) {
+    const double mean = st[2 * i] / npix;
+    const double var = st[2 * i + 1] / npix - mean * mean;
+    mi[i] = make_float2((float)mean, rsqrtf((float)var + eps));
+  }
   const int p0 = (int)((long long)npix * slice / slices), p1 = (int)((long long)npix * (slice + 1) / slices);
   auto norm = [&](float4 v, size_t off) {
     v.x = (v.x - mi[0].x) * mi[0].y;
@@ -149,18 +143,17 @@ static int instance_norm_impl(float* x, const float* residual, int n, int npix, 
   instnorm_stats_kernel<<<dim3(slices, n), 256, 0, s>>>(x, static_cast<double*>(scratch), npix, c / 4, slices);
   int aslices = (RAFTK_SM_COUNT * 16 + n - 1) / n;
   if (aslices > npix) aslices = npix;
-  instnorm_finalize_kernel<<<(n * c + 255) / 256, 256, 0, s>>>(static_cast<double*>(scratch), n * c, npix, eps);
   const double* st = static_cast<const double*>(scratch);
   const dim3 grid(aslices, n);
   if (residual) {
     if (relu)
-      instnorm_apply_kernel<true, true><<<grid, 256, 0, s>>>(x, residual, st, npix, c / 4, aslices);
+      instnorm_apply_kernel<true, true><<<grid, 256, 0, s>>>(x, residual, st, npix, c / 4, aslices, eps);
     else
-      instnorm_apply_kernel<false, true><<<grid, 256, 0, s>>>(x, residual, st, npix, c / 4, aslices);
+      instnorm_apply_kernel<false, true><<<grid, 256, 0, s>>>(x, residual, st, npix, c / 4, aslices, eps);
   } else if (relu) {
-    instnorm_apply_kernel<true, false><<<grid, 256, 0, s>>>(x, nullptr, st, npix, c / 4, aslices);
+    instnorm_apply_kernel<true, false><<<grid, 256, 0, s>>>(x, nullptr, st, npix, c / 4, aslices, eps);
   } else {
-    instnorm_apply_kernel<false, false><<<grid, 256, 0, s>>>(x, nullptr, st, npix, c / 4, aslices);
+    instnorm_apply_kernel<false, false><<<grid, 256, 0, s>>>(x, nullptr, st, npix, c / 4, aslices, eps);
   }
   return launch_status();
 }

@@ -358,7 +358,7 @@ def _instance_norm_(y, relu: bool, eps: float = 1e-5, residual=None):
             rc = lib.raftk_instance_norm_residual_nhwc(y.data_ptr(), residual.data_ptr(), n, h * w, c, eps, 1 if relu else 0,
                                                        scratch.data_ptr(), nbytes, _lib.current_stream_ptr(y.device))
     _lib.check("raftk_instance_norm_nhwc", rc)
-    _lib.count_launch(3)
+    _lib.count_launch(2)
     return y
 
 
