@@ -269,14 +269,24 @@ class _TimedCorr:
         self.build_events.append((a, b))
         return out
 
+    @property
+    def fused_conv_supported(self):
+        return getattr(self.inner, "fused_conv_supported", False)
+
+    def index_pyramid_update(self, pyr, *args):  # the lookup with the coordinate update folded in (same kernel)
+        return self._timed_lookup(lambda: self.inner.index_pyramid_update(pyr, *args))
+
     def index_pyramid(self, pyr, coords):
+        return self._timed_lookup(lambda: self.inner.index_pyramid(pyr, coords))
+
+    def _timed_lookup(self, call):
         e0, e1 = self._pair()  # nothing between them: what an event pair costs by itself at this point of the graph
         e0.record()
         e1.record()
         self.empty_events.append((e0, e1))
         a, b = self._pair()
         a.record()
-        out = self.inner.index_pyramid(pyr, coords)
+        out = call()
         b.record()
         self.lookup_events.append((a, b))
         return out

@@ -110,6 +110,15 @@ int raftk_corr_pyramid_simt(const float* fmap1, const float* fmap2, float* const
  * ---------------------------------------------------------------------------------- */
 int raftk_corr_lookup(const float* const* levels, int num_levels, const float* coords,
                       float* out, int Q, int h, int w, int radius, void* stream);
+/* The same lookup preceded, per query, by the tail of the PREVIOUS UpdateCell iteration (model.py:504-506):
+ *   coords1 += delta_pre + bias (in place);  flow = coords1 - coords0;  out = lookup(coords1)
+ * so that the update costs no launch of its own.  delta_pre has pixel stride ld_delta (>= 2, even), bias is
+ * the flow head's two bias values (device), flow_pitched (may be NULL) a second copy of the flow with pixel
+ * stride ld_flow.  num_levels == 4 and radius in {3, 4} only (else RAFTK_ERR_UNSUPPORTED: call
+ * raftk_flow_update and raftk_corr_lookup). */
+int raftk_corr_lookup_update(const float* const* levels, int num_levels, const float* delta_pre, int ld_delta,
+                             const float* bias, const float* coords0, float* coords1, float* flow, float* flow_pitched,
+                             int ld_flow, float* out, int Q, int h, int w, int radius, void* stream);
 
 /* Stand-alone form of the reference's grid_sample helper, model.py:24-34 (bilinear sample of an
  * NHWC image at absolute pixel coordinates, each corner zero outside; jax map_coordinates order=1

@@ -61,6 +61,8 @@ SIGNATURES = {
     "raftk_corr_lookup_conv1x1": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_set_pdl": (c_int, [c_int]),
     "raftk_mask_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "raftk_corr_lookup_update": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                         c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_convex_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
 }
 

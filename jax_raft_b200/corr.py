@@ -124,6 +124,34 @@ class CorrBlock:
         return out
 
 
+    def index_pyramid_update(self, corr_pyramid: Sequence[torch.Tensor], coords0: torch.Tensor, coords1: torch.Tensor,
+                             delta_pre: torch.Tensor, bias: torch.Tensor, flow: torch.Tensor,
+                             flow_pitched: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``coords1 += delta_pre[..., :2] + bias[:2]`` (in place), ``flow = coords1 - coords0`` (also into the
+        first two channels of ``flow_pitched``), then ``index_pyramid(corr_pyramid, coords1)`` — UpdateCell's
+        tail (model.py:504-506) folded into the next iteration's lookup.  ``delta_pre`` is (B, h, w, C >= 2)
+        NHWC memory; 4 levels and radius 3 or 4 only."""
+        assert self.fused_conv_supported
+        b, hq, wq, _ = coords1.shape
+        q = b * hq * wq
+        assert coords1.is_contiguous() and coords0.is_contiguous() and flow.is_contiguous() and coords1.dtype == torch.float32
+        lv0 = corr_pyramid[0]
+        assert lv0.shape[0] == q
+        h, w = int(lv0.shape[1]), int(lv0.shape[2])
+        levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(corr_pyramid)]
+        ld_delta = delta_pre.numel() // max(q, 1)
+        out = torch.empty((b, hq, wq, self.out_channels), dtype=torch.float32, device=coords1.device)
+        lib = _lib.load()
+        with torch.cuda.device(coords1.device):
+            rc = lib.raftk_corr_lookup_update(
+                _lib.ptr_array(levels), self.num_levels, delta_pre.data_ptr(), ld_delta, bias.data_ptr(), coords0.data_ptr(),
+                coords1.data_ptr(), flow.data_ptr(), None if flow_pitched is None else flow_pitched.data_ptr(),
+                0 if flow_pitched is None else flow_pitched.numel() // max(q, 1), out.data_ptr(), q, h, w, self.radius,
+                _lib.current_stream_ptr(coords1.device))
+        _lib.check("raftk_corr_lookup_update", rc)
+        _lib.count_launch(1)
+        return out
+
     # -- SURVEY.md §8(f) f1: lookup fused with the 1x1 convolution that consumes it ----------------
     @property
     def fused_conv_supported(self) -> bool:

@@ -32,6 +32,15 @@ struct LookupParams {
   int Q;
   int L;
   int r;
+  // fused coordinate update (raftk_corr_lookup_update; fast path only): coords_rw += delta + dbias first
+  const float* delta;   // NULL: plain lookup
+  int ld_delta;
+  const float* dbias;
+  const float* coords0;
+  float* coords_rw;
+  float* flow;
+  float* flow_pitched;  // may be NULL
+  int ld_flow;
 };
 
 // Generic staging: per level the (2r+2)^2 footprint as [l][2r+2][2r+2], zeros outside the level.
@@ -185,12 +194,32 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
   // Software pipeline over this warp's queries: the chunk loads of query q + nwarps are issued before
   // the taps of query q are evaluated, so DRAM latency and tap arithmetic overlap inside one warp
   // (at batch 1 every warp has only one or two queries and no other warp's phase to hide behind).
+  // the query's coordinates; with the fused update (UpdateCell's tail of the PREVIOUS iteration,
+  // model.py:504-506) they are first advanced, coords1 += delta + bias, and written back with the flow
+  auto load_coords = [&](int qq, float& x, float& y) {
+    if (p.delta == nullptr) {
+      x = __ldg(p.coords + 2 * (size_t)qq);
+      y = __ldg(p.coords + 2 * (size_t)qq + 1);
+      return;
+    }
+    const float2 c1 = *reinterpret_cast<const float2*>(p.coords_rw + 2 * (size_t)qq);
+    const float2 d = *reinterpret_cast<const float2*>(p.delta + (size_t)qq * p.ld_delta);
+    const float2 b = __ldg(reinterpret_cast<const float2*>(p.dbias));
+    const float2 c0 = __ldg(reinterpret_cast<const float2*>(p.coords0) + qq);
+    x = __fadd_rn(c1.x, __fadd_rn(d.x, b.x));
+    y = __fadd_rn(c1.y, __fadd_rn(d.y, b.y));
+    if (lane == 0) {
+      const float2 f = make_float2(__fadd_rn(x, -c0.x), __fadd_rn(y, -c0.y));
+      *reinterpret_cast<float2*>(p.coords_rw + 2 * (size_t)qq) = make_float2(x, y);
+      *reinterpret_cast<float2*>(p.flow + 2 * (size_t)qq) = f;
+      if (p.flow_pitched) *reinterpret_cast<float2*>(p.flow_pitched + (size_t)qq * p.ld_flow) = f;
+    }
+  };
   int q = blockIdx.x * kFastWarps + warp;
   float cx = 0.0f, cy = 0.0f;
   Chunks cur;
   if (q < p.Q) {
-    cx = __ldg(p.coords + 2 * (size_t)q);
-    cy = __ldg(p.coords + 2 * (size_t)q + 1);
+    load_coords(q, cx, cy);
     if (near(cx, cy)) fetch(q, cx, cy, cur);
   }
   while (q < p.Q) {
@@ -207,8 +236,7 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
     // ---- prefetch the next query of this warp ----
     float ncx = 0.0f, ncy = 0.0f;
     if (qn < p.Q) {
-      ncx = __ldg(p.coords + 2 * (size_t)qn);
-      ncy = __ldg(p.coords + 2 * (size_t)qn + 1);
+      load_coords(qn, ncx, ncy);
       if (near(ncx, ncy)) fetch(qn, ncx, ncy, cur);
     }
     if (!fast) {
@@ -254,8 +282,19 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
 
 }  // namespace raftk
 
-extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, const float* coords,
-                                 float* out, int Q, int h, int w, int radius, void* stream) {
+struct raftk_lookup_update_args {
+  const float* delta;
+  int ld_delta;
+  const float* bias;
+  const float* coords0;
+  float* coords1;
+  float* flow;
+  float* flow_pitched;
+  int ld_flow;
+};
+
+static int corr_lookup_launch(const float* const* levels, int num_levels, const float* coords, float* out, int Q, int h,
+                              int w, int radius, const raftk_lookup_update_args* upd, void* stream) {
   using namespace raftk;
   if (Q < 0 || h <= 0 || w <= 0 || radius < 0 || num_levels < 1 || num_levels > RAFTK_MAX_LEVELS)
     return RAFTK_ERR_SHAPE;
@@ -277,6 +316,17 @@ extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, con
   p.r = radius;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const bool fast = (radius == 3 || radius == 4) && num_levels == 4;
+  if (upd) {
+    if (!fast) return RAFTK_ERR_UNSUPPORTED;
+    p.delta = upd->delta;
+    p.ld_delta = upd->ld_delta;
+    p.dbias = upd->bias;
+    p.coords0 = upd->coords0;
+    p.coords_rw = upd->coords1;
+    p.flow = upd->flow;
+    p.flow_pitched = upd->flow_pitched;
+    p.ld_flow = upd->ld_flow;
+  }
   for (int l = 0; l < num_levels; ++l)
     p.aligned[l] = (p.lw[l] % 4 == 0) && (((uintptr_t)p.level[l] & 15) == 0);
   if (fast) {
@@ -302,4 +352,24 @@ extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, con
   else
     corr_lookup_kernel<0><<<blocks, kLookupWarps * 32, smem, s>>>(p);
   return launch_status();
+}
+
+extern "C" int raftk_corr_lookup(const float* const* levels, int num_levels, const float* coords,
+                                 float* out, int Q, int h, int w, int radius, void* stream) {
+  return corr_lookup_launch(levels, num_levels, coords, out, Q, h, w, radius, nullptr, stream);
+}
+
+extern "C" int raftk_corr_lookup_update(const float* const* levels, int num_levels, const float* delta_pre, int ld_delta,
+                                        const float* bias, const float* coords0, float* coords1, float* flow,
+                                        float* flow_pitched, int ld_flow, float* out, int Q, int h, int w, int radius,
+                                        void* stream) {
+  if (Q > 0) {
+    if (!delta_pre || !bias || !coords0 || !coords1 || !flow) return RAFTK_ERR_NULL;
+    if (ld_delta < 2 || ld_delta % 2 || (flow_pitched && (ld_flow < 2 || ld_flow % 2))) return RAFTK_ERR_SHAPE;
+    if (((uintptr_t)delta_pre | (uintptr_t)bias | (uintptr_t)coords0 | (uintptr_t)coords1 | (uintptr_t)flow |
+         (uintptr_t)flow_pitched) & 7)
+      return RAFTK_ERR_ALIGN;
+  }
+  const raftk_lookup_update_args upd{delta_pre, ld_delta, bias, coords0, coords1, flow, flow_pitched, ld_flow};
+  return corr_lookup_launch(levels, num_levels, coords1, out, Q, h, w, radius, &upd, stream);
 }

@@ -445,6 +445,7 @@ class _RecurrentState:
         self.flow = torch.zeros((n, h, w, 2), dtype=torch.float32, device=hidden.device)  # coords1 - coords0
         # the same flow in channels 0-1 of an 8-channel tensor: input of the zero-padded 7x7 flow convolution
         self.flow8 = torch.empty((n, 8, h, w), **opts).zero_()
+        self.pending_delta = None  # (flow-head output, its parameters) of an iteration whose update is still to run
         self.A[:, :hid] = hidden
         self.h.copy_(hidden)
         self.A[:, hid:hid + ctx] = context
@@ -507,7 +508,8 @@ class RAFT:
     """Counterpart of the reference's ``RAFT`` module (model.py:513-605) + ``UpdateCell`` (484-510)."""
 
     def __init__(self, config: RaftConfig, corr_block=None, precision: str = "tf32", fused_update: bool = True,
-                 concurrent: bool = True, fused_lookup_conv: bool = False, fused_mask_upsample: bool = True):
+                 concurrent: bool = True, fused_lookup_conv: bool = False, fused_mask_upsample: bool = True,
+                 fused_flow_update: bool = True):
         assert precision in ("tf32", "fp32")
         # fused_update: UpdateCell's element-wise work through csrc/gru_glue.cu (same arithmetic as the
         # unfused path, which stays for configurations whose channel counts are odd and for A/B tests)
@@ -528,6 +530,11 @@ class RAFT:
         self.precision = precision
         # fused_lookup_conv: the lookup and MotionEncoder.convcorr1 as one kernel (raftk_corr_lookup_conv1x1,
         # SURVEY §8 f1).  Off by default: measured slower than the two kernels it replaces.
+        # fused_flow_update: UpdateCell's tail (coords1 += delta; flow = coords1 - coords0) inside the next
+        # iteration's lookup kernel (raftk_corr_lookup_update) instead of a launch of its own
+        self.fused_flow_update = (fused_flow_update and self.concurrent and not fused_lookup_conv
+                                  and hasattr(self.corr_block, "index_pyramid_update")
+                                  and getattr(self.corr_block, "fused_conv_supported", False))
         # fused_mask_upsample: MaskPredictor's last 1x1 convolution inside the upsampler (raftk_mask_upsample,
         # SURVEY §8 f2): parity at batch 1, 40 % faster than convolution + upsampler from batch 4 up
         hidden_mask = 256  # MaskPredictor's hidden size (model.py:383)
@@ -612,6 +619,9 @@ class RAFT:
                 else:
                     coords1, hidden_state, up = self._update_cell(P, corr_pyramid, coords0, coords1, hidden_state, context)
                 flows.append(up)
+            if state is not None and state.pending_delta is not None:  # the last iteration's coordinate update
+                state.update_flow(*state.pending_delta, coords0, coords1)
+                state.pending_delta = None
             if pending is not None:
                 pending()
             if sa is not None:  # the last mask predictor + upsampler
@@ -669,6 +679,11 @@ class RAFT:
             if packed is None:
                 packed = pc._packed = self.corr_block.pack_conv_weight(pc.w)
             corr = self.corr_block.index_pyramid_conv(corr_pyramid, coords1, packed, pc.b, relu=True).permute(0, 3, 1, 2)
+        elif state.pending_delta is not None:  # the previous iteration's coordinate update rides on this lookup
+            dp, pd = state.pending_delta
+            corr_features = self.corr_block.index_pyramid_update(corr_pyramid, coords0, coords1, dp, pd.b, state.flow,
+                                                                 state.flow8)
+            state.pending_delta = None
         else:
             corr_features = self.corr_block.index_pyramid(corr_pyramid, coords1)  # (B, h, w, C) NHWC
         if sb is not None:  # forked after the lookup, which is HBM-bound and wants the machine to itself
@@ -719,7 +734,13 @@ class RAFT:
                 up_mask = mask_branch()
         d = _conv(state.h, P["update_block/flow_head/conv1"], padding=1, act="relu")
         p = P["update_block/flow_head/conv2/padded"]
-        state.update_flow(_cl(F.conv2d(d, p.w, None, padding=1)), p, coords0, coords1)
+        delta_pre = _cl(F.conv2d(d, p.w, None, padding=1))
+        if self.fused_flow_update and sa is not None and cfg.use_mask_predictor:
+            # coords1 += delta, flow = coords1 - coords0 happen inside the NEXT iteration's lookup kernel
+            # (raftk_corr_lookup_update); everything that reads the new flow is issued after that lookup
+            state.pending_delta = (delta_pre, p)
+        else:
+            state.update_flow(delta_pre, p, coords0, coords1)
         if not cfg.use_mask_predictor:
             return upsample_flow(flow=state.flow), None
         if sa is None:
@@ -825,6 +846,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
     concurrent = kwargs.pop("concurrent", True)
     fused_lookup_conv = kwargs.pop("fused_lookup_conv", False)
     fused_mask_upsample = kwargs.pop("fused_mask_upsample", True)
+    fused_flow_update = kwargs.pop("fused_flow_update", True)
     if kwargs:
         raise TypeError(
             f"unsupported keyword(s) {sorted(kwargs)}: this build replaces the correlation block "
@@ -834,7 +856,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
         from .checkpoint import load_msgpack
 
         model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent,
-                     fused_lookup_conv=fused_lookup_conv, fused_mask_upsample=fused_mask_upsample)
+                     fused_lookup_conv=fused_lookup_conv, fused_mask_upsample=fused_mask_upsample, fused_flow_update=fused_flow_update)
         return model, load_msgpack(pretrained)
     if pretrained:
         # model.py:684-689 downloads a msgpack from GitHub; this environment has no network.
@@ -842,7 +864,7 @@ def _raft(cfg: RaftConfig, *, pretrained: bool = False, seed: int = 0, **kwargs)
             "pretrained=True needs network access (model.py:17-21, 684-689); pass pretrained='<file>.msgpack' "
             "(a local copy of the released checkpoint) or use variables_from_torch_state_dict(torch.load(path))")
     model = RAFT(cfg, corr_block=corr_block, precision=precision, fused_update=fused_update, concurrent=concurrent,
-                     fused_lookup_conv=fused_lookup_conv, fused_mask_upsample=fused_mask_upsample)
+                     fused_lookup_conv=fused_lookup_conv, fused_mask_upsample=fused_mask_upsample, fused_flow_update=fused_flow_update)
     return model, model.init(seed)
 
 

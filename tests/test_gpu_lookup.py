@@ -146,3 +146,30 @@ def test_programmatic_dependent_launch_switch(cuda, lib):
         assert lib.raftk_set_pdl(0) == 1 and lib.raftk_set_pdl(1) == 0
     finally:
         lib.raftk_set_pdl(prev)
+
+
+@pytest.mark.parametrize("shape,r", [((1, 16, 24), 4), ((2, 19, 21), 3), ((1, 55, 128), 4)])
+def test_lookup_with_fused_coordinate_update(cuda, lib, shape, r):
+    """raftk_corr_lookup_update == raftk_flow_update followed by raftk_corr_lookup, bit for bit, including the
+    in-place coordinates, the flow and its pitched copy."""
+    b, h, w = shape
+    gen = torch.Generator(device=cuda).manual_seed(h + r)
+    q = b * h * w
+    pyr = [torch.randn((q, h >> l, w >> l, 1), device=cuda, generator=gen) for l in range(4)]
+    c0 = J.make_coords_grid(b, h, w, device=cuda)
+    c1 = c0 + (torch.rand((b, h, w, 2), device=cuda, generator=gen) - 0.5) * 10
+    c1[0, 1, 1] = 3.0e6  # a far query takes the slow path
+    delta = torch.randn((b, h, w, 8), device=cuda, generator=gen)  # padded flow-head output
+    bias = torch.randn((8,), device=cuda, generator=gen)
+    cb = J.CorrBlock(4, r)
+    ref_c1 = c1 + (delta[..., :2] + bias[:2])
+    ref_flow = ref_c1 - c0
+    ref_out = cb.index_pyramid(pyr, ref_c1)
+    flow = torch.full((b, h, w, 2), 9.0, device=cuda)
+    flow8 = torch.zeros((b, h, w, 8), device=cuda)
+    got_c1 = c1.clone()
+    out = cb.index_pyramid_update(pyr, c0, got_c1, delta, bias, flow, flow8)
+    assert torch.equal(got_c1, ref_c1) and torch.equal(flow, ref_flow)
+    assert torch.equal(flow8[..., :2], ref_flow) and not flow8[..., 2:].any()
+    assert torch.equal(out, ref_out)
+    assert not J.CorrBlock(3, 4).fused_conv_supported  # other configurations: flow_update + lookup

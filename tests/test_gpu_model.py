@@ -119,6 +119,21 @@ def test_fused_mask_upsample_in_the_model(cuda, lib, golden):
     assert _epe(a[-1], b[-1]) <= 5e-3
 
 
+def test_fused_flow_update_gives_identical_flows(cuda, lib, golden):
+    """The coordinate update folded into the next lookup kernel is the same float32 arithmetic: the flows are
+    bit-identical to the ones with a separate raftk_flow_update launch (full-precision convolutions, so that
+    the library makes the same choices in both models)."""
+    g = golden("e2e_raft_large")
+    img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
+    a_model, variables = J.raft_large(precision="fp32", fused_mask_upsample=False, seed=2)
+    b_model, _ = J.raft_large(precision="fp32", fused_mask_upsample=False, fused_flow_update=False)
+    assert a_model.fused_flow_update and not b_model.fused_flow_update
+    for graph in (False, True):
+        a = a_model.apply(variables, img1, img2, num_flow_updates=iters, use_cuda_graph=graph)
+        b = b_model.apply(variables, img1, img2, num_flow_updates=iters, use_cuda_graph=graph)
+        assert torch.equal(a, b)
+
+
 def test_alt_corr_block_drops_in(cuda, lib, golden):
     g = golden("e2e_raft_large")
     img1, img2, iters = g["image1"], g["image2"], int(g["iters"])
