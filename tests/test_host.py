@@ -183,3 +183,31 @@ def test_jax_ffi_layer_is_gated_not_faked():
     assert defined == named and len(defined) == 6
     for fn in re.findall(r"\b(raftk_\w+)\(", cc):
         assert fn in open(os.path.join(os.path.dirname(os.path.dirname(J.__file__)), "include", "raftk.h")).read(), fn
+
+
+def test_weight_packing_for_the_fused_kernels():
+    """Host-side layouts of the f1 / f2 kernels (pure index work, checked without a GPU):
+    pack_mask_predictor: row g*144 + k*16 + t <- mask channel k*64 + 16*g + t;
+    CorrBlock.pack_conv_weight: column l*KL + t <- channel l*(2r+1)^2 + t, zero padding up to KL."""
+    import torch
+
+    w = torch.arange(576 * 5, dtype=torch.float32).reshape(576, 5, 1, 1)
+    b = torch.arange(576, dtype=torch.float32)
+    pw, pb = J.pack_mask_predictor(w, b)
+    assert pw.shape == (576, 5) and pb.shape == (576,)
+    for g, k, t in ((0, 0, 0), (1, 3, 7), (3, 8, 15), (2, 5, 0)):
+        ch = k * 64 + 16 * g + t
+        row = g * 144 + k * 16 + t
+        assert pb[row] == ch and torch.equal(pw[row], w[ch, :, 0, 0])
+    assert sorted(pb.tolist()) == list(range(576))  # a permutation
+
+    for r, kl in ((4, 96), (3, 64)):
+        cb = J.CorrBlock(4, r)
+        ss = (2 * r + 1) ** 2
+        wc = torch.arange(32 * 4 * ss, dtype=torch.float32).reshape(32, 4 * ss, 1, 1) + 1
+        packed = cb.pack_conv_weight(wc)
+        assert packed.shape == (32, 4 * kl)
+        for l in range(4):
+            assert torch.equal(packed[:, l * kl:l * kl + ss], wc[:, l * ss:(l + 1) * ss, 0, 0])
+            assert not packed[:, l * kl + ss:(l + 1) * kl].any()
+    assert not J.CorrBlock(3, 4).fused_conv_supported and not J.CorrBlock(4, 2).fused_conv_supported
