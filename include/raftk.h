@@ -8,7 +8,9 @@
  * are float32, dense, row-major, in the reference's layouts (NHWC, coords = (x, y)).
  *
  * Return value: 0 on success; a negative RAFTK_ERR_* for a rejected call (nothing was
- * launched); a positive value is the cudaError_t of a failed launch.  Nothing throws
+ * launched); a positive value is a cudaError_t seen at the launch — the launch's own failure,
+ * or an earlier error of the context that nobody had collected (it is peeked, not cleared, so
+ * the host framework still sees it).  Nothing throws
  * across this boundary.  A jax.ffi handler maps non-zero to an XLA_FFI_Error
  * (see INTEGRATION.md).
  *
@@ -119,6 +121,41 @@ int raftk_corr_lookup(const float* const* levels, int num_levels, const float* c
 int raftk_corr_lookup_update(const float* const* levels, int num_levels, const float* delta_pre, int ld_delta,
                              const float* bias, const float* coords0, float* coords1, float* flow, float* flow_pitched,
                              int ld_flow, float* out, int Q, int h, int w, int radius, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Tiled pyramid (the product path since round 2).  The reference passes the pyramid from
+ * build_pyramid to index_pyramid as an opaque value (contract model.py:530-539; stored at
+ * :491, :601), so its layout in memory is this library's to choose.  Level l of one query
+ * pixel is stored as tiles of 4 x 4 float32 — one 64-byte L2 fetch granule each:
+ *
+ *   tiles_y = ceil((h>>l) / 4),  tiles_x = 2 * ceil((w>>l) / 8)
+ *   slab floats = tiles_y * tiles_x * 16                   (raftk_pyramid_tiled_slab_floats)
+ *   cell (y, x) of query slab q = levels[l] + q * slab + ((y>>2) * tiles_x + (x>>2)) * 16 + (y&3)*4 + (x&3)
+ *   cells outside the level (y >= h>>l or x >= w>>l) hold 0.
+ *
+ * so a (2r+2)^2 lookup footprint costs ~10.6 granules per level instead of ~15.6 in a
+ * row-major slab.  levels[l] must be 128-byte aligned.  Values, pooling bounds and lookup
+ * results are those of the row-major entry points above, bit for bit.
+ *
+ *   raftk_corr_pyramid_tiled          = raftk_corr_pyramid writing tiled slabs (same scratch)
+ *   raftk_corr_lookup_tiled(_update)  = raftk_corr_lookup(_update) reading them
+ *   raftk_pyramid_tile / _untile      convert (Q, h>>l, w>>l) row-major levels <-> tiled slabs
+ *                                     (for callers that bring a row-major pyramid, and for tests)
+ * ---------------------------------------------------------------------------------- */
+size_t raftk_pyramid_tiled_slab_floats(int h, int w, int level);
+int raftk_corr_pyramid_tiled(const float* fmap1, const float* fmap2, float* const* levels,
+                             int num_levels, int B, int nq, int h, int w, int D,
+                             void* scratch, size_t scratch_bytes, void* stream);
+int raftk_corr_lookup_tiled(const float* const* levels, int num_levels, const float* coords,
+                            float* out, int Q, int h, int w, int radius, void* stream);
+int raftk_corr_lookup_tiled_update(const float* const* levels, int num_levels, const float* delta_pre, int ld_delta,
+                                   const float* bias, const float* coords0, float* coords1, float* flow,
+                                   float* flow_pitched, int ld_flow, float* out, int Q, int h, int w, int radius,
+                                   void* stream);
+int raftk_pyramid_tile(const float* const* rowmajor, float* const* tiled, int num_levels, long long Q,
+                       int h, int w, void* stream);
+int raftk_pyramid_untile(const float* const* tiled, float* const* rowmajor, int num_levels, long long Q,
+                         int h, int w, void* stream);
 
 /* Stand-alone form of the reference's grid_sample helper, model.py:24-34 (bilinear sample of an
  * NHWC image at absolute pixel coordinates, each corner zero outside; jax map_coordinates order=1

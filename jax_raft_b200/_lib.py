@@ -63,6 +63,20 @@ SIGNATURES = {
     "raftk_mask_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_corr_lookup_update": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                          c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "raftk_pyramid_tiled_slab_floats": (c_size_t, [c_int, c_int, c_int]),
+    "raftk_corr_pyramid_tiled": (
+        c_int,
+        [c_void_p, c_void_p, _FloatPtrArray, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
+         c_size_t, c_void_p],
+    ),
+    "raftk_corr_lookup_tiled": (
+        c_int,
+        [_FloatPtrArray, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
+    ),
+    "raftk_corr_lookup_tiled_update": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                               c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "raftk_pyramid_tile": (c_int, [_FloatPtrArray, _FloatPtrArray, c_int, ctypes.c_longlong, c_int, c_int, c_void_p]),
+    "raftk_pyramid_untile": (c_int, [_FloatPtrArray, _FloatPtrArray, c_int, ctypes.c_longlong, c_int, c_int, c_void_p]),
     "raftk_convex_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
 }
 

@@ -57,26 +57,126 @@ def _check_fmaps(fmap1, fmap2, num_levels, query_rows):
     return fmap1, fmap2
 
 
-class CorrBlock:
-    """All-pairs correlation pyramid + radius-r window lookup (model.py:403-481)."""
+class TiledPyramid:
+    """The correlation pyramid in the library's tiled layout (``include/raftk.h``: 4 x 4-float tiles, one 64-byte
+    L2 fetch granule each).  The reference treats the pyramid as an opaque value handed from ``build_pyramid`` to
+    ``index_pyramid`` (model.py:530-539), so this is what :class:`CorrBlock` returns by default.
 
-    def __init__(self, num_levels: int = 4, radius: int = 4, kernel: str = "tc"):
+    ``levels[l]`` is a (Q, tiles_y, tiles_x, 4, 4) float32 tensor.  Indexing, iterating or ``dense()`` give the
+    reference's row-major levels (Q, h>>l, w>>l, 1) as copies (``raftk_pyramid_untile``), for inspection and tests.
+    """
+
+    def __init__(self, levels: List[torch.Tensor], q: int, h: int, w: int):
+        self.levels = levels
+        self.q, self.h, self.w = q, h, w
+        self._dense = None
+
+    @staticmethod
+    def level_shape(q: int, h: int, w: int, l: int):
+        lh, lw = h >> l, w >> l
+        return (q, (lh + 3) // 4, 2 * ((lw + 7) // 8), 4, 4)
+
+    @classmethod
+    def empty(cls, q: int, h: int, w: int, num_levels: int, device) -> "TiledPyramid":
+        lib = _lib.load()
+        levels = []
+        for l in range(num_levels):
+            shape = cls.level_shape(q, h, w, l)
+            assert shape[1] * shape[2] * 16 == lib.raftk_pyramid_tiled_slab_floats(h, w, l)
+            levels.append(torch.empty(shape, dtype=torch.float32, device=device))
+        return cls(levels, q, h, w)
+
+    @classmethod
+    def from_dense(cls, levels: Sequence[torch.Tensor]) -> "TiledPyramid":
+        """Row-major levels (Q, h>>l, w>>l[, 1]) -> tiled slabs (``raftk_pyramid_tile``)."""
+        levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(levels)]
+        q, h, w = int(levels[0].shape[0]), int(levels[0].shape[1]), int(levels[0].shape[2])
+        for l, t in enumerate(levels):
+            assert tuple(t.shape[:3]) == (q, h >> l, w >> l), "levels must be (Q, h>>l, w>>l[, 1])"
+        out = cls.empty(q, h, w, len(levels), levels[0].device)
+        lib = _lib.load()
+        with torch.cuda.device(levels[0].device):
+            rc = lib.raftk_pyramid_tile(_lib.ptr_array(levels), _lib.ptr_array(out.levels), len(levels), q, h, w,
+                                        _lib.current_stream_ptr(levels[0].device))
+        _lib.check("raftk_pyramid_tile", rc)
+        _lib.count_launch(len(levels))
+        return out
+
+    def dense(self) -> List[torch.Tensor]:
+        dev = self.levels[0].device
+        out = [torch.empty((self.q, self.h >> l, self.w >> l, 1), dtype=torch.float32, device=dev)
+               for l in range(len(self.levels))]
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            rc = lib.raftk_pyramid_untile(_lib.ptr_array(self.levels), _lib.ptr_array(out), len(out), self.q, self.h,
+                                          self.w, _lib.current_stream_ptr(dev))
+        _lib.check("raftk_pyramid_untile", rc)
+        _lib.count_launch(len(out))
+        return out
+
+    def _cached_dense(self):
+        if self._dense is None:
+            self._dense = self.dense()
+        return self._dense
+
+    def __len__(self):
+        return len(self.levels)
+
+    def __getitem__(self, i):
+        return self._cached_dense()[i]
+
+    def __iter__(self):
+        return iter(self._cached_dense())
+
+
+class CorrBlock:
+    """All-pairs correlation pyramid + radius-r window lookup (model.py:403-481).
+
+    ``layout="tiled"`` (default): ``build_pyramid`` returns a :class:`TiledPyramid` and ``index_pyramid`` reads it
+    with the tiled kernels; ``layout="rowmajor"`` keeps the reference's (B*nq, h>>l, w>>l, 1) tensors.  Either way
+    ``index_pyramid`` accepts both kinds (a list of row-major levels goes through the row-major kernels)."""
+
+    def __init__(self, num_levels: int = 4, radius: int = 4, kernel: str = "tc", layout: str = "tiled"):
         assert 1 <= num_levels <= _lib.MAX_LEVELS
         assert kernel in ("tc", "simt")
+        assert layout in ("tiled", "rowmajor")
         self.num_levels = num_levels
         self.radius = radius
         self.out_channels = num_levels * (2 * radius + 1) ** 2  # model.py:416
         self.kernel = kernel
+        self.layout = layout
 
     # -- model.py:418-446 ---------------------------------------------------------------
     def build_pyramid(self, fmap1: torch.Tensor, fmap2: torch.Tensor,
                       query_rows: Optional[Tuple[int, int]] = None) -> List[torch.Tensor]:
-        """Returns ``num_levels`` tensors (B*nq, h>>l, w>>l, 1).
+        """Returns the pyramid: ``num_levels`` levels of (B*nq, h>>l, w>>l, 1), as a :class:`TiledPyramid` or
+        (``layout="rowmajor"``) a list of tensors.
 
         ``query_rows=(y0, y1)`` builds only the volume rows of fmap1 rows [y0, y1): the
         row-sharded mode of SURVEY.md §8e (fmap2 must be the full, all-gathered map).
         """
         fmap1, fmap2 = _check_fmaps(fmap1, fmap2, self.num_levels, query_rows)
+        b, h, w, d = fmap2.shape
+        nq = fmap1.shape[1] * w
+        lib = _lib.load()
+        if self.layout == "tiled":
+            direct = self.kernel == "tc" and self.num_levels <= 4 and d % 64 == 0 and d <= 256
+            if not direct:  # configurations the tiled epilogue does not cover: row-major kernels, then convert
+                return TiledPyramid.from_dense(self._build_rowmajor(fmap1, fmap2))
+            pyr = TiledPyramid.empty(b * nq, h, w, self.num_levels, fmap1.device)
+            stream = _lib.current_stream_ptr(fmap1.device)
+            with torch.cuda.device(fmap1.device):
+                nbytes = lib.raftk_corr_pyramid_scratch_bytes(b, nq, h, w, d)
+                scratch = torch.empty((max(nbytes, 1),), dtype=torch.uint8, device=fmap1.device)
+                rc = lib.raftk_corr_pyramid_tiled(fmap1.data_ptr(), fmap2.data_ptr(), _lib.ptr_array(pyr.levels),
+                                                  self.num_levels, b, nq, h, w, d, scratch.data_ptr(), nbytes, stream)
+            _lib.check("raftk_corr_pyramid_tiled", rc)
+            _lib.count_launch(2)  # bf16 split + tcgen05 GEMM
+            return pyr
+        return self._build_rowmajor(fmap1, fmap2)
+
+    def _build_rowmajor(self, fmap1: torch.Tensor, fmap2: torch.Tensor) -> List[torch.Tensor]:
+        """fmap1 (B, rows, w, D): the query rows held by this call, already checked and sliced."""
         b, h, w, d = fmap2.shape
         nq = fmap1.shape[1] * w
         lib = _lib.load()
@@ -109,12 +209,21 @@ class CorrBlock:
         b, hq, wq, _ = coords.shape
         q = b * hq * wq
         assert len(corr_pyramid) == self.num_levels
+        out = torch.empty((b, hq, wq, self.out_channels), dtype=torch.float32, device=coords.device)
+        lib = _lib.load()
+        if isinstance(corr_pyramid, TiledPyramid):
+            assert corr_pyramid.q == q, "pyramid and coords disagree on the number of query pixels"
+            with torch.cuda.device(coords.device):
+                rc = lib.raftk_corr_lookup_tiled(_lib.ptr_array(corr_pyramid.levels), self.num_levels, coords.data_ptr(),
+                                                 out.data_ptr(), q, corr_pyramid.h, corr_pyramid.w, self.radius,
+                                                 _lib.current_stream_ptr(coords.device))
+            _lib.check("raftk_corr_lookup_tiled", rc)
+            _lib.count_launch(1)
+            return out
         lv0 = corr_pyramid[0]
         assert lv0.shape[0] == q, "pyramid and coords disagree on the number of query pixels"
         h, w = int(lv0.shape[1]), int(lv0.shape[2])
         levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(corr_pyramid)]
-        out = torch.empty((b, hq, wq, self.out_channels), dtype=torch.float32, device=coords.device)
-        lib = _lib.load()
         with torch.cuda.device(coords.device):
             rc = lib.raftk_corr_lookup(_lib.ptr_array(levels), self.num_levels, coords.data_ptr(), out.data_ptr(),
                                        q, h, w, self.radius, _lib.current_stream_ptr(coords.device))
@@ -135,20 +244,37 @@ class CorrBlock:
         b, hq, wq, _ = coords1.shape
         q = b * hq * wq
         assert coords1.is_contiguous() and coords0.is_contiguous() and flow.is_contiguous() and coords1.dtype == torch.float32
-        lv0 = corr_pyramid[0]
-        assert lv0.shape[0] == q
-        h, w = int(lv0.shape[1]), int(lv0.shape[2])
-        levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(corr_pyramid)]
-        ld_delta = delta_pre.numel() // max(q, 1)
+
+        def pixel_stride(name, t):
+            # dense NHWC memory, given either as (B, h, w, C) contiguous or as (B, C, h, w) channels_last; anything
+            # else (an NCHW-contiguous tensor, a slice) would hand the kernel wrong strides
+            assert t.dtype == torch.float32 and t.dim() == 4 and t.shape[0] == b, f"{name}: 4-D float32, batch {b}"
+            if tuple(t.shape[1:3]) == (hq, wq) and t.is_contiguous():
+                return int(t.shape[3])
+            if tuple(t.shape[2:]) == (hq, wq) and t.is_contiguous(memory_format=torch.channels_last):
+                return int(t.shape[1])
+            raise AssertionError(f"{name} must be dense NHWC memory: (B, h, w, C) contiguous or (B, C, h, w) channels_last")
+
+        ld_delta = pixel_stride("delta_pre", delta_pre)
+        ld_flow = 0 if flow_pitched is None else pixel_stride("flow_pitched", flow_pitched)
         out = torch.empty((b, hq, wq, self.out_channels), dtype=torch.float32, device=coords1.device)
         lib = _lib.load()
+        tiled = isinstance(corr_pyramid, TiledPyramid)
+        if tiled:
+            assert corr_pyramid.q == q
+            h, w, levels = corr_pyramid.h, corr_pyramid.w, corr_pyramid.levels
+            fn, name = lib.raftk_corr_lookup_tiled_update, "raftk_corr_lookup_tiled_update"
+        else:
+            lv0 = corr_pyramid[0]
+            assert lv0.shape[0] == q
+            h, w = int(lv0.shape[1]), int(lv0.shape[2])
+            levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(corr_pyramid)]
+            fn, name = lib.raftk_corr_lookup_update, "raftk_corr_lookup_update"
         with torch.cuda.device(coords1.device):
-            rc = lib.raftk_corr_lookup_update(
-                _lib.ptr_array(levels), self.num_levels, delta_pre.data_ptr(), ld_delta, bias.data_ptr(), coords0.data_ptr(),
-                coords1.data_ptr(), flow.data_ptr(), None if flow_pitched is None else flow_pitched.data_ptr(),
-                0 if flow_pitched is None else flow_pitched.numel() // max(q, 1), out.data_ptr(), q, h, w, self.radius,
-                _lib.current_stream_ptr(coords1.device))
-        _lib.check("raftk_corr_lookup_update", rc)
+            rc = fn(_lib.ptr_array(levels), self.num_levels, delta_pre.data_ptr(), ld_delta, bias.data_ptr(), coords0.data_ptr(),
+                    coords1.data_ptr(), flow.data_ptr(), None if flow_pitched is None else flow_pitched.data_ptr(),
+                    ld_flow, out.data_ptr(), q, h, w, self.radius, _lib.current_stream_ptr(coords1.device))
+        _lib.check(name, rc)
         _lib.count_launch(1)
         return out
 
@@ -180,6 +306,8 @@ class CorrBlock:
         b, hq, wq, _ = coords.shape
         q = b * hq * wq
         assert len(corr_pyramid) == self.num_levels
+        assert not isinstance(corr_pyramid, TiledPyramid), \
+            "raftk_corr_lookup_conv1x1 reads row-major levels: build the pyramid with CorrBlock(layout='rowmajor')"
         lv0 = corr_pyramid[0]
         assert lv0.shape[0] == q, "pyramid and coords disagree on the number of query pixels"
         h, w = int(lv0.shape[1]), int(lv0.shape[2])

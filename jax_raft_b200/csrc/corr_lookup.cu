@@ -336,11 +336,8 @@ static int corr_lookup_launch(const float* const* levels, int num_levels, const 
     // (measured: 8.5 us against 9.0 us with one); persistent beyond 8 blocks per SM
     int blocks = (Q + 2 * kFastWarps - 1) / (2 * kFastWarps);
     if (blocks > RAFTK_SM_COUNT * 8) blocks = RAFTK_SM_COUNT * 8;
-    if (radius == 4)
-      launch_pdl(corr_lookup_fast_kernel<4>, blocks, kFastWarps * 32, smem, s, p);
-    else
-      launch_pdl(corr_lookup_fast_kernel<3>, blocks, kFastWarps * 32, smem, s, p);
-    return launch_status();
+    if (radius == 4) return launch_pdl(corr_lookup_fast_kernel<4>, blocks, kFastWarps * 32, smem, s, p);
+    return launch_pdl(corr_lookup_fast_kernel<3>, blocks, kFastWarps * 32, smem, s, p);
   }
   const int FP = 2 * radius + 2;
   const size_t smem = (size_t)kLookupWarps * num_levels * FP * FP * sizeof(float);

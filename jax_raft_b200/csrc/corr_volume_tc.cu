@@ -44,6 +44,7 @@
 #include <cuda_bf16.h>
 
 #include "raftk_common.cuh"
+#include "pyramid_tiled.cuh"
 
 namespace raftk {
 
@@ -68,6 +69,8 @@ struct Params {
   float* level[4];
   int lh[4], lw[4];
   int vec_ok[4];  // level row pitch and base allow 16-byte stores
+  int ltx[4], lty[4];   // tiled layout: tiles per tile row / tile rows of each level
+  long long lslab[4];   // tiled layout: floats per query slab
   int L;          // levels written by this kernel (<= 4)
   int B, nq, h, w, D;
   int m_tiles, px_tiles, n_tiles;
@@ -343,12 +346,55 @@ __device__ __forceinline__ void pool_rows(const float* a, const float* b, float*
     out[i] = __fadd_rn(__fadd_rn(a[2 * i], a[2 * i + 1]), __fadd_rn(b[2 * i], b[2 * i + 1])) * 0.25f;
 }
 
+
+// ---- tiled-layout epilogue (pyramid_tiled.cuh) ----------------------------------------------
+__device__ __forceinline__ void tma_store_5d(const CUtensorMap* tm, const void* src, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+               : "memory");
+}
+
+// Stage 32 floats per lane (lane = query: two adjacent 4x4 tiles = 128 contiguous bytes of its slab) in the warp's
+// swizzled staging tile and send them as ONE bulk tensor store: tile pair `pair`, tile row `trow` of queries
+// [m_first, m_first + 32) of pair b.  The tensor map (32 floats, tile pairs, tile rows, query, pair) clips tile
+// pairs / tile rows / queries that do not exist.
+__device__ __forceinline__ void emit_pair(float* S, const float* v, const CUtensorMap* tm, int b, int m_first, int pair,
+                                          int trow, int lane) {
+  if (lane == 0) bulk_wait_read_all();  // the previous store may still be reading S
+  __syncwarp();
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    *reinterpret_cast<float4*>(S + lane * 32 + ((c ^ (lane & 7)) * 4)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+  fence_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_5d(tm, S, 0, pair, trow, m_first, b);
+    bulk_commit();
+  }
+}
+
+// 2x2 pooling of a 4x4 block stored row-major with pitch 4 -> its 2x2 result (pitch `op`), the reference's
+// order ((a+b)+(c+d))/4
+__device__ __forceinline__ void pool_tile(const float* t, float* out, int op) {
+#pragma unroll
+  for (int py = 0; py < 2; ++py)
+#pragma unroll
+    for (int px = 0; px < 2; ++px) {
+      const float* s = t + (2 * py) * 4 + 2 * px;
+      out[py * op + px] = __fadd_rn(__fadd_rn(s[0], s[1]), __fadd_rn(s[4], s[5])) * 0.25f;
+    }
+}
+
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per
 // 256-query tile: each CTA keeps its own 128 query rows of A and loads HALF of every target
 // patch (4 of its 8 rows); the leader CTA issues M = 256 MMAs that read both halves and write
 // each CTA's 128 accumulator lanes.  Per-CTA operand traffic and shared memory per stage halve,
 // which doubles the number of k-block stages in flight.
-template <int CG>
+// TILED: the accumulator columns are in tile order (target pixel (y, x) of the patch at column
+// (y>>2)*128 + (x>>2)*16 + (y&3)*4 + (x&3)): the producer fetches the patch as 4x4-pixel boxes, one per tile, and
+// the epilogue writes the tiled slabs of pyramid_tiled.cuh.
+template <int CG, bool TILED>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
@@ -449,7 +495,20 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           const int kcoord = (j & 1) ? p.D + kb * KBLK : kb * KBLK;
           mbar_wait(&b_empty[stage], phase ^ 1);
           if (leader) mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);  // both CTAs' halves
-          if (CG == 1)
+          if (TILED) {
+            // one 4x4-pixel box per tile (16 rows x 128 B = 2 KB), tile order = accumulator column order
+            uint8_t* dst = smem_b + stage * kBStage;
+            if (CG == 1) {
+#pragma unroll
+              for (int t = 0; t < 16; ++t)
+                tma_load_4d(&tmB, &b_full[stage], dst + t * 2048, kcoord, x0 + 4 * (t & 7), y0 + 4 * (t >> 3), b);
+            } else {
+              const uint32_t bar = mapa_shared(smem_u32(&b_full[stage]), 0);
+#pragma unroll
+              for (int t = 0; t < 8; ++t)  // this CTA's tile row of the patch
+                tma_load_4d_pair(&tmB, bar, dst + t * 2048, kcoord, x0 + 4 * t, y0 + (int)rank * (PH / 2), b);
+            }
+          } else if (CG == 1)
             tma_load_4d(&tmB, &b_full[stage], smem_b + stage * kBStage, kcoord, x0, y0, b);
           else  // this CTA's 4 of the patch's 8 rows
             tma_load_4d_pair(&tmB, mapa_shared(smem_u32(&b_full[stage]), 0), smem_b + stage * kBStage, kcoord, x0,
@@ -556,6 +615,98 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
       mbar_wait(&acc_full[buf], acc_phase);
       tc_fence_after();
+      if (TILED) {
+        // half = which four tile columns (16 target columns) of the patch this warp owns, both tile rows
+        const uint32_t tcol = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 64);
+        const bool last_row = y0 + PH >= p.h;
+        float l1t[2][16];  // this warp's two level-1 tiles, [u][cy * 4 + cx]
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          float a[2][32];
+          tmem_ld_32x32(tcol + u * 32, a[0]);        // tile row 0: tiles 4*half + 2u, +1
+          tmem_ld_32x32(tcol + 128 + u * 32, a[1]);  // tile row 1
+          tmem_ld_wait();
+          if (u == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (CG == 1) mbar_arrive(&acc_empty[buf]);
+              else mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[buf]), 0));
+            }
+          }
+          const int pair0 = (x0 >> 3) + 2 * half + u;
+          if (pair0 * 2 < p.ltx[0]) {
+            emit_pair(S, a[0], &tmO0, b, m0, pair0, (y0 >> 2), lane);
+            if ((y0 >> 2) + 1 < p.lty[0]) emit_pair(S, a[1], &tmO0, b, m0, pair0, (y0 >> 2) + 1, lane);
+          }
+          if (p.L > 1) {
+#pragma unroll
+            for (int ty = 0; ty < 2; ++ty)
+#pragma unroll
+              for (int t = 0; t < 2; ++t) pool_tile(a[ty] + t * 16, l1t[u] + (2 * ty) * 4 + 2 * t, 4);
+          }
+        }
+        if (p.L > 1) {
+          // level 1: rows (y0>>1) + 0..3, columns (x0>>1) + 8*half + 4u + 0..3; cells past the level are zero
+          const int ry1 = p.lh[1] - (y0 >> 1), rx1 = p.lw[1] - ((x0 >> 1) + 8 * half);
+          if (ry1 < 4 || rx1 < 8) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+              for (int cy = 0; cy < 4; ++cy)
+#pragma unroll
+                for (int cx = 0; cx < 4; ++cx)
+                  if (cy >= ry1 || 4 * u + cx >= rx1) l1t[u][cy * 4 + cx] = 0.0f;
+          }
+          if (rx1 > 0 && ry1 > 0) emit_pair(S, &l1t[0][0], &tmO1, b, m0, (x0 >> 4) + half, y0 >> 3, lane);
+        }
+        if (p.L > 2) {
+          // level 2: rows (y0>>2) + r, columns (x0>>2) + 4*half + c -> half a tile (2 rows x 4 columns)
+          float l2[2][4];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) pool_tile(l1t[u], &l2[0][2 * u], 4);
+          const int ry2 = p.lh[2] - (y0 >> 2), rx2 = p.lw[2] - ((x0 >> 2) + 4 * half);
+#pragma unroll
+          for (int r = 0; r < 2; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              if (r >= ry2 || c >= rx2) l2[r][c] = 0.0f;
+          const int q = m0 + lane;
+          const int tcol2 = (x0 >> 4) + half, trow2 = y0 >> 4, rt2 = (y0 >> 2) & 3;
+          if (q < p.nq && rx2 > 0 && trow2 * 4 < p.lh[2]) {  // the tile holds valid cells
+            float* t2 = p.level[2] + ((long long)b * p.nq + q) * p.lslab[2] + ((long long)trow2 * p.ltx[2] + tcol2) * 16;
+            *reinterpret_cast<float4*>(t2 + rt2 * 4) = make_float4(l2[0][0], l2[0][1], l2[0][2], l2[0][3]);
+            *reinterpret_cast<float4*>(t2 + rt2 * 4 + 4) = make_float4(l2[1][0], l2[1][1], l2[1][2], l2[1][3]);
+            if (last_row && rt2 == 0) {  // no patch below: the tile's lower half is padding
+              *reinterpret_cast<float4*>(t2 + 8) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+              *reinterpret_cast<float4*>(t2 + 12) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            }
+          }
+          if (p.L > 3) {
+            // level 3: row y0>>3, columns (x0>>3) + 2*half + c -> 8 bytes of a tile row
+            const int ry3 = p.lh[3] - (y0 >> 3), rx3 = p.lw[3] - ((x0 >> 3) + 2 * half);
+            float l3[2];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              l3[c] = __fadd_rn(__fadd_rn(l2[0][2 * c], l2[0][2 * c + 1]), __fadd_rn(l2[1][2 * c], l2[1][2 * c + 1])) * 0.25f;
+              if (ry3 < 1 || c >= rx3) l3[c] = 0.0f;
+            }
+            const int tcol3 = x0 >> 5, trow3 = y0 >> 5, rt3 = (y0 >> 3) & 3;
+            if (q < p.nq && tcol3 * 4 < p.lw[3] && trow3 * 4 < p.lh[3]) {  // the tile holds valid cells
+              float* t3 = p.level[3] + ((long long)b * p.nq + q) * p.lslab[3] + ((long long)trow3 * p.ltx[3] + tcol3) * 16 +
+                          2 * half;
+              *reinterpret_cast<float2*>(t3 + rt3 * 4) = make_float2(l3[0], l3[1]);
+              if (last_row)  // no patch below: the rest of the tile is padding
+                for (int r = rt3 + 1; r < 4; ++r) *reinterpret_cast<float2*>(t3 + r * 4) = make_float2(0.0f, 0.0f);
+            }
+          }
+        }
+        if (++buf == 2) {
+          buf = 0;
+          acc_phase ^= 1;
+        }
+        continue;
+      }
       const uint32_t taddr =
           tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 4 * PW);
 
@@ -663,14 +814,20 @@ extern "C" size_t raftk_corr_pyramid_scratch_bytes(int B, int nq, int h, int w, 
   return raftk::tc::scratch_bytes(B, nq, h, w, D);
 }
 
-extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float* const* levels, int num_levels,
-                                  int B, int nq, int h, int w, int D, void* scratch, size_t scratch_bytes,
-                                  void* stream) {
+static int corr_pyramid_impl(const float* fmap1, const float* fmap2, float* const* levels, int num_levels, int B, int nq,
+                             int h, int w, int D, void* scratch, size_t scratch_bytes, void* stream, bool tiled) {
   using namespace raftk;
   using namespace raftk::tc;
   int rc = check_pyramid_args(fmap1, fmap2, levels, num_levels, B, nq, h, w, D);
   if (rc != RAFTK_OK) return rc;
   if (B == 0 || nq == 0) return RAFTK_OK;
+  if (tiled) {
+    // the tiled epilogue covers what the 8x32 patch reaches (4 levels) on the tensor-core tiling; other
+    // configurations: build row-major levels and convert (raftk_pyramid_tile)
+    if (!supported(D) || num_levels > 4) return RAFTK_ERR_UNSUPPORTED;
+    for (int l = 0; l < num_levels; ++l)
+      if ((uintptr_t)levels[l] & 127) return RAFTK_ERR_ALIGN;
+  }
   // Feature widths the tensor-core tiling does not cover (D not a multiple of 64, or an A tile
   // larger than shared memory) take the fp32 FMA kernels: same contract, no scratch.
   if (!supported(D)) return raftk_corr_pyramid_simt(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, stream);
@@ -711,7 +868,8 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   {
     const cuuint64_t dims[4] = {(cuuint64_t)(2 * D), (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)B};
     const cuuint64_t strides[3] = {(cuuint64_t)(2 * D) * 2, (cuuint64_t)w * 2 * D * 2, (cuuint64_t)h * w * 2 * D * 2};
-    const cuuint32_t box[4] = {KBLK, PW, (cuuint32_t)(PH / CG), 1};  // a CTA pair loads half a patch each
+    // row-major: a CTA (pair) loads (half) a patch per stage; tiled: one 4x4-pixel box per tile
+    const cuuint32_t box[4] = {KBLK, tiled ? 4u : (cuuint32_t)PW, tiled ? 4u : (cuuint32_t)(PH / CG), 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     if (encode(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, b_split, dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -732,6 +890,25 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   CUtensorMap tmO[4];
   memset(tmO, 0, sizeof(tmO));
   for (int l = 0; l < p.L; ++l) {
+    p.ltx[l] = tiled_tiles_x(w >> l);
+    p.lty[l] = tiled_tiles_y(h >> l);
+    p.lslab[l] = tiled_slab_floats(h >> l, w >> l);
+  }
+  if (tiled) {
+    // levels 0 and 1 leave through bulk tensor stores: (32 floats = tile pair, pairs per tile row, tile rows, query, pair)
+    for (int l = 0; l < p.L && l < 2; ++l) {
+      const cuuint64_t dims[5] = {32, (cuuint64_t)p.ltx[l] / 2, (cuuint64_t)p.lty[l], (cuuint64_t)nq, (cuuint64_t)B};
+      const cuuint64_t strides[4] = {128, (cuuint64_t)p.ltx[l] * 64, (cuuint64_t)p.lslab[l] * 4,
+                                     (cuuint64_t)nq * p.lslab[l] * 4};
+      const cuuint32_t box[5] = {32, 1, 1, 32, 1};
+      const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+      if (encode(&tmO[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 5, levels[l], dims, strides, box, estr,
+                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return RAFTK_ERR_UNSUPPORTED;
+    }
+  }
+  for (int l = 0; l < p.L && !tiled; ++l) {
     if (!p.vec_ok[l]) continue;
     const cuuint64_t lw = (cuuint64_t)(w >> l), lh = (cuuint64_t)(h >> l);
     const cuuint64_t dims[4] = {lw, lh, (cuuint64_t)nq, (cuuint64_t)B};
@@ -763,7 +940,8 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   const long long max_units = RAFTK_SM_COUNT / CG;
   const long long tiles_per_pair = (long long)p.m_tiles * p.n_tiles;
   const int units = (int)(tiles_per_pair < max_units ? tiles_per_pair : max_units);
-  auto kernel = CG == 2 ? corr_pyramid_tc_kernel<2> : corr_pyramid_tc_kernel<1>;
+  auto kernel = tiled ? (CG == 2 ? corr_pyramid_tc_kernel<2, true> : corr_pyramid_tc_kernel<1, true>)
+                      : (CG == 2 ? corr_pyramid_tc_kernel<2, false> : corr_pyramid_tc_kernel<1, false>);
   // per-device attribute; cheap enough to set on every call (keeps the library stateless)
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT) != cudaSuccess)
     return launch_status();
@@ -786,6 +964,18 @@ extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float*
   // levels beyond the 8x32 patch's reach (only if a caller asks for more than 4)
   if (num_levels > 4) return launch_pool_levels(levels, 4, num_levels, (long long)B * nq, h, w, s);
   return RAFTK_OK;
+}
+
+extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float* const* levels, int num_levels,
+                                  int B, int nq, int h, int w, int D, void* scratch, size_t scratch_bytes,
+                                  void* stream) {
+  return corr_pyramid_impl(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, scratch, scratch_bytes, stream, false);
+}
+
+extern "C" int raftk_corr_pyramid_tiled(const float* fmap1, const float* fmap2, float* const* levels, int num_levels,
+                                        int B, int nq, int h, int w, int D, void* scratch, size_t scratch_bytes,
+                                        void* stream) {
+  return corr_pyramid_impl(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, scratch, scratch_bytes, stream, true);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -135,11 +135,8 @@ extern "C" int raftk_gru_gate(const float* zr_pre, const float* bias_zr, const f
   if (bits & 7) return RAFTK_ERR_ALIGN;
   const bool v4 = !(bits & 15) && hidden % 4 == 0 && ldh % 4 == 0 && ld_rh % 4 == 0;
   auto s = static_cast<cudaStream_t>(stream);
-  if (v4)
-    launch_pdl(gru_gate_kernel<4>, grid_for(npix * (hidden / 4)), 256, 0, s, zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
-  else
-    launch_pdl(gru_gate_kernel<2>, grid_for(npix * (hidden / 2)), 256, 0, s, zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
-  return launch_status();
+  if (v4) return launch_pdl(gru_gate_kernel<4>, grid_for(npix * (hidden / 4)), 256, 0, s, zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
+  return launch_pdl(gru_gate_kernel<2>, grid_for(npix * (hidden / 2)), 256, 0, s, zr_pre, bias_zr, h, ldh, z_out, rh_out, ld_rh, npix, hidden);
 }
 
 extern "C" int raftk_gru_update(const float* q_pre, const float* bq, const float* z, float* h, int ldh, float* h_dense,
@@ -152,11 +149,8 @@ extern "C" int raftk_gru_update(const float* q_pre, const float* bq, const float
   if (bits & 7) return RAFTK_ERR_ALIGN;
   const bool v4 = !(bits & 15) && hidden % 4 == 0 && ldh % 4 == 0;
   auto s = static_cast<cudaStream_t>(stream);
-  if (v4)
-    launch_pdl(gru_update_kernel<4>, grid_for(npix * (hidden / 4)), 256, 0, s, q_pre, bq, z, h, ldh, h_dense, npix, hidden);
-  else
-    launch_pdl(gru_update_kernel<2>, grid_for(npix * (hidden / 2)), 256, 0, s, q_pre, bq, z, h, ldh, h_dense, npix, hidden);
-  return launch_status();
+  if (v4) return launch_pdl(gru_update_kernel<4>, grid_for(npix * (hidden / 4)), 256, 0, s, q_pre, bq, z, h, ldh, h_dense, npix, hidden);
+  return launch_pdl(gru_update_kernel<2>, grid_for(npix * (hidden / 2)), 256, 0, s, q_pre, bq, z, h, ldh, h_dense, npix, hidden);
 }
 
 extern "C" int raftk_motion_scatter(const float* cf_pre, int ld_src, const float* bias, const float* flow, float* dst_a,
@@ -166,9 +160,8 @@ extern "C" int raftk_motion_scatter(const float* cf_pre, int ld_src, const float
   if (npix == 0) return RAFTK_OK;
   if (!cf_pre || !bias || !flow || !dst_a || !dst_b) return RAFTK_ERR_NULL;
   if (((uintptr_t)cf_pre | (uintptr_t)bias | (uintptr_t)flow | (uintptr_t)dst_a | (uintptr_t)dst_b) & 7) return RAFTK_ERR_ALIGN;
-  launch_pdl(motion_scatter_kernel, grid_for(npix * (c_cf / 2 + 1)), 256, 0, static_cast<cudaStream_t>(stream), cf_pre, bias,
+  return launch_pdl(motion_scatter_kernel, grid_for(npix * (c_cf / 2 + 1)), 256, 0, static_cast<cudaStream_t>(stream), cf_pre, bias,
              flow, dst_a, dst_b, ld, npix, c_cf, ld_src);
-  return launch_status();
 }
 
 extern "C" int raftk_flow_update(const float* delta_pre, int ld_delta, const float* bias, const float* coords0,
@@ -181,8 +174,7 @@ extern "C" int raftk_flow_update(const float* delta_pre, int ld_delta, const flo
   if (((uintptr_t)delta_pre | (uintptr_t)bias | (uintptr_t)coords0 | (uintptr_t)coords1 | (uintptr_t)flow |
        (uintptr_t)flow_pitched) & 7)
     return RAFTK_ERR_ALIGN;
-  launch_pdl(flow_update_kernel, grid_for(npix), 256, 0, static_cast<cudaStream_t>(stream), delta_pre, ld_delta,
+  return launch_pdl(flow_update_kernel, grid_for(npix), 256, 0, static_cast<cudaStream_t>(stream), delta_pre, ld_delta,
              reinterpret_cast<const float2*>(bias), reinterpret_cast<const float2*>(coords0),
              reinterpret_cast<float2*>(coords1), reinterpret_cast<float2*>(flow), flow_pitched, ld_flow, npix);
-  return launch_status();
 }

@@ -8,13 +8,27 @@
 
 #include "raftk.h"
 
-#define RAFTK_SM_COUNT 148  // B200: 2 dies x 74 SMs
-
 namespace raftk {
 
-// Launch-error check: peek so an earlier sticky error is reported but not cleared twice.
+// SMs of the current device (B200: 148 = 2 dies x 74), queried once per device; grids are sized from it.
+static inline int sm_count() {
+  static int cached[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (!cached[dev]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;  // racing writers store the same value
+  }
+  return cached[dev];
+}
+#define RAFTK_SM_COUNT (::raftk::sm_count())
+
+// Status after a <<<>>> launch: the last error of the runtime, PEEKED (not cleared).  It is this launch's own
+// failure (bad configuration) or an earlier error of the context that nobody has collected yet; either way the
+// host framework still sees it.
 static inline int launch_status() {
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = cudaPeekAtLastError();
   return e == cudaSuccess ? RAFTK_OK : static_cast<int>(e);
 }
 
@@ -37,8 +51,9 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 int& pdl_flag();
 static inline bool pdl_enabled() { return pdl_flag() != 0; }
 
+// Returns the launch's own status (cudaLaunchKernelEx's return value).
 template <typename... KArgs, typename... Args>
-static inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+static inline int launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
@@ -50,7 +65,8 @@ static inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+  return e == cudaSuccess ? RAFTK_OK : static_cast<int>(e);
 }
 
 // Streaming 128-bit store / load: the volume is written once and read much later,

@@ -521,7 +521,10 @@ class RAFT:
         self.concurrent = concurrent and self.fused_update
         self._streams: Dict[str, Any] = {}
         self.config = config
-        self.corr_block = corr_block or CorrBlock(config.corr_block_num_levels, config.corr_block_radius)
+        # the pyramid is opaque to the model (model.py:530-539): tiled slabs, unless the optional lookup+convolution
+        # kernel (which reads row-major levels) is asked for
+        self.corr_block = corr_block or CorrBlock(config.corr_block_num_levels, config.corr_block_radius,
+                                                  layout="rowmajor" if fused_lookup_conv else "tiled")
         expected = config.corr_block_num_levels * (2 * config.corr_block_radius + 1) ** 2
         assert self.corr_block.out_channels == expected, (
             f"corr_block.out_channels={self.corr_block.out_channels} does not match the motion encoder ({expected})")
