@@ -19,8 +19,20 @@
 //                 tasks are consecutive too, so the 32 tasks of a pass fill (2r+1)*128 contiguous bytes of
 //                 the output: staged in shared memory (stride 2r+1 words: conflict-free) and sent as ONE
 //                 bulk copy (cp.async.bulk shared -> global) per pass — no LSU store wavefronts at all.
-//   latency       a warp works on G queries at a time (4G (query, level) footprints, 4G(2r+1) tasks) and
-//                 issues the half-tile loads of its NEXT group before the taps of the current one.
+//   latency       a warp works on G = 2 queries at a time (8 (query, level) footprints, 72 column tasks: two full
+//                 passes of 32 lanes, and the last 8 columns split four ways so the third pass costs a third),
+//                 and while it evaluates one group the half-tile loads of its next group (registers) and the
+//                 coordinates of the one after (2 registers) are in flight.
+//
+// Measured on B200 (profiles/lookup_time.py, back to back, 8 coordinate sets): batch 16: 78 us = 4.2 TB/s of
+// algorithmic bytes (0.64 of the measured HBM peak), batch 64: 299 us (0.67); the row-major kernel: 100 us (0.50).
+// DRAM moves 2557 + 1296 B per query (ncu), i.e. 1.33x the algorithmic 2904 B: with the previous launch's output
+// still being written back that is 435 MB per launch = 74 us at the 5.9 TB/s this access pattern reaches
+// (profiles/layout_bench.cu), so the kernel runs within ~5 % of what the layout allows.
+// Tried and dropped, with ncu in hand (all bit-exact, none faster): one footprint tile per shared-memory
+// instruction (27 lanes x 3 taps, pitch 14: conflict-free reads, but every lane recomputes its y weights —
+// 77 us); cp.async staging straight into double-buffered tiles (88 us: LDGSTS issue rate); no software pipeline
+// with 5 blocks per SM (104 us); one query per warp (113 us).
 //
 // Arithmetic.  Per tap and per axis the reference evaluates (jax map_coordinates, order 1)
 //     s = c_l + d;  i0 = floor(s);  w1 = s - i0;  w0 = 1 - w1          (c_l = c / 2^l, exact; d = offset)
@@ -377,6 +389,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Pa
   if (lane == 0) bulk_wait_read<0>();  // shared memory must outlive the last bulk copies
 }
 
+
 // ---- generic path over tiled slabs (any radius <= 7, <= RAFTK_MAX_LEVELS levels): one warp per query, scalar
 // staged footprints, the tap code of corr_lookup.cu ----
 struct GenericParams {
@@ -459,20 +472,13 @@ int lookup_variant() {
 
 template <int R, bool UPDATE>
 int launch_fast_r(const raftk::lt::Params& p, cudaStream_t s) {
-  switch (lookup_variant()) {
-    case 1: return launch_fast<R, 2, 4, 4, true, UPDATE>(p, s);
-    case 2: return launch_fast<R, 2, 4, 5, true, UPDATE>(p, s);
-    case 3: return launch_fast<R, 2, 4, 5, false, UPDATE>(p, s);
-    case 4: return launch_fast<R, 2, 4, 6, false, UPDATE>(p, s);
-    case 5: return launch_fast<R, 2, 8, 3, false, UPDATE>(p, s);
-    case 6: return launch_fast<R, 1, 4, 8, false, UPDATE>(p, s);
-    case 7: return launch_fast<R, 4, 4, 3, false, UPDATE>(p, s);
-    case 8: return launch_fast<R, 1, 8, 4, true, UPDATE>(p, s);
-    case 9: return launch_fast<R, 2, 4, 3, true, UPDATE>(p, s);
-    case 10: return launch_fast<R, 2, 8, 2, true, UPDATE>(p, s);
-    case 11: return launch_fast<R, 2, 2, 8, true, UPDATE>(p, s);
+  switch (lookup_variant()) {  // A/B variants behind the numbers in DESIGN.md §4.2
+    case 1: return launch_fast<R, 2, 4, 3, true, UPDATE>(p, s);   // 3 blocks per SM (more registers)
+    case 2: return launch_fast<R, 2, 4, 5, false, UPDATE>(p, s);  // no software pipeline, 5 blocks per SM
+    case 3: return launch_fast<R, 1, 4, 8, true, UPDATE>(p, s);   // one query per warp, 8 blocks per SM
     default: break;
   }
+  // two queries per warp, 4 warps per block, 4 blocks per SM (128 registers), software-pipelined
   return launch_fast<R, 2, 4, 4, true, UPDATE>(p, s);
 }
 
