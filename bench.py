@@ -343,6 +343,9 @@ def lookup_back_to_back(torch, J, dev, hbm_gbs, batch):
     coords = [J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
               for _ in range(8)]
     cb = J.CorrBlock(L, r)
+    from jax_raft_b200.corr import TiledPyramid
+
+    pyr = TiledPyramid.from_dense(pyr)  # the product layout (what build_pyramid returns)
     side = torch.cuda.Stream(device=dev)
     side.wait_stream(torch.cuda.current_stream(dev))
     graph = torch.cuda.CUDAGraph()

@@ -202,18 +202,24 @@ __global__ void __launch_bounds__(kFastWarps * 32) corr_lookup_fast_kernel(const
       y = __ldg(p.coords + 2 * (size_t)qq + 1);
       return;
     }
-    const float2 c1 = *reinterpret_cast<const float2*>(p.coords_rw + 2 * (size_t)qq);
-    const float2 d = *reinterpret_cast<const float2*>(p.delta + (size_t)qq * p.ld_delta);
-    const float2 b = __ldg(reinterpret_cast<const float2*>(p.dbias));
-    const float2 c0 = __ldg(reinterpret_cast<const float2*>(p.coords0) + qq);
-    x = __fadd_rn(c1.x, __fadd_rn(d.x, b.x));
-    y = __fadd_rn(c1.y, __fadd_rn(d.y, b.y));
+    // lane 0 alone reads, advances and writes the query's coordinates (one reader-writer per address), then
+    // hands them to the warp
+    x = 0.0f;
+    y = 0.0f;
     if (lane == 0) {
+      const float2 c1 = *reinterpret_cast<const float2*>(p.coords_rw + 2 * (size_t)qq);
+      const float2 d = *reinterpret_cast<const float2*>(p.delta + (size_t)qq * p.ld_delta);
+      const float2 b = __ldg(reinterpret_cast<const float2*>(p.dbias));
+      const float2 c0 = __ldg(reinterpret_cast<const float2*>(p.coords0) + qq);
+      x = __fadd_rn(c1.x, __fadd_rn(d.x, b.x));
+      y = __fadd_rn(c1.y, __fadd_rn(d.y, b.y));
       const float2 f = make_float2(__fadd_rn(x, -c0.x), __fadd_rn(y, -c0.y));
       *reinterpret_cast<float2*>(p.coords_rw + 2 * (size_t)qq) = make_float2(x, y);
       *reinterpret_cast<float2*>(p.flow + 2 * (size_t)qq) = f;
       if (p.flow_pitched) *reinterpret_cast<float2*>(p.flow_pitched + (size_t)qq * p.ld_flow) = f;
     }
+    x = __shfl_sync(0xffffffffu, x, 0);
+    y = __shfl_sync(0xffffffffu, y, 0);
   };
   int q = blockIdx.x * kFastWarps + warp;
   float cx = 0.0f, cy = 0.0f;

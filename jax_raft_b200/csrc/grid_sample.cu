@@ -3,7 +3,8 @@
 // mode='constant') vmapped over batch and channel.  The correlation lookup has this fused
 // (lookup_taps.cuh); this entry point is the stand-alone form of the reference's helper.
 //
-// One thread per (sample, 4-channel group) when C % 4 == 0, else per (sample, channel).
+// One thread per (sample, channel), scalar loads: C = 1 on the correlation path (one pyramid level), where there
+// is nothing to vectorise over; a wide-C caller pays strided loads.
 // Arithmetic per sample, float32, no FMA contraction, as the reference:
 //   i0 = floor(c); w1 = c - i0; w0 = 1 - w1;
 //   out = (((wy0*wx0)*v00 + (wy0*wx1)*v01) + (wy1*wx0)*v10) + (wy1*wx1)*v11,  v = 0 outside.

@@ -24,6 +24,7 @@ import subprocess
 try:
     import jax
     import jax.numpy as jnp
+    import numpy as np
 except ImportError as exc:  # pragma: no cover - jax is absent on the build image
     raise ImportError(
         "jax_raft_b200.jaxffi needs jax/jaxlib (absent on the build image: no wheels, no network). "
@@ -96,7 +97,7 @@ class CorrBlock:
         assert centroids_coords.shape[-1] == 2
         b, h, w, _ = centroids_coords.shape
         out = jax.ShapeDtypeStruct((b, h, w, self.out_channels), jnp.float32)
-        return jax.ffi.ffi_call("raftk_corr_lookup", out)(*corr_pyramid, centroids_coords, radius=self.radius)
+        return jax.ffi.ffi_call("raftk_corr_lookup", out)(*corr_pyramid, centroids_coords, radius=np.int32(self.radius))
 
 
 class AltCorrBlock(CorrBlock):
@@ -113,7 +114,7 @@ class AltCorrBlock(CorrBlock):
         fmap1, levels = corr_pyramid
         b, h, w, _ = centroids_coords.shape
         out = jax.ShapeDtypeStruct((b, h, w, self.out_channels), jnp.float32)
-        return jax.ffi.ffi_call("raftk_altcorr_lookup", out)(fmap1, *levels, centroids_coords, radius=self.radius)
+        return jax.ffi.ffi_call("raftk_altcorr_lookup", out)(fmap1, *levels, centroids_coords, radius=np.int32(self.radius))
 
 
 def upsample_flow(flow, up_mask=None, factor: int = 8):
