@@ -245,6 +245,20 @@ def run_reference(args):
 # ---------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------
+SWEEP_SIZES = ((46, 128), (55, 128), (68, 120), (90, 160), (136, 240))  # BASELINE config 5 (1/8-resolution h x w)
+NCCL_BUS_REFERENCE_GBS = 725.0  # measured all-gather bus bandwidth of this pool's NVSwitch boxes
+
+
+def torchvision_init_variables(J, torch, name: str = "raft_large", seed: int = 0):
+    """The weights every end-to-end parity test uses: torchvision's random initialisation under
+    ``torch.manual_seed(seed)``, converted by the checkpoint converter's rules."""
+    import torchvision.models.optical_flow as tvof
+
+    torch.manual_seed(seed)
+    net = getattr(tvof, name)(weights=None).eval()
+    return J.variables_from_torch_state_dict(net.state_dict())
+
+
 class _TimedCorr:
     """Wraps a corr block and records CUDA events around its launches.
 
@@ -252,7 +266,7 @@ class _TimedCorr:
     graph, so on replay the kernels are timed back to back on the launching stream, without the
     host launch gaps an eager pass would put between an event and its kernel."""
 
-    def __init__(self, inner, torch, external: bool):
+    def __init__(self, inner, torch, external: bool = True):
         self.inner, self.torch, self.external = inner, torch, external
         self.out_channels = inner.out_channels
         self.lookup_events, self.build_events, self.empty_events = [], [], []
@@ -292,60 +306,58 @@ class _TimedCorr:
         return out
 
 
-def time_hot_path_kernels(torch, J, model, variables, runner, flush, dev, passes):
-    """Mean launch duration (ms) of the lookup and of build_pyramid inside full forwards.  Also leaves the
-    mean duration of an EMPTY event pair (two event nodes with nothing between) in
-    ``time_hot_path_kernels.event_overhead_ms``: the part of every event-bracketed figure that is the
-    events themselves."""
-    time_hot_path_kernels.event_overhead_ms = None
-    P = model.prepare(variables, dev)
-    try:
-        tcorr = _TimedCorr(model.corr_block, torch, external=True)
-        model_t = J.RAFT(model.config, corr_block=tcorr, precision=model.precision)
-        g = torch.cuda.CUDAGraph()
-        with torch.no_grad(), torch.cuda.graph(g):
-            model_t.forward(P, runner.image1, runner.image2, ITERS)
-        lk, bd, ov = [], [], []
-        for _ in range(passes):
-            flush.fill_(1)
-            g.replay()
-            torch.cuda.synchronize(dev)
-            lk += [a.elapsed_time(b) for a, b in tcorr.lookup_events]
-            bd += [a.elapsed_time(b) for a, b in tcorr.build_events]
-            ov += [a.elapsed_time(b) for a, b in tcorr.empty_events]
-        time_hot_path_kernels.event_overhead_ms = sum(ov) / len(ov) if ov else None
-        return lk, bd, "CUDA events recorded as graph nodes around each launch, graph replay of the full forward"
-    except Exception as exc:  # older torch without external events: eager pass behind a GPU backlog
-        tcorr = _TimedCorr(model.corr_block, torch, external=False)
-        model_t = J.RAFT(model.config, corr_block=tcorr, precision=model.precision)
+class _Captured:
+    """One CUDA graph of the full forward at a given batch, optionally with event nodes around the hot-path
+    launches.  The eager warm-ups (library autotune) run on the plain model; the timed twin shares its weights."""
+
+    def __init__(self, torch, J, model, variables, batch, dev, timed_corr: bool):
+        P = model.prepare(variables, dev)
+        self.tcorr = None
+        m = model
+        if timed_corr:
+            self.tcorr = _TimedCorr(model.corr_block, torch, external=True)
+            m = J.RAFT(model.config, corr_block=self.tcorr, precision=model.precision)
+        self.model = m
+        self.image1 = torch.zeros((batch, H, W, 3), dtype=torch.float32, device=dev)
+        self.image2 = torch.zeros((batch, H, W, 3), dtype=torch.float32, device=dev)
         with torch.no_grad():
-            for i in range(1 + passes):
-                if i == 1:
-                    tcorr.lookup_events.clear()
-                    tcorr.build_events.clear()
-                flush.fill_(1)
-                torch.cuda._sleep(int(60e6))  # ~30 ms backlog so launches queue behind it
-                model_t.forward(P, runner.image1, runner.image2, ITERS)
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    model.forward(P, self.image1, self.image2, ITERS)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self.flows = m.forward(P, self.image1, self.image2, ITERS)
         torch.cuda.synchronize(dev)
-        lk = [a.elapsed_time(b) for a, b in tcorr.lookup_events]
-        bd = [a.elapsed_time(b) for a, b in tcorr.build_events]
-        return lk, bd, f"CUDA events around each launch in eager forwards behind a GPU backlog ({type(exc).__name__})"
+
+    def hot_path_ms(self):
+        """Mean durations (ms) between the event nodes of the LAST replay: lookup, build_pyramid, empty pair."""
+        t = self.tcorr
+        mean = lambda evs: (sum(a.elapsed_time(b) for a, b in evs) / len(evs)) if evs else None  # noqa: E731
+        return mean(t.lookup_events), mean(t.build_events), mean(t.empty_events)
 
 
-def lookup_back_to_back(torch, J, dev, hbm_gbs, batch):
+def lookup_bytes_per_query(r: int = 4, L: int = 4) -> int:
+    """read L*(2r+2)^2*4 + 8, write L*(2r+1)^2*4 (float32 pyramid and output): 2904 B at r = 4."""
+    return L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4
+
+
+def lookup_back_to_back(torch, J, dev, hbm_gbs, batch, h=H // 8, w=W // 8):
     """The lookup alone with no host or event between launches: one CUDA graph of 8 launches over 8
-    different coordinate sets (8 x 29 MB of footprints per pair, so a launch does not find its rows in
-    L2), replayed 4 times between two events; best of 5.  Kernel-to-kernel throughput, not latency."""
-    h, w, r, L = H // 8, W // 8, 4, 4
+    different coordinate sets (so a launch does not find its footprints in L2), replayed 4 times between
+    two events; best of 5.  Kernel-to-kernel throughput, not latency."""
+    from jax_raft_b200.corr import TiledPyramid
+
+    r, L = 4, 4
     g = torch.Generator(device=dev).manual_seed(0)
     q = batch * h * w
-    pyr = [torch.randn((q, h >> l, w >> l, 1), device=dev, generator=g) for l in range(L)]
+    pyr = TiledPyramid.from_dense([torch.randn((q, h >> l, w >> l, 1), device=dev, generator=g) for l in range(L)])
     coords = [J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
               for _ in range(8)]
     cb = J.CorrBlock(L, r)
-    from jax_raft_b200.corr import TiledPyramid
-
-    pyr = TiledPyramid.from_dense(pyr)  # the product layout (what build_pyramid returns)
     side = torch.cuda.Stream(device=dev)
     side.wait_stream(torch.cuda.current_stream(dev))
     graph = torch.cuda.CUDAGraph()
@@ -366,27 +378,27 @@ def lookup_back_to_back(torch, J, dev, hbm_gbs, batch):
         e1.record()
         torch.cuda.synchronize(dev)
         best = min(best, e0.elapsed_time(e1) / 32)
-    nbytes = q * (L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4)
+    nbytes = q * lookup_bytes_per_query(r, L)
     gbs = nbytes / (best * 1e-3) / 1e9
     return {"batch": batch, "ms_per_launch": best, "algorithmic_bytes": nbytes, "hbm_gbs": gbs, "frac_of_hbm_peak": gbs / hbm_gbs}
 
 
-def kernel_microbench(torch, J, dev, flush, hbm_gbs, batch, iters=10):
-    """The three kernel families alone, at the Sintel 1/8 shape and `batch` pairs: CUDA events around
-    each launch, L2 flushed before every launch.  Gives the roofline fractions at a size that
-    fills the machine (the batch-1 step is launch/latency-bound: 20 MB per launch)."""
-    h, w, d, r, L = H // 8, W // 8, 256, 4, 4
+def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=6, with_mask_upsample=False, with_altcorr=False):
+    """The kernel families alone at 1/8-resolution size h x w, D = 256, `batch` pairs: CUDA events around each
+    call, L2 flushed before every call, host launch overhead included.  Fractions: algorithmic bytes (SURVEY.md
+    §8d) over the measured HBM copy peak; issued bf16 tensor FLOPs (3 products per float32 product, §4.1) over the
+    measured bf16 burst peak."""
+    d, r, L = 256, 4, 4
+    hbm_gbs, bf16_tf = peaks
     g = torch.Generator(device=dev).manual_seed(0)
     f1 = torch.randn((batch, h, w, d), device=dev, generator=g) * 1.45
     f2 = torch.randn((batch, h, w, d), device=dev, generator=g) * 1.45
     coords = J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
     flow = torch.randn((batch, h, w, 2), device=dev, generator=g)
-    mask = torch.randn((batch, h, w, 576), device=dev, generator=g)
     cb = J.CorrBlock(L, r)
 
     def timed(fn):
-        ts = []
-        out = None
+        ts, out = [], None
         for i in range(iters + 2):
             flush.fill_(i)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -398,36 +410,190 @@ def kernel_microbench(torch, J, dev, flush, hbm_gbs, batch, iters=10):
                 ts.append(a.elapsed_time(b))
         return sum(ts) / len(ts), out
 
-    nq = batch * h * w
-    P_l = sum((h >> l) * (w >> l) for l in range(L))
-    pyr_ms, pyr = timed(lambda: cb.build_pyramid(f1, f2))
-    lk_ms, _ = timed(lambda: cb.index_pyramid(pyr, coords))
-    up_ms, _ = timed(lambda: J.upsample_flow(flow, mask))
-    pyr_bytes = 4 * (2 * nq * d + nq * P_l)
-    lk_bytes = nq * (L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4)
-    up_bytes = nq * (2304 + 8 + 512)
-    flops = 2.0 * batch * (h * w) ** 2 * d
-
-    def entry(ms, nbytes, extra=None):
-        e = {"mean_ms": ms, "algorithmic_bytes": nbytes, "hbm_gbs": nbytes / (ms * 1e-3) / 1e9,
+    def hbm(ms, nbytes, extra=None):
+        e = {"mean_ms": ms, "algorithmic_bytes": int(nbytes), "hbm_gbs": nbytes / (ms * 1e-3) / 1e9,
              "frac_of_hbm_peak": nbytes / (ms * 1e-3) / 1e9 / hbm_gbs}
-        if extra:
-            e.update(extra)
+        e.update(extra or {})
         return e
 
-    return {
-        "batch": batch,
-        "how": "events around each call (split + GEMM for the pyramid), L2 flushed before each, host launch overhead included",
-        "corr_pyramid": entry(pyr_ms, pyr_bytes, {"tflops_algorithmic": flops / (pyr_ms * 1e-3) / 1e12,
-                                                  "tflops_issued_bf16": 3 * flops / (pyr_ms * 1e-3) / 1e12}),
-        "corr_lookup": entry(lk_ms, lk_bytes),
-        "convex_upsample": entry(up_ms, up_bytes),
-        "corr_lookup_back_to_back": {
-            "how": "graph of 8 launches over 8 coordinate sets, no events or host between launches (throughput, not latency)",
-            "batch_1": lookup_back_to_back(torch, J, dev, hbm_gbs, 1),
-            f"batch_{batch}": lookup_back_to_back(torch, J, dev, hbm_gbs, batch),
-        },
+    nq = batch * h * w
+    P_l = sum((h >> l) * (w >> l) for l in range(L))
+    flops = 2.0 * batch * (h * w) ** 2 * d
+    res = {"h": h, "w": w, "batch": batch, "queries": nq}
+    pyr_ms, pyr = timed(lambda: cb.build_pyramid(f1, f2))
+    issued = 3 * flops / (pyr_ms * 1e-3) / 1e12
+    res["corr_pyramid"] = hbm(pyr_ms, 4 * (2 * nq * d + nq * P_l), {
+        "tflops_algorithmic": flops / (pyr_ms * 1e-3) / 1e12, "tflops_issued_bf16": issued,
+        "frac_of_tensor_peak": issued / bf16_tf if bf16_tf else None, "includes": "bf16 split pre-pass + tcgen05 GEMM"})
+    lk_ms, _ = timed(lambda: cb.index_pyramid(pyr, coords))
+    res["corr_lookup"] = hbm(lk_ms, nq * lookup_bytes_per_query(r, L))
+    del pyr
+    mask = torch.randn((batch, h, w, 576), device=dev, generator=g)
+    up_ms, _ = timed(lambda: J.upsample_flow(flow, mask))
+    res["convex_upsample"] = hbm(up_ms, nq * (2304 + 8 + 512))
+    del mask
+    if with_mask_upsample:
+        k = 256
+        feats = torch.relu(torch.randn((batch, h, w, k), device=dev, generator=g))
+        weight = torch.randn((576, k, 1, 1), device=dev, generator=g) / 16
+        bias = torch.randn((576,), device=dev, generator=g)
+        pw, pb = J.pack_mask_predictor(weight, bias)
+        out = torch.empty((batch, 8 * h, 8 * w, 2), device=dev)
+        mu_ms, _ = timed(lambda: J.mask_upsample(flow, feats, pw, pb, out=out))
+        mu_flops = 2.0 * nq * 576 * k
+        tf = mu_flops / (mu_ms * 1e-3) / 1e12
+        res["mask_upsample"] = hbm(mu_ms, nq * (k * 4 + 8 + 512), {
+            "tflops_tf32": tf, "frac_of_tensor_peak": tf / (bf16_tf / 2) if bf16_tf else None,
+            "tensor_peak": "TF32 rate taken as the measured bf16 burst peak / 2 (no TF32 peak is measured)"})
+        del feats, out
+    if with_altcorr:
+        ab = J.AltCorrBlock(L, r)
+        # smooth +-8 px flow (what RAFT sees between iterations)
+        yy, xx = torch.meshgrid(torch.arange(h, device=dev), torch.arange(w, device=dev), indexing="ij")
+        sm = torch.stack([8 * torch.sin(6.28 * (xx / w + 0.3 * yy / h)), 8 * torch.cos(6.28 * (yy / h - 0.2 * xx / w))], -1)[None].float()
+        c_s = (J.make_coords_grid(batch, h, w, device=dev) + sm).contiguous()
+        pool_ms, apyr = timed(lambda: ab.build_pyramid(f1, f2))
+        alt_ms, _ = timed(lambda: ab.index_pyramid(apyr, c_s))
+        aflops = 2.0 * nq * L * (2 * r + 2) ** 2 * d
+        res["altcorr"] = {"pool_fmap2_ms": pool_ms, "lookup_ms_per_iter": alt_ms, "tflops": aflops / (alt_ms * 1e-3) / 1e12,
+                          "flops_per_iter": aflops}
+    return res
+
+
+def sync_max(torch, dist, world, dev, x):
+    if world == 1:
+        return float(x)
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def gather_all(torch, dist, world, dev, x):
+    if world == 1:
+        return [float(x)]
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    out = torch.empty((world,), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(out, t)
+    return [float(v) for v in out.tolist()]
+
+
+def config3_strong(torch, dist, J, model, variables, dev, rank, world, flush, hbm_gbs, steps=2, warmup=1):
+    """BASELINE config 3: 64 Sintel-shape pairs, 32 iterations, batch-sharded over the ranks with no collective
+    (64 / N pairs per GPU, strong scaling).  The captured forward carries event nodes around its lookup launches."""
+    from jax_raft_b200 import sharding
+
+    sl = sharding.batch_slice(64, world, rank)
+    b = sl.stop - sl.start
+    cap = _Captured(torch, J, model, variables, b, dev, timed_corr=True)
+    img1, img2 = synthetic_pairs(b, seed=100 + rank)
+    cap.image1.copy_(torch.from_numpy(img1))
+    cap.image2.copy_(torch.from_numpy(img2))
+    for _ in range(warmup):
+        cap.graph.replay()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    evs = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        cap.graph.replay()
+        e.record()
+        evs.append((a, e))
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    mine = sum(a.elapsed_time(e) for a, e in evs)
+    assert bool(torch.isfinite(cap.flows[-1]).all()), "non-finite flow (config 3)"
+    lk_ms, bd_ms, ov_ms = cap.hot_path_ms()
+    total = sync_max(torch, dist, world, dev, mine)
+    per_rank = gather_all(torch, dist, world, dev, mine / steps)
+    lk_max = sync_max(torch, dist, world, dev, lk_ms)
+    nbytes = b * (H // 8) * (W // 8) * lookup_bytes_per_query()
+    res = {
+        "workload": "raft_large 440x1024, 64 pairs, 32 iterations, batch-sharded (strong scaling, no collective)",
+        "pairs_per_gpu": b, "n_gpus": world, "steps": steps, "warmup": warmup, "value": 64 * steps / (total * 1e-3),
+        "unit": UNIT, "ms_per_step": total / steps, "per_rank_ms_per_step": per_rank,
+        "lookup_in_step": {"mean_launch_ms": lk_max, "algorithmic_bytes_per_launch": nbytes,
+                           "hbm_gbs": nbytes / (lk_max * 1e-3) / 1e9, "frac_of_hbm_peak": nbytes / (lk_max * 1e-3) / 1e9 / hbm_gbs,
+                           "event_pair_overhead_ms": ov_ms},
+        "pyramid_in_step_ms": bd_ms,
     }
+    del cap
+    torch.cuda.empty_cache()
+    return res
+
+
+def config4_rowshard(torch, dist, J, dev, rank, world, iters=ITERS):
+    """BASELINE config 4 at hot-path level: 1088x1920 (136x240 at 1/8), D = 256, alt_corr lookup with the query rows
+    sharded over the ranks and ONE NCCL all-gather of fmap2 per pair.  Every rank checks its band
+    against the materialised-volume path on its own GPU.  All operands of every kernel are local memory: fmap2
+    arrives through NCCL into a local buffer first."""
+    from jax_raft_b200 import sharding
+
+    B, h, w, D, r = 1, 136, 240, 256, 4
+    g = torch.Generator(device=dev).manual_seed(0)  # same maps on every rank; each keeps only its band
+    f1 = torch.randn((B, h, w, D), device=dev, generator=g) * 1.45
+    f2 = torch.randn((B, h, w, D), device=dev, generator=g) * 1.45
+    yy, xx = torch.meshgrid(torch.arange(h, device=dev), torch.arange(w, device=dev), indexing="ij")
+    flow = torch.stack([8 * torch.sin(6.28 * (xx / w + 0.3 * yy / h)), 8 * torch.cos(6.28 * (yy / h - 0.2 * xx / w))], -1)[None].float()
+    y0, y1 = sharding.row_range(h, world, rank)
+    f1_rows, f2_rows = f1[:, y0:y1].contiguous(), f2[:, y0:y1].contiguous()
+    coords_rows = (J.make_coords_grid(B, h, w, device=dev) + flow)[:, y0:y1].contiguous()
+    corr = sharding.RowShardedCorr(J.AltCorrBlock(4, r))
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    for _ in range(2):  # warm-up (NCCL channels, module load)
+        pyr = corr.build_pyramid(f1_rows, f2_rows, h)
+        out = corr.index_pyramid(pyr, coords_rows)
+    gather, pool = [], []
+    for _ in range(3):
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+        a, b_, c = ev(), ev(), ev()
+        a.record()
+        full2 = sharding.all_gather_rows(f2_rows, h)
+        b_.record()
+        pyr = corr.corr_block.build_pyramid(f1_rows, full2, query_rows=(y0, y1))
+        c.record()
+        torch.cuda.synchronize(dev)
+        gather.append(sync_max(torch, dist, world, dev, a.elapsed_time(b_)))
+        pool.append(sync_max(torch, dist, world, dev, b_.elapsed_time(c)))
+    lk = []
+    for _ in range(iters):
+        s, e = ev(), ev()
+        s.record()
+        out = corr.index_pyramid(pyr, coords_rows)
+        e.record()
+        lk.append((s, e))
+    torch.cuda.synchronize(dev)
+    lookup_ms = sync_max(torch, dist, world, dev, sum(s.elapsed_time(e) for s, e in lk) / len(lk))
+    gathered_ok = bool(torch.equal(full2, f2))
+    vol = J.CorrBlock(4, r)
+    ref = vol.index_pyramid(vol.build_pyramid(f1, f2, query_rows=(y0, y1)), coords_rows)
+    scale = float(ref.abs().mean())
+    err = float((out - ref).abs().max())
+    ok = torch.tensor([1.0 if (gathered_ok and err <= 1e-3 * max(scale, 1.0)) else 0.0], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    errs = gather_all(torch, dist, world, dev, err)
+    nq = B * (y1 - y0) * w
+    total_bytes = int(f2.numel() * 4)
+    gather_ms = min(gather)
+    res = {
+        "workload": f"1088x1920 ({h}x{w} at 1/8), D={D}, r={r}: alt_corr lookup, query rows over {world} GPUs, one NCCL all-gather of fmap2 per pair",
+        "n_gpus": world, "rows_per_rank": y1 - y0, "queries_per_rank": nq,
+        "all_gather_fmap2_ms": gather_ms, "all_gather_fmap2_ms_runs": gather, "all_gather_bytes_total": total_bytes,
+        "all_gather_bus_gbs": total_bytes * (world - 1) / world / (gather_ms * 1e-3) / 1e9,
+        "nccl_bus_reference_gbs": NCCL_BUS_REFERENCE_GBS,
+        "pool_fmap2_ms": min(pool), "altcorr_lookup_ms_per_iter": lookup_ms, "iters_timed": iters,
+        "altcorr_tflops_per_rank": 2.0 * nq * 4 * (2 * r + 2) ** 2 * D / (lookup_ms * 1e-3) / 1e12,
+        "band_matches_volume_path": bool(ok.item() > 0), "max_abs_err_per_rank": errs, "corr_scale": scale,
+        "timing": "CUDA events, max over ranks; all-gather: best of 3 (includes the host-side band padding / concatenation of sharding.all_gather_rows)",
+        "rest_of_model": "not sharded at this resolution (BASELINE.json does not define it; DESIGN.md §6)",
+    }
+    del f1, f2, full2, pyr, ref, out
+    torch.cuda.empty_cache()
+    return res
 
 
 def run_b200(args):
@@ -448,7 +614,8 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     B = args.batch
 
-    model, variables = J.raft_large(seed=0)
+    model, _ = J.raft_large()
+    variables = torchvision_init_variables(J, torch)  # the weights the end-to-end parity tests pin
     img1_np, img2_np = synthetic_pairs(B, seed=1 + rank)
     pin1 = torch.from_numpy(img1_np).pin_memory()
     pin2 = torch.from_numpy(img2_np).pin_memory()
@@ -480,51 +647,66 @@ def run_b200(args):
             b.record(stream)
             evs.append((a, b))
         barrier()
-        total_ms = sum(a.elapsed_time(b) for a, b in evs)
-        if world > 1:
-            t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            total_ms = float(t.item())
-        return total_ms
+        mine = sum(a.elapsed_time(b) for a, b in evs)
+        return sync_max(torch, dist, world, dev, mine), gather_all(torch, dist, world, dev, mine / steps)
 
     def step_resident():
         runner.graph.replay()
 
     def step_e2e():
-        runner.image1.copy_(pin1, non_blocking=True)
-        runner.image2.copy_(pin2, non_blocking=True)
-        runner.graph.replay()
-        out_pin.copy_(runner.flows[-1], non_blocking=True)
+        # the public call with HOST inputs (model.py:557), then the result a user reads — the last flow
+        # (scripts/validate_sintel.py:186) — back to host memory
+        flows = model.apply(variables, pin1, pin2, train=False, num_flow_updates=ITERS)
+        out_pin.copy_(flows[-1], non_blocking=True)
 
     sampler = ClockSampler(local_rank, str(getattr(torch.cuda.get_device_properties(dev), 'uuid', '')) or None).start() if rank == 0 else None
-    total_ms = timed(step_resident, args.steps, args.warmup)
+    total_ms, per_rank_ms = timed(step_resident, args.steps, args.warmup)
     clocks = sampler.stop() if sampler else None
-    e2e_ms = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    e2e_ms, e2e_per_rank = timed(step_e2e, args.steps, max(1, args.warmup // 2))
     torch.cuda.synchronize(dev)
     assert torch.isfinite(out_pin).all(), "non-finite flow"
+    assert model.runner(variables, B, H, W, ITERS, device=dev) is runner, "apply() and runner() must share one captured graph"
 
-    # ---- lookup-kernel roofline: events around every lookup launch of full forwards ----
-    lk_ms, bd_ms, how = time_hot_path_kernels(torch, J, model, variables, runner, flush, dev, args.roofline_passes)
+    # ---- lookup-kernel roofline: event nodes around every lookup launch of the captured forward ----
+    cap = _Captured(torch, J, model, variables, B, dev, timed_corr=True)
+    cap.image1.copy_(pin1)
+    cap.image2.copy_(pin2)
+    lk, bd, ov = [], [], []
+    for _ in range(args.roofline_passes):
+        flush.fill_(1)
+        cap.graph.replay()
+        torch.cuda.synchronize(dev)
+        a, b, c = cap.hot_path_ms()
+        lk.append(a)
+        bd.append(b)
+        ov.append(c)
+    lk_mean_ms, pyr_ms, ev_ov = sum(lk) / len(lk), sum(bd) / len(bd), sum(ov) / len(ov)
+    launches_timed = len(cap.tcorr.lookup_events) * args.roofline_passes
+    del cap
+
+    hbm_gbs, peak_src, peaks = measured_peaks()
+    bf16_tf = float(peaks.get("bf16_tflops_burst", peaks.get("bf16_tflops", 0.0)) or 0.0)
+    configs = {}
+    if not args.skip_configs:
+        configs["c3"] = config3_strong(torch, dist, J, model, variables, dev, rank, world, flush, hbm_gbs)
+        if world > 1:
+            configs["c4"] = config4_rowshard(torch, dist, J, dev, rank, world)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    hbm_gbs, peak_src, peaks = measured_peaks()
     cfg = model.config
     r, L = cfg.corr_block_radius, cfg.corr_block_num_levels
     nq = B * (H // 8) * (W // 8)
-    lookup_bytes = nq * (L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4)  # 2904 B/query
-    lk_mean_ms = sum(lk_ms) / len(lk_ms)
-    ev_ov = time_hot_path_kernels.event_overhead_ms
+    lookup_bytes = nq * lookup_bytes_per_query(r, L)  # 2904 B/query
     achieved = lookup_bytes / (lk_mean_ms * 1e-3) / 1e9
     N = (H // 8) * (W // 8)
     P_l = sum((H // 8 >> l) * (W // 8 >> l) for l in range(L))
     pyr_bytes = 4 * (2 * B * N * 256 + B * N * P_l)
-    pyr_ms = sum(bd_ms) / len(bd_ms)
 
-    traffic, traffic_src = ncu_traffic_per_launch("corr_lookup") if B == 1 else (None, None)
+    traffic, traffic_src = ncu_traffic_per_launch("lookup_tiled") if B == 1 else (None, None)
     pairs = world * B * args.steps
     line = {
         "metric": METRIC, "value": pairs / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
@@ -532,30 +714,34 @@ def run_b200(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {
-            "workload": f"raft_large {H}x{W} batch {B} per GPU, {ITERS} iterations (BASELINE config 2), random-init weights",
+            "workload": f"raft_large {H}x{W} batch {B} per GPU, {ITERS} iterations (BASELINE config 2), torchvision random-init weights (seed 0)",
             "global_batch": world * B, "parallelism": f"batch-sharded x{world}, no collective",
             "conv_precision": model.precision + " (cuDNN library path, out of kernel scope)",
             "l2": "flushed between timed steps (256 MiB write outside the events); step working set "
                   "(261 MB pyramid + activations) also exceeds the 126 MB L2",
             "timing": "per-step CUDA events on the launching stream, summed; barrier + synchronize both sides; max over ranks",
         },
+        "per_rank_ms": per_rank_ms,
         "e2e": {"value": pairs / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
-                "h2d_bytes_per_step": int(pin1.numel() * 4 * 2), "d2h_bytes_per_step": int(out_pin.numel() * 4)},
+                "h2d_bytes_per_step": int(pin1.numel() * 4 * 2), "d2h_bytes_per_step": int(out_pin.numel() * 4),
+                "per_rank_ms": e2e_per_rank,
+                "how": "model.apply(variables, host_image1, host_image2, train=False, num_flow_updates=32) with pinned host "
+                       "inputs, then flows[-1] copied to pinned host memory, every step"},
         "gpu_launches": int(per_forward * args.steps),
         "gpu_launches_per_step": int(per_forward),
         "clocks": clocks,
         "roofline": {
-            "kernel": "corr_lookup_fast_kernel<4> (raftk_corr_lookup)", "bound": "hbm", "achieved": achieved,
+            "kernel": "lookup_tiled_kernel<4, ...> (raftk_corr_lookup_tiled_update)", "bound": "hbm", "achieved": achieved,
             "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": traffic,
             "traffic_source": traffic_src,
             "peak_source": peak_src, "algorithmic_bytes_per_launch": lookup_bytes,
-            "mean_launch_ms": lk_mean_ms, "launches_timed": len(lk_ms),
-            "how": how,
+            "mean_launch_ms": lk_mean_ms, "launches_timed": launches_timed,
+            "how": "CUDA events recorded as graph nodes around each launch, graph replay of the full forward",
             # what the bracketing events cost by themselves (an empty pair at the same place in the graph);
             # `achieved` and `frac` above are NOT corrected for it — these two are
             "event_pair_overhead_ms": ev_ov,
-            "frac_net_of_event_overhead": (lookup_bytes / (max(lk_mean_ms - ev_ov, 1e-6) * 1e-3) / 1e9 / hbm_gbs
-                                           if ev_ov is not None else None),
+            "frac_net_of_event_overhead": lookup_bytes / (max(lk_mean_ms - ev_ov, 1e-6) * 1e-3) / 1e9 / hbm_gbs,
+            "note": "batch 1 is 20 MB per launch (3.1 us at peak): launch/latency-bound; kernels_saturating has the same kernel at sizes that fill the machine",
         },
         "kernels_in_step": {
             "corr_pyramid": {"mean_ms": pyr_ms, "algorithmic_bytes": pyr_bytes,
@@ -563,8 +749,46 @@ def run_b200(args):
                              "tflops_algorithmic": 2.0 * B * N * N * 256 / (pyr_ms * 1e-3) / 1e12},
         },
     }
+    if world == 1 and not args.skip_fp32:
+        # the same step with full-precision library convolutions (and the unfused mask convolution)
+        model32, _ = J.raft_large(precision="fp32")
+        r32 = model32.runner(variables, B, H, W, ITERS, device=dev)
+        r32.image1.copy_(pin1)
+        r32.image2.copy_(pin2)
+        ms32, _ = timed(lambda: r32.graph.replay(), max(2, args.steps // 2), 1)
+        steps32 = max(2, args.steps // 2)
+        line["fp32_convolutions"] = {"value": B * steps32 / (ms32 * 1e-3), "unit": UNIT, "ms_per_step": ms32 / steps32,
+                                     "max_abs_flow_difference_from_tf32_px": float((r32.flows[-1] - runner.flows[-1]).abs().max()),
+                                     "mean_epe_from_tf32_px": float((r32.flows[-1] - runner.flows[-1]).norm(dim=-1).mean())}
+        del r32, model32
+        torch.cuda.empty_cache()
     if world == 1 and args.micro_batch > 0:
-        line["kernels_saturating"] = kernel_microbench(torch, J, dev, flush, hbm_gbs, args.micro_batch)
+        pk = (hbm_gbs, bf16_tf)
+        sat = {"how": "events around each call, L2 flushed before each, host launch overhead included; "
+                      "corr_lookup_back_to_back: graph of 8 launches over 8 coordinate sets, no events or host between launches"}
+        for mb in sorted({args.micro_batch, 64}):
+            e = hot_kernels_at(torch, J, dev, flush, pk, H // 8, W // 8, mb, with_mask_upsample=True)
+            e["corr_lookup_back_to_back"] = lookup_back_to_back(torch, J, dev, hbm_gbs, mb)
+            sat[f"batch_{mb}"] = e
+            torch.cuda.empty_cache()
+        sat["batch_1"] = hot_kernels_at(torch, J, dev, flush, pk, H // 8, W // 8, 1, with_mask_upsample=True)
+        sat["batch_1"]["corr_lookup_back_to_back"] = lookup_back_to_back(torch, J, dev, hbm_gbs, 1)
+        # top-level aliases of the first batch, as in round 1
+        first = sat[f"batch_{args.micro_batch}"]
+        sat.update({"batch": args.micro_batch, "corr_pyramid": first["corr_pyramid"], "corr_lookup": first["corr_lookup"],
+                    "convex_upsample": first["convex_upsample"], "mask_upsample": first["mask_upsample"]})
+        line["kernels_saturating"] = sat
+        if not args.skip_configs:
+            sweep = []
+            for (sh, sw) in SWEEP_SIZES:
+                for sb in (1, max(1, round(112640 / (sh * sw)))):
+                    sweep.append(hot_kernels_at(torch, J, dev, flush, pk, sh, sw, sb, iters=4,
+                                                with_altcorr=(sb == 1 and (sh, sw) == (136, 240))))
+                    torch.cuda.empty_cache()
+            configs["c5"] = {"workload": "correlation microbench: pyramid build + lookup + upsampler over 1/8-resolution sizes, D=256, "
+                                         "batch 1 and the batch that gives ~112k queries", "sweep": sweep}
+    if configs:
+        line["configs"] = configs
     if world == 1 and not args.skip_cpu_baseline:
         v, per_pair, cores, sample, phases = cpu_oracle_pairs_per_s(steps=1, warmup=0, budget_s=25.0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
@@ -583,6 +807,8 @@ def main():
     ap.add_argument("--batch", type=int, default=1, help="pairs per GPU (BASELINE config 2: 1)")
     ap.add_argument("--roofline-passes", type=int, default=2)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-configs", action="store_true", help="leave out the configs c3/c4/c5 block")
+    ap.add_argument("--skip-fp32", action="store_true", help="leave out the fp32-convolution step time")
     ap.add_argument("--micro-batch", type=int, default=16,
                     help="pairs for the kernel-only roofline lines (0 = skip); extra info, not the headline")
     args = ap.parse_args()

@@ -45,6 +45,12 @@ def all_gather_rows(local_rows: torch.Tensor, h: int, group: Optional[dist.Proce
     y0, y1 = row_range(h, world, rank)
     assert rows == y1 - y0, f"rank {rank} should hold rows [{y0}, {y1}) of {h}, got {rows}"
     max_rows = (h + world - 1) // world
+    if b == 1 and h % world == 0:
+        # equal bands of a single pair are already the full map's memory order: gather straight into the result
+        # (no padding, no concatenation pass; one collective and nothing else)
+        full = local_rows.new_empty((1, h, w, d))
+        dist.all_gather_into_tensor(full.view(-1), local_rows.contiguous().view(-1), group=group)
+        return full
     send = local_rows
     if rows != max_rows:
         send = local_rows.new_zeros((b, max_rows, w, d))
