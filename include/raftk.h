@@ -157,6 +157,38 @@ int raftk_pyramid_tile(const float* const* rowmajor, float* const* tiled, int nu
 int raftk_pyramid_untile(const float* const* tiled, float* const* rowmajor, int num_levels, long long Q,
                          int h, int w, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Tiled pyramid with float16 storage (optional; CorrBlock(storage="fp16") on the host side).
+ * Same tile geometry as above with 2-byte elements: a 4 x 4 tile is one 32-byte sector, slab
+ * bytes = raftk_pyramid_tiled_slab_floats(h, w, l) * 2, cell (y, x) at the same ELEMENT offset.
+ * Every level is computed in float32 exactly as by raftk_corr_pyramid_tiled (level l+1 pooled
+ * from the unrounded float32 level l, model.py:443-445) and rounded once, to nearest even, when
+ * it is stored: relative error <= 2^-11 = 4.9e-4 per value on top of the GEMM's ~2e-5, inside
+ * the 1e-3 the north-star allows for correlation values; pooling bounds and padding are exact.
+ * The lookup widens the stored values to float32 and then runs the float32 tap arithmetic of
+ * raftk_corr_lookup unchanged, so its output is bit-identical to a float32 CPU evaluation of
+ * model.py:448-470 on the stored (rounded) pyramid.  Halves the pyramid's footprint (130.7 MB
+ * per 440x1024 pair), the GEMM's store traffic and the lookup's read traffic.
+ * levels[l] must be 128-byte aligned.
+ *
+ *   raftk_corr_pyramid_tiled_f16        replaces model.py:418-446 (4 levels, D % 64 == 0, D <= 256)
+ *   raftk_corr_lookup_tiled_f16(_update) replaces model.py:448-470 (+ :504-506), any radius <= 7
+ *   raftk_pyramid_tile_f16 / _untile_f16 float32 row-major levels <-> float16 tiled slabs
+ * ---------------------------------------------------------------------------------- */
+int raftk_corr_pyramid_tiled_f16(const float* fmap1, const float* fmap2, void* const* levels,
+                                 int num_levels, int B, int nq, int h, int w, int D,
+                                 void* scratch, size_t scratch_bytes, void* stream);
+int raftk_corr_lookup_tiled_f16(const void* const* levels, int num_levels, const float* coords,
+                                float* out, int Q, int h, int w, int radius, void* stream);
+int raftk_corr_lookup_tiled_f16_update(const void* const* levels, int num_levels, const float* delta_pre, int ld_delta,
+                                       const float* bias, const float* coords0, float* coords1, float* flow,
+                                       float* flow_pitched, int ld_flow, float* out, int Q, int h, int w, int radius,
+                                       void* stream);
+int raftk_pyramid_tile_f16(const float* const* rowmajor, void* const* tiled, int num_levels, long long Q,
+                           int h, int w, void* stream);
+int raftk_pyramid_untile_f16(const void* const* tiled, float* const* rowmajor, int num_levels, long long Q,
+                             int h, int w, void* stream);
+
 /* Stand-alone form of the reference's grid_sample helper, model.py:24-34 (bilinear sample of an
  * NHWC image at absolute pixel coordinates, each corner zero outside; jax map_coordinates order=1
  * mode='constant').  img (n, h, w, c); grid (n, gh, gw, 2) as (x, y); out (n, gh, gw, c).  Same

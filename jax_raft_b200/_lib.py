@@ -78,6 +78,19 @@ SIGNATURES = {
     "raftk_pyramid_tile": (c_int, [_FloatPtrArray, _FloatPtrArray, c_int, ctypes.c_longlong, c_int, c_int, c_void_p]),
     "raftk_pyramid_untile": (c_int, [_FloatPtrArray, _FloatPtrArray, c_int, ctypes.c_longlong, c_int, c_int, c_void_p]),
     "raftk_convex_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "raftk_corr_pyramid_tiled_f16": (
+        c_int,
+        [c_void_p, c_void_p, _FloatPtrArray, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
+         c_size_t, c_void_p],
+    ),
+    "raftk_corr_lookup_tiled_f16": (
+        c_int,
+        [_FloatPtrArray, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
+    ),
+    "raftk_corr_lookup_tiled_f16_update": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                   c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "raftk_pyramid_tile_f16": (c_int, [_FloatPtrArray, _FloatPtrArray, c_int, ctypes.c_longlong, c_int, c_int, c_void_p]),
+    "raftk_pyramid_untile_f16": (c_int, [_FloatPtrArray, _FloatPtrArray, c_int, ctypes.c_longlong, c_int, c_int, c_void_p]),
 }
 
 _lib = None

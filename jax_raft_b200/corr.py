@@ -62,13 +62,15 @@ class TiledPyramid:
     L2 fetch granule each).  The reference treats the pyramid as an opaque value handed from ``build_pyramid`` to
     ``index_pyramid`` (model.py:530-539), so this is what :class:`CorrBlock` returns by default.
 
-    ``levels[l]`` is a (Q, tiles_y, tiles_x, 4, 4) float32 tensor.  Indexing, iterating or ``dense()`` give the
-    reference's row-major levels (Q, h>>l, w>>l, 1) as copies (``raftk_pyramid_untile``), for inspection and tests.
+    ``levels[l]`` is a (Q, tiles_y, tiles_x, 4, 4) tensor, float32 or — ``storage="fp16"`` — float16 (values rounded
+    once to nearest even when stored).  Indexing, iterating or ``dense()`` give the reference's row-major float32
+    levels (Q, h>>l, w>>l, 1) as copies (``raftk_pyramid_untile[_f16]``), for inspection and tests.
     """
 
     def __init__(self, levels: List[torch.Tensor], q: int, h: int, w: int):
         self.levels = levels
         self.q, self.h, self.w = q, h, w
+        self.storage = "fp16" if levels[0].dtype == torch.float16 else "fp32"
         self._dense = None
 
     @staticmethod
@@ -77,28 +79,31 @@ class TiledPyramid:
         return (q, (lh + 3) // 4, 2 * ((lw + 7) // 8), 4, 4)
 
     @classmethod
-    def empty(cls, q: int, h: int, w: int, num_levels: int, device) -> "TiledPyramid":
+    def empty(cls, q: int, h: int, w: int, num_levels: int, device, storage: str = "fp32") -> "TiledPyramid":
+        assert storage in ("fp32", "fp16")
         lib = _lib.load()
         levels = []
         for l in range(num_levels):
             shape = cls.level_shape(q, h, w, l)
             assert shape[1] * shape[2] * 16 == lib.raftk_pyramid_tiled_slab_floats(h, w, l)
-            levels.append(torch.empty(shape, dtype=torch.float32, device=device))
+            levels.append(torch.empty(shape, dtype=torch.float16 if storage == "fp16" else torch.float32, device=device))
         return cls(levels, q, h, w)
 
     @classmethod
-    def from_dense(cls, levels: Sequence[torch.Tensor]) -> "TiledPyramid":
-        """Row-major levels (Q, h>>l, w>>l[, 1]) -> tiled slabs (``raftk_pyramid_tile``)."""
+    def from_dense(cls, levels: Sequence[torch.Tensor], storage: str = "fp32") -> "TiledPyramid":
+        """Row-major float32 levels (Q, h>>l, w>>l[, 1]) -> tiled slabs (``raftk_pyramid_tile[_f16]``)."""
         levels = [_check_cuda_f32(f"pyramid[{i}]", t) for i, t in enumerate(levels)]
         q, h, w = int(levels[0].shape[0]), int(levels[0].shape[1]), int(levels[0].shape[2])
         for l, t in enumerate(levels):
             assert tuple(t.shape[:3]) == (q, h >> l, w >> l), "levels must be (Q, h>>l, w>>l[, 1])"
-        out = cls.empty(q, h, w, len(levels), levels[0].device)
+        out = cls.empty(q, h, w, len(levels), levels[0].device, storage)
         lib = _lib.load()
+        fn, name = ((lib.raftk_pyramid_tile_f16, "raftk_pyramid_tile_f16") if storage == "fp16"
+                    else (lib.raftk_pyramid_tile, "raftk_pyramid_tile"))
         with torch.cuda.device(levels[0].device):
-            rc = lib.raftk_pyramid_tile(_lib.ptr_array(levels), _lib.ptr_array(out.levels), len(levels), q, h, w,
-                                        _lib.current_stream_ptr(levels[0].device))
-        _lib.check("raftk_pyramid_tile", rc)
+            rc = fn(_lib.ptr_array(levels), _lib.ptr_array(out.levels), len(levels), q, h, w,
+                    _lib.current_stream_ptr(levels[0].device))
+        _lib.check(name, rc)
         _lib.count_launch(len(levels))
         return out
 
@@ -107,10 +112,12 @@ class TiledPyramid:
         out = [torch.empty((self.q, self.h >> l, self.w >> l, 1), dtype=torch.float32, device=dev)
                for l in range(len(self.levels))]
         lib = _lib.load()
+        fn, name = ((lib.raftk_pyramid_untile_f16, "raftk_pyramid_untile_f16") if self.storage == "fp16"
+                    else (lib.raftk_pyramid_untile, "raftk_pyramid_untile"))
         with torch.cuda.device(dev):
-            rc = lib.raftk_pyramid_untile(_lib.ptr_array(self.levels), _lib.ptr_array(out), len(out), self.q, self.h,
-                                          self.w, _lib.current_stream_ptr(dev))
-        _lib.check("raftk_pyramid_untile", rc)
+            rc = fn(_lib.ptr_array(self.levels), _lib.ptr_array(out), len(out), self.q, self.h, self.w,
+                    _lib.current_stream_ptr(dev))
+        _lib.check(name, rc)
         _lib.count_launch(len(out))
         return out
 
@@ -134,12 +141,20 @@ class CorrBlock:
 
     ``layout="tiled"`` (default): ``build_pyramid`` returns a :class:`TiledPyramid` and ``index_pyramid`` reads it
     with the tiled kernels; ``layout="rowmajor"`` keeps the reference's (B*nq, h>>l, w>>l, 1) tensors.  Either way
-    ``index_pyramid`` accepts both kinds (a list of row-major levels goes through the row-major kernels)."""
+    ``index_pyramid`` accepts both kinds (a list of row-major levels goes through the row-major kernels).
 
-    def __init__(self, num_levels: int = 4, radius: int = 4, kernel: str = "tc", layout: str = "tiled"):
+    ``storage="fp16"`` (tiled layout only): the slabs hold float16 — each correlation value rounded once, relative
+    error <= 4.9e-4 (the north-star's bar for correlation values is 1e-3); window indexing, pooling bounds and the
+    lookup's float32 arithmetic are unchanged.  Halves the pyramid's memory and the traffic of both kernels."""
+
+    def __init__(self, num_levels: int = 4, radius: int = 4, kernel: str = "tc", layout: str = "tiled",
+                 storage: str = "fp32"):
         assert 1 <= num_levels <= _lib.MAX_LEVELS
         assert kernel in ("tc", "simt")
         assert layout in ("tiled", "rowmajor")
+        assert storage in ("fp32", "fp16")
+        assert storage == "fp32" or layout == "tiled", "float16 storage exists for the tiled layout only"
+        self.storage = storage
         self.num_levels = num_levels
         self.radius = radius
         self.out_channels = num_levels * (2 * radius + 1) ** 2  # model.py:416
@@ -162,15 +177,17 @@ class CorrBlock:
         if self.layout == "tiled":
             direct = self.kernel == "tc" and self.num_levels <= 4 and d % 64 == 0 and d <= 256
             if not direct:  # configurations the tiled epilogue does not cover: row-major kernels, then convert
-                return TiledPyramid.from_dense(self._build_rowmajor(fmap1, fmap2))
-            pyr = TiledPyramid.empty(b * nq, h, w, self.num_levels, fmap1.device)
+                return TiledPyramid.from_dense(self._build_rowmajor(fmap1, fmap2), self.storage)
+            pyr = TiledPyramid.empty(b * nq, h, w, self.num_levels, fmap1.device, self.storage)
             stream = _lib.current_stream_ptr(fmap1.device)
+            fn, name = ((lib.raftk_corr_pyramid_tiled_f16, "raftk_corr_pyramid_tiled_f16") if self.storage == "fp16"
+                        else (lib.raftk_corr_pyramid_tiled, "raftk_corr_pyramid_tiled"))
             with torch.cuda.device(fmap1.device):
                 nbytes = lib.raftk_corr_pyramid_scratch_bytes(b, nq, h, w, d)
                 scratch = torch.empty((max(nbytes, 1),), dtype=torch.uint8, device=fmap1.device)
-                rc = lib.raftk_corr_pyramid_tiled(fmap1.data_ptr(), fmap2.data_ptr(), _lib.ptr_array(pyr.levels),
-                                                  self.num_levels, b, nq, h, w, d, scratch.data_ptr(), nbytes, stream)
-            _lib.check("raftk_corr_pyramid_tiled", rc)
+                rc = fn(fmap1.data_ptr(), fmap2.data_ptr(), _lib.ptr_array(pyr.levels), self.num_levels, b, nq, h, w, d,
+                        scratch.data_ptr(), nbytes, stream)
+            _lib.check(name, rc)
             _lib.count_launch(2)  # bf16 split + tcgen05 GEMM
             return pyr
         return self._build_rowmajor(fmap1, fmap2)
@@ -213,11 +230,12 @@ class CorrBlock:
         lib = _lib.load()
         if isinstance(corr_pyramid, TiledPyramid):
             assert corr_pyramid.q == q, "pyramid and coords disagree on the number of query pixels"
+            fn, name = ((lib.raftk_corr_lookup_tiled_f16, "raftk_corr_lookup_tiled_f16") if corr_pyramid.storage == "fp16"
+                        else (lib.raftk_corr_lookup_tiled, "raftk_corr_lookup_tiled"))
             with torch.cuda.device(coords.device):
-                rc = lib.raftk_corr_lookup_tiled(_lib.ptr_array(corr_pyramid.levels), self.num_levels, coords.data_ptr(),
-                                                 out.data_ptr(), q, corr_pyramid.h, corr_pyramid.w, self.radius,
-                                                 _lib.current_stream_ptr(coords.device))
-            _lib.check("raftk_corr_lookup_tiled", rc)
+                rc = fn(_lib.ptr_array(corr_pyramid.levels), self.num_levels, coords.data_ptr(), out.data_ptr(), q,
+                        corr_pyramid.h, corr_pyramid.w, self.radius, _lib.current_stream_ptr(coords.device))
+            _lib.check(name, rc)
             _lib.count_launch(1)
             return out
         lv0 = corr_pyramid[0]
@@ -263,7 +281,9 @@ class CorrBlock:
         if tiled:
             assert corr_pyramid.q == q
             h, w, levels = corr_pyramid.h, corr_pyramid.w, corr_pyramid.levels
-            fn, name = lib.raftk_corr_lookup_tiled_update, "raftk_corr_lookup_tiled_update"
+            fn, name = ((lib.raftk_corr_lookup_tiled_f16_update, "raftk_corr_lookup_tiled_f16_update")
+                        if corr_pyramid.storage == "fp16"
+                        else (lib.raftk_corr_lookup_tiled_update, "raftk_corr_lookup_tiled_update"))
         else:
             lv0 = corr_pyramid[0]
             assert lv0.shape[0] == q

@@ -46,6 +46,8 @@
 // Queries with non-finite or |c| > 1e6 coordinates read nothing: their footprints are zeros and the weight
 // arithmetic above yields the reference's 0 (finite c) or NaN (non-finite c).
 
+#include <cuda_fp16.h>
+
 #include "pyramid_tiled.cuh"
 #include "lookup_taps.cuh"
 
@@ -53,8 +55,8 @@ namespace raftk {
 namespace lt {
 
 struct Params {
-  const float* level[4];
-  long long slab[4];  // floats per query slab
+  const void* level[4];  // float32 slabs, or (HALF kernels) float16 slabs of the same tile geometry
+  long long slab[4];     // ELEMENTS per query slab
   int lh[4], lw[4], tx[4];
   const float* coords;
   float* out;
@@ -116,6 +118,8 @@ __device__ __forceinline__ void bulk_store(float* dst, const float* src_smem, ui
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ float load_as_float(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float load_as_float(const __half* p) { return __half2float(__ldg(p)); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -145,7 +149,10 @@ __device__ __forceinline__ void column_taps(const float* Fp, const float* wyp, f
   }
 }
 
-template <int R, int G, int WARPS, int MINB, bool PIPE, bool UPDATE>
+// HALF: the slabs hold float16 (pyramid_tiled.cuh, "float16 storage"): a 4 x 4 tile is 32 bytes, so one LDG.256 brings
+// a whole tile (two per lane and query instead of three half tiles); values are widened to float32 while they are
+// staged, and everything after the staging — weights, taps, stores — is the float32 code path unchanged.
+template <int R, int G, int WARPS, int MINB, bool PIPE, bool UPDATE, bool HALF>
 __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Params p) {
   using X = Geo<R, G>;
   constexpr int S1 = X::S1, FP = X::FP, P = X::P, TILE = X::TILE, NQL = X::NQL;
@@ -162,8 +169,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Pa
   const int lvl = lane >> 3, c4 = 4 * (lane & 3), hi = (lane >> 2) & 1;
   // third round: rows only 2 pairs apart, so the hi = 1 lanes take the chunks two columns over (different banks)
   const int c4x = c4 ^ (hi << 3);
-  const float* const lbase = p.level[lvl];
-  const long long lslab = p.slab[lvl];
+  const char* const lbase = static_cast<const char*>(p.level[lvl]);
+  const long long lslab = p.slab[lvl] * (HALF ? 2 : 4);  // bytes per query slab
   const int llh = p.lh[lvl], llw = p.lw[lvl], ltx = p.tx[lvl];
   // ---- per-lane constants of the tap phase: task T = lane + 32 * pass -> (query-level ql, x offset i)
   // (full passes: one column per lane; remainder pass: column REM_T0 + lane / SPL, y offsets JP * (lane % SPL) ..)
@@ -246,15 +253,36 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Pa
 
   // ---- phase B: half-tile loads of group g into registers: round (qi, j) = this lane's row pair k(j) of
   // footprint (qi, lvl); state: bit 2m = the slot holds footprint rows, bit 2m+1 = ... and was loaded ----
-  float v[3 * G][8];
+  float v[(HALF ? 2 : 3) * G][8];
   unsigned state = 0;
   auto prefetch = [&](int g, const QLRec* rq) {
     state = 0;
 #pragma unroll
     for (int qi = 0; qi < G; ++qi) {
       const int4 o = *reinterpret_cast<const int4*>(&rq[qi * 4 + lvl].bxa);  // bxa, by, xs, far
+      const char* slab = lbase + (size_t)(g * G + qi) * lslab;
+      if (HALF) {
+        // slot (qi, j) = whole tile: tile column c4 / 4, tile row 2 * j + hi of the footprint's 4 x 4 tile block
+        const int ys = o.y & 3;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int m = qi * 2 + j;
+          const int tyr = 2 * j + hi;
+          const int gx = o.x + c4;
+          const bool xneed = c4 <= o.z + FP - 1;
+          const bool xin = !o.w && (unsigned)gx < (unsigned)llw;
+          const int gy = o.y - ys + 4 * tyr;
+          const bool need = xneed && 4 * tyr <= FP - 1 + ys;
+          const bool ld = need && xin && (unsigned)gy < (unsigned)llh;
+          if (need) state |= 1u << (2 * m);
+          if (ld) {
+            state |= 2u << (2 * m);
+            ldg256_hint(reinterpret_cast<const float*>(slab + ((size_t)((gy >> 2) * ltx + (gx >> 2))) * 32), v[m], pol);
+          }
+        }
+        continue;
+      }
       const int ys = o.y & 1;
-      const float* slab = lbase + (size_t)(g * G + qi) * lslab;
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         const int m = qi * 3 + j;
@@ -269,7 +297,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Pa
         if (need) state |= 1u << (2 * m);
         if (ld) {
           state |= 2u << (2 * m);
-          ldg256_hint(slab + ((gy >> 2) * ltx + (gx >> 2)) * 16 + (gy & 2) * 4, v[m], pol);
+          ldg256_hint(reinterpret_cast<const float*>(slab + ((size_t)(((gy >> 2) * ltx + (gx >> 2)) * 16 + (gy & 2) * 4)) * 4), v[m],
+                      pol);
         }
       }
     }
@@ -280,8 +309,26 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Pa
   auto stage = [&](const QLRec* rq) {
 #pragma unroll
     for (int qi = 0; qi < G; ++qi) {
-      const int ys = rq[qi * 4 + lvl].by & 1;
       float* tile = F + (qi * 4 + lvl) * TILE;
+      if (HALF) {
+        const int ys = rq[qi * 4 + lvl].by & 3;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int m = qi * 2 + j;
+          const int r0 = 4 * (2 * j + hi) - ys;
+          const bool need = (state >> (2 * m)) & 1u, ld = (state >> (2 * m + 1)) & 1u;
+          float* t = tile + r0 * P + c4;
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr) {  // tile row rr = 4 halves = words 2 rr, 2 rr + 1
+            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v[m][2 * rr]));
+            const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&v[m][2 * rr + 1]));
+            const float4 val = ld ? make_float4(a.x, a.y, b.x, b.y) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (need && (unsigned)(r0 + rr) < (unsigned)FP) *reinterpret_cast<float4*>(t + rr * P) = val;
+          }
+        }
+        continue;
+      }
+      const int ys = rq[qi * 4 + lvl].by & 1;
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         const int m = qi * 3 + j;
@@ -393,7 +440,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Pa
 // ---- generic path over tiled slabs (any radius <= 7, <= RAFTK_MAX_LEVELS levels): one warp per query, scalar
 // staged footprints, the tap code of corr_lookup.cu ----
 struct GenericParams {
-  const float* level[RAFTK_MAX_LEVELS];
+  const void* level[RAFTK_MAX_LEVELS];
   long long slab[RAFTK_MAX_LEVELS];
   int lh[RAFTK_MAX_LEVELS], lw[RAFTK_MAX_LEVELS], tx[RAFTK_MAX_LEVELS];
   const float* coords;
@@ -401,6 +448,7 @@ struct GenericParams {
   int Q, L, r;
 };
 
+template <typename T>
 __global__ void __launch_bounds__(256) lookup_tiled_generic_kernel(const GenericParams p) {
   extern __shared__ float smem[];
   const int r = p.r, S = 2 * r + 1, FP = 2 * r + 2;
@@ -413,13 +461,13 @@ __global__ void __launch_bounds__(256) lookup_tiled_generic_kernel(const Generic
   for (int l = 0; l < p.L; ++l, sc *= 0.5f) {
     const int lh = p.lh[l], lw = p.lw[l], tx = p.tx[l];
     const int bx = clamp_to_int(floorf(cx * sc)) - r, by = clamp_to_int(floorf(cy * sc)) - r;
-    const float* slab = p.level[l] + (size_t)q * p.slab[l];
+    const T* slab = static_cast<const T*>(p.level[l]) + (size_t)q * p.slab[l];
     float* Fl = F + l * FP * FP;
     for (int e = lane; e < FP * FP; e += 32) {
       const int ry = e / FP, rx = e - ry * FP;
       const int gy = by + ry, gx = bx + rx;
       float val = 0.0f;
-      if ((unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) val = __ldg(slab + tiled_offset(gy, gx, tx));
+      if ((unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) val = load_as_float(slab + tiled_offset(gy, gx, tx));
       Fl[e] = val;
     }
   }
@@ -443,12 +491,12 @@ struct raftk_tiled_update_args {
 
 namespace {
 
-template <int R, int G, int WARPS, int MINB, bool PIPE, bool UPDATE>
+template <int R, int G, int WARPS, int MINB, bool PIPE, bool UPDATE, bool HALF>
 int launch_fast(const raftk::lt::Params& p, cudaStream_t s) {
   using namespace raftk;
   using X = lt::Geo<R, G>;
   const size_t smem = (size_t)(WARPS * X::WARP_FLOATS) * sizeof(float);
-  auto kernel = lt::lookup_tiled_kernel<R, G, WARPS, MINB, PIPE, UPDATE>;
+  auto kernel = lt::lookup_tiled_kernel<R, G, WARPS, MINB, PIPE, UPDATE, HALF>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return static_cast<int>(e);
@@ -460,30 +508,20 @@ int launch_fast(const raftk::lt::Params& p, cudaStream_t s) {
   return launch_pdl(kernel, blocks, WARPS * 32, smem, s, p);
 }
 
-// 0: the default; otherwise a tuning variant (RAFTK_LOOKUP_VARIANT, read once)
-int lookup_variant() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("RAFTK_LOOKUP_VARIANT");
-    v = e ? atoi(e) : 0;
-  }
-  return v;
-}
-
-template <int R, bool UPDATE>
+// two queries per warp, 4 warps per block, 4 blocks per SM (128 registers), software-pipelined; the schedules this
+// was chosen against are in the file header
+template <int R, bool UPDATE, bool HALF>
 int launch_fast_r(const raftk::lt::Params& p, cudaStream_t s) {
-  switch (lookup_variant()) {  // A/B variants behind the numbers in DESIGN.md §4.2
-    case 1: return launch_fast<R, 2, 4, 3, true, UPDATE>(p, s);   // 3 blocks per SM (more registers)
-    case 2: return launch_fast<R, 2, 4, 5, false, UPDATE>(p, s);  // no software pipeline, 5 blocks per SM
-    case 3: return launch_fast<R, 1, 4, 8, true, UPDATE>(p, s);   // one query per warp, 8 blocks per SM
-    default: break;
-  }
-  // two queries per warp, 4 warps per block, 4 blocks per SM (128 registers), software-pipelined
-  return launch_fast<R, 2, 4, 4, true, UPDATE>(p, s);
+  return launch_fast<R, 2, 4, 4, true, UPDATE, HALF>(p, s);
 }
 
-int lookup_tiled_launch(const float* const* levels, int num_levels, const float* coords, float* out, int Q, int h, int w,
-                        int radius, const raftk_tiled_update_args* upd, void* stream) {
+template <bool UPDATE, bool HALF>
+int launch_fast_rh(const raftk::lt::Params& p, int radius, cudaStream_t s) {
+  return radius == 4 ? launch_fast_r<4, UPDATE, HALF>(p, s) : launch_fast_r<3, UPDATE, HALF>(p, s);
+}
+
+int lookup_tiled_launch(const void* const* levels, int num_levels, const float* coords, float* out, int Q, int h, int w,
+                        int radius, const raftk_tiled_update_args* upd, void* stream, bool half) {
   using namespace raftk;
   if (Q < 0 || h <= 0 || w <= 0 || radius < 0 || num_levels < 1 || num_levels > RAFTK_MAX_LEVELS) return RAFTK_ERR_SHAPE;
   if ((h >> (num_levels - 1)) < 1 || (w >> (num_levels - 1)) < 1) return RAFTK_ERR_TOO_SMALL;
@@ -514,7 +552,10 @@ int lookup_tiled_launch(const float* const* levels, int num_levels, const float*
     g.r = radius;
     const int FP = 2 * radius + 2;
     const size_t smem = (size_t)8 * num_levels * FP * FP * sizeof(float);
-    lt::lookup_tiled_generic_kernel<<<(Q + 7) / 8, 256, smem, s>>>(g);
+    if (half)
+      lt::lookup_tiled_generic_kernel<__half><<<(Q + 7) / 8, 256, smem, s>>>(g);
+    else
+      lt::lookup_tiled_generic_kernel<float><<<(Q + 7) / 8, 256, smem, s>>>(g);
     return launch_status();
   }
   lt::Params p{};
@@ -537,22 +578,13 @@ int lookup_tiled_launch(const float* const* levels, int num_levels, const float*
     p.flow = upd->flow;
     p.flow_pitched = upd->flow_pitched;
     p.ld_flow = upd->ld_flow;
-    return radius == 4 ? launch_fast_r<4, true>(p, s) : launch_fast_r<3, true>(p, s);
+    return half ? launch_fast_rh<true, true>(p, radius, s) : launch_fast_rh<true, false>(p, radius, s);
   }
-  return radius == 4 ? launch_fast_r<4, false>(p, s) : launch_fast_r<3, false>(p, s);
+  return half ? launch_fast_rh<false, true>(p, radius, s) : launch_fast_rh<false, false>(p, radius, s);
 }
 
-}  // namespace
-
-extern "C" int raftk_corr_lookup_tiled(const float* const* levels, int num_levels, const float* coords, float* out, int Q,
-                                       int h, int w, int radius, void* stream) {
-  return lookup_tiled_launch(levels, num_levels, coords, out, Q, h, w, radius, nullptr, stream);
-}
-
-extern "C" int raftk_corr_lookup_tiled_update(const float* const* levels, int num_levels, const float* delta_pre,
-                                              int ld_delta, const float* bias, const float* coords0, float* coords1,
-                                              float* flow, float* flow_pitched, int ld_flow, float* out, int Q, int h,
-                                              int w, int radius, void* stream) {
+int check_update_args(const float* delta_pre, int ld_delta, const float* bias, const float* coords0, float* coords1,
+                      float* flow, float* flow_pitched, int ld_flow, int Q) {
   if (Q > 0) {
     if (!delta_pre || !bias || !coords0 || !coords1 || !flow) return RAFTK_ERR_NULL;
     if (ld_delta < 2 || ld_delta % 2 || (flow_pitched && (ld_flow < 2 || ld_flow % 2))) return RAFTK_ERR_SHAPE;
@@ -560,6 +592,39 @@ extern "C" int raftk_corr_lookup_tiled_update(const float* const* levels, int nu
          (uintptr_t)flow_pitched) & 7)
       return RAFTK_ERR_ALIGN;
   }
+  return RAFTK_OK;
+}
+
+}  // namespace
+
+extern "C" int raftk_corr_lookup_tiled(const float* const* levels, int num_levels, const float* coords, float* out, int Q,
+                                       int h, int w, int radius, void* stream) {
+  return lookup_tiled_launch(reinterpret_cast<const void* const*>(levels), num_levels, coords, out, Q, h, w, radius, nullptr,
+                             stream, false);
+}
+
+extern "C" int raftk_corr_lookup_tiled_update(const float* const* levels, int num_levels, const float* delta_pre,
+                                              int ld_delta, const float* bias, const float* coords0, float* coords1,
+                                              float* flow, float* flow_pitched, int ld_flow, float* out, int Q, int h,
+                                              int w, int radius, void* stream) {
+  const int rc = check_update_args(delta_pre, ld_delta, bias, coords0, coords1, flow, flow_pitched, ld_flow, Q);
+  if (rc != RAFTK_OK) return rc;
   const raftk_tiled_update_args upd{delta_pre, ld_delta, bias, coords0, coords1, flow, flow_pitched, ld_flow};
-  return lookup_tiled_launch(levels, num_levels, coords1, out, Q, h, w, radius, &upd, stream);
+  return lookup_tiled_launch(reinterpret_cast<const void* const*>(levels), num_levels, coords1, out, Q, h, w, radius, &upd,
+                             stream, false);
+}
+
+extern "C" int raftk_corr_lookup_tiled_f16(const void* const* levels, int num_levels, const float* coords, float* out, int Q,
+                                           int h, int w, int radius, void* stream) {
+  return lookup_tiled_launch(levels, num_levels, coords, out, Q, h, w, radius, nullptr, stream, true);
+}
+
+extern "C" int raftk_corr_lookup_tiled_f16_update(const void* const* levels, int num_levels, const float* delta_pre,
+                                                  int ld_delta, const float* bias, const float* coords0, float* coords1,
+                                                  float* flow, float* flow_pitched, int ld_flow, float* out, int Q, int h,
+                                                  int w, int radius, void* stream) {
+  const int rc = check_update_args(delta_pre, ld_delta, bias, coords0, coords1, flow, flow_pitched, ld_flow, Q);
+  if (rc != RAFTK_OK) return rc;
+  const raftk_tiled_update_args upd{delta_pre, ld_delta, bias, coords0, coords1, flow, flow_pitched, ld_flow};
+  return lookup_tiled_launch(levels, num_levels, coords1, out, Q, h, w, radius, &upd, stream, true);
 }

@@ -42,6 +42,7 @@
 #include <cuda.h>
 #include <cstring>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "raftk_common.cuh"
 #include "pyramid_tiled.cuh"
@@ -66,7 +67,7 @@ constexpr int NUM_THREADS = 128 + 32 * NUM_EPI_WARPS;
 constexpr int SMEM_LIMIT = 232448;  // 227 KB
 
 struct Params {
-  float* level[4];
+  void* level[4];  // float32 (row-major or tiled) or, OUT_TILED_F16, float16 tiled slabs
   int lh[4], lw[4];
   int vec_ok[4];  // level row pitch and base allow 16-byte stores
   int ltx[4], lty[4];   // tiled layout: tiles per tile row / tile rows of each level
@@ -374,6 +375,34 @@ __device__ __forceinline__ void emit_pair(float* S, const float* v, const CUtens
   }
 }
 
+// eight float32 -> eight float16 (round to nearest even), 16 bytes
+__device__ __forceinline__ uint4 pack8_f16(const float* v) {
+  const __half2 a = __floats2half2_rn(v[0], v[1]), b = __floats2half2_rn(v[2], v[3]);
+  const __half2 c = __floats2half2_rn(v[4], v[5]), d = __floats2half2_rn(v[6], v[7]);
+  return make_uint4(*reinterpret_cast<const unsigned*>(&a), *reinterpret_cast<const unsigned*>(&b),
+                    *reinterpret_cast<const unsigned*>(&c), *reinterpret_cast<const unsigned*>(&d));
+}
+
+// float16 slabs: stage 64 values per lane (lane = query: four adjacent 4x4 tiles = 128 contiguous bytes of its slab,
+// v0 = tiles 0-1, v1 = tiles 2-3) in the warp's swizzled staging tile and send them as ONE bulk tensor store: tile
+// pairs `pair`, `pair` + 1 of tile row `trow`, queries [m_first, m_first + 32) of pair b.  The tensor map
+// (32 halves = tile pair, tile pairs, tile rows, query, pair; box {32, 2, 1, 32, 1}) clips what does not exist.
+__device__ __forceinline__ void emit_quad_f16(float* S, const float* v0, const float* v1, const CUtensorMap* tm, int b,
+                                              int m_first, int pair, int trow, int lane) {
+  if (lane == 0) bulk_wait_read_all();  // the previous store may still be reading S
+  __syncwarp();
+  // dense [query][128 B] (the tensor map is unswizzled: with a 64-byte inner box the 128-byte swizzle does not map to
+  // a per-query XOR); same-chunk stores of 8 lanes share 4 banks, 256 cycles per emit against the ~2400 of its wait
+#pragma unroll
+  for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(S + lane * 32 + c * 4) = pack8_f16((c < 4 ? v0 : v1) + 8 * (c & 3));
+  fence_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_5d(tm, S, 0, pair, trow, m_first, b);
+    bulk_commit();
+  }
+}
+
 // 2x2 pooling of a 4x4 block stored row-major with pitch 4 -> its 2x2 result (pitch `op`), the reference's
 // order ((a+b)+(c+d))/4
 __device__ __forceinline__ void pool_tile(const float* t, float* out, int op) {
@@ -394,12 +423,18 @@ __device__ __forceinline__ void pool_tile(const float* t, float* out, int op) {
 // TILED: the accumulator columns are in tile order (target pixel (y, x) of the patch at column
 // (y>>2)*128 + (x>>2)*16 + (y&3)*4 + (x&3)): the producer fetches the patch as 4x4-pixel boxes, one per tile, and
 // the epilogue writes the tiled slabs of pyramid_tiled.cuh.
-template <int CG, bool TILED>
+// OUT_TILED_F16: the tiled slabs hold float16 (round-to-nearest-even of the float32 values; every level is pooled in
+// float32 from the unrounded level below and rounded once).  Level 0 leaves as 32 queries x 128 B (four tiles) per
+// bulk tensor store — two per accumulator and warp instead of four — and the small levels as plain 16/64-byte stores.
+enum { OUT_ROWMAJOR = 0, OUT_TILED = 1, OUT_TILED_F16 = 2 };
+
+template <int CG, int OUT>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
                        const __grid_constant__ CUtensorMap tmO2, const __grid_constant__ CUtensorMap tmO3,
                        const Params p) {
+  constexpr bool TILED = OUT != OUT_ROWMAJOR;
   constexpr int kBStage = B_STAGE_BYTES / CG;  // bytes of one B stage held by this CTA
   const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
   const bool leader = rank == 0;
@@ -599,10 +634,10 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     // bar_ready: "upper row written".
     float* X = reinterpret_cast<float*>(smem_stage + (4 + quarter) * STAGING_PER_WARP) + 768;
     const int bar_ready = 1 + quarter, bar_free = 5 + quarter;
-    const LevelDst dst[4] = {{&tmO0, p.level[0], p.lh[0], p.lw[0], p.vec_ok[0] != 0},
-                             {&tmO1, p.level[1], p.lh[1], p.lw[1], p.vec_ok[1] != 0},
-                             {&tmO2, p.level[2], p.lh[2], p.lw[2], p.vec_ok[2] != 0},
-                             {&tmO3, p.level[3], p.lh[3], p.lw[3], p.vec_ok[3] != 0}};
+    const LevelDst dst[4] = {{&tmO0, static_cast<float*>(p.level[0]), p.lh[0], p.lw[0], p.vec_ok[0] != 0},
+                             {&tmO1, static_cast<float*>(p.level[1]), p.lh[1], p.lw[1], p.vec_ok[1] != 0},
+                             {&tmO2, static_cast<float*>(p.level[2]), p.lh[2], p.lw[2], p.vec_ok[2] != 0},
+                             {&tmO3, static_cast<float*>(p.level[3]), p.lh[3], p.lw[3], p.vec_ok[3] != 0}};
     int buf = 0;
     uint32_t acc_phase = 0;
     for (int pair_b = 0; pair_b < p.B; ++pair_b)
@@ -615,6 +650,98 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
       mbar_wait(&acc_full[buf], acc_phase);
       tc_fence_after();
+      if (OUT == OUT_TILED_F16) {
+        // half = which four tile columns (16 target columns) of the patch this warp owns, both tile rows
+        const uint32_t tcol = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 64);
+        const bool last_row = y0 + PH >= p.h;
+        const int q = m0 + lane;
+        float l1t[2][16];  // this warp's two level-1 tiles, [u][cy * 4 + cx]
+#pragma unroll
+        for (int ty = 0; ty < 2; ++ty) {
+          float a[2][32];  // tile row ty: tiles 4*half + 0, 1 and + 2, 3
+          tmem_ld_32x32(tcol + ty * 128, a[0]);
+          tmem_ld_32x32(tcol + ty * 128 + 32, a[1]);
+          tmem_ld_wait();
+          if (ty == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (CG == 1) mbar_arrive(&acc_empty[buf]);
+              else mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[buf]), 0));
+            }
+          }
+          const int pair0 = (x0 >> 3) + 2 * half, trow = (y0 >> 2) + ty;
+          if (pair0 * 2 < p.ltx[0] && trow < p.lty[0]) emit_quad_f16(S, a[0], a[1], &tmO0, b, m0, pair0, trow, lane);
+          if (p.L > 1) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+              for (int t = 0; t < 2; ++t) pool_tile(a[u] + t * 16, l1t[u] + (2 * ty) * 4 + 2 * t, 4);
+          }
+        }
+        if (p.L > 1) {
+          // level 1: rows (y0>>1) + 0..3, columns (x0>>1) + 8*half + 4u + 0..3 = tiles 2*half + u of tile row y0>>3:
+          // 64 contiguous bytes per query; cells past the level are zero
+          const int ry1 = p.lh[1] - (y0 >> 1), rx1 = p.lw[1] - ((x0 >> 1) + 8 * half);
+          if (ry1 < 4 || rx1 < 8) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+              for (int cy = 0; cy < 4; ++cy)
+#pragma unroll
+                for (int cx = 0; cx < 4; ++cx)
+                  if (cy >= ry1 || 4 * u + cx >= rx1) l1t[u][cy * 4 + cx] = 0.0f;
+          }
+          if (q < p.nq && rx1 > 0 && ry1 > 0) {
+            __half* t1 = static_cast<__half*>(p.level[1]) + ((long long)b * p.nq + q) * p.lslab[1] +
+                         ((long long)(y0 >> 3) * p.ltx[1] + (x0 >> 3) + 2 * half) * 16;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(t1 + 8 * c) = pack8_f16(&l1t[0][0] + 8 * c);
+          }
+        }
+        if (p.L > 2) {
+          // level 2: rows (y0>>2) + r, columns (x0>>2) + 4*half + c -> rows rt2, rt2 + 1 of one tile: 16 contiguous bytes
+          float l2[2][4];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) pool_tile(l1t[u], &l2[0][2 * u], 4);
+          const int ry2 = p.lh[2] - (y0 >> 2), rx2 = p.lw[2] - ((x0 >> 2) + 4 * half);
+#pragma unroll
+          for (int r = 0; r < 2; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              if (r >= ry2 || c >= rx2) l2[r][c] = 0.0f;
+          const int tcol2 = (x0 >> 4) + half, trow2 = y0 >> 4, rt2 = (y0 >> 2) & 3;
+          if (q < p.nq && rx2 > 0 && trow2 * 4 < p.lh[2]) {  // the tile holds valid cells
+            __half* t2 = static_cast<__half*>(p.level[2]) + ((long long)b * p.nq + q) * p.lslab[2] +
+                         ((long long)trow2 * p.ltx[2] + tcol2) * 16;
+            *reinterpret_cast<uint4*>(t2 + rt2 * 4) = pack8_f16(&l2[0][0]);
+            if (last_row && rt2 == 0) *reinterpret_cast<uint4*>(t2 + 8) = make_uint4(0u, 0u, 0u, 0u);  // padding rows
+          }
+          if (p.L > 3) {
+            // level 3: row y0>>3, columns (x0>>3) + 2*half + c -> 4 bytes of a tile row
+            const int ry3 = p.lh[3] - (y0 >> 3), rx3 = p.lw[3] - ((x0 >> 3) + 2 * half);
+            float l3[2];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              l3[c] = __fadd_rn(__fadd_rn(l2[0][2 * c], l2[0][2 * c + 1]), __fadd_rn(l2[1][2 * c], l2[1][2 * c + 1])) * 0.25f;
+              if (ry3 < 1 || c >= rx3) l3[c] = 0.0f;
+            }
+            const int tcol3 = x0 >> 5, trow3 = y0 >> 5, rt3 = (y0 >> 3) & 3;
+            if (q < p.nq && tcol3 * 4 < p.lw[3] && trow3 * 4 < p.lh[3]) {  // the tile holds valid cells
+              __half* t3 = static_cast<__half*>(p.level[3]) + ((long long)b * p.nq + q) * p.lslab[3] +
+                           ((long long)trow3 * p.ltx[3] + tcol3) * 16 + 2 * half;
+              *reinterpret_cast<__half2*>(t3 + rt3 * 4) = __floats2half2_rn(l3[0], l3[1]);
+              if (last_row)  // no patch below: the rest of the tile is padding
+                for (int r = rt3 + 1; r < 4; ++r) *reinterpret_cast<__half2*>(t3 + r * 4) = __floats2half2_rn(0.0f, 0.0f);
+            }
+          }
+        }
+        if (++buf == 2) {
+          buf = 0;
+          acc_phase ^= 1;
+        }
+        continue;
+      }
       if (TILED) {
         // half = which four tile columns (16 target columns) of the patch this warp owns, both tile rows
         const uint32_t tcol = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 64);
@@ -674,7 +801,7 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           const int q = m0 + lane;
           const int tcol2 = (x0 >> 4) + half, trow2 = y0 >> 4, rt2 = (y0 >> 2) & 3;
           if (q < p.nq && rx2 > 0 && trow2 * 4 < p.lh[2]) {  // the tile holds valid cells
-            float* t2 = p.level[2] + ((long long)b * p.nq + q) * p.lslab[2] + ((long long)trow2 * p.ltx[2] + tcol2) * 16;
+            float* t2 = static_cast<float*>(p.level[2]) + ((long long)b * p.nq + q) * p.lslab[2] + ((long long)trow2 * p.ltx[2] + tcol2) * 16;
             *reinterpret_cast<float4*>(t2 + rt2 * 4) = make_float4(l2[0][0], l2[0][1], l2[0][2], l2[0][3]);
             *reinterpret_cast<float4*>(t2 + rt2 * 4 + 4) = make_float4(l2[1][0], l2[1][1], l2[1][2], l2[1][3]);
             if (last_row && rt2 == 0) {  // no patch below: the tile's lower half is padding
@@ -693,7 +820,7 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             }
             const int tcol3 = x0 >> 5, trow3 = y0 >> 5, rt3 = (y0 >> 3) & 3;
             if (q < p.nq && tcol3 * 4 < p.lw[3] && trow3 * 4 < p.lh[3]) {  // the tile holds valid cells
-              float* t3 = p.level[3] + ((long long)b * p.nq + q) * p.lslab[3] + ((long long)trow3 * p.ltx[3] + tcol3) * 16 +
+              float* t3 = static_cast<float*>(p.level[3]) + ((long long)b * p.nq + q) * p.lslab[3] + ((long long)trow3 * p.ltx[3] + tcol3) * 16 +
                           2 * half;
               *reinterpret_cast<float2*>(t3 + rt3 * 4) = make_float2(l3[0], l3[1]);
               if (last_row)  // no patch below: the rest of the tile is padding
@@ -814,11 +941,12 @@ extern "C" size_t raftk_corr_pyramid_scratch_bytes(int B, int nq, int h, int w, 
   return raftk::tc::scratch_bytes(B, nq, h, w, D);
 }
 
-static int corr_pyramid_impl(const float* fmap1, const float* fmap2, float* const* levels, int num_levels, int B, int nq,
-                             int h, int w, int D, void* scratch, size_t scratch_bytes, void* stream, bool tiled) {
+static int corr_pyramid_impl(const float* fmap1, const float* fmap2, void* const* levels, int num_levels, int B, int nq,
+                             int h, int w, int D, void* scratch, size_t scratch_bytes, void* stream, int out_mode) {
   using namespace raftk;
   using namespace raftk::tc;
-  int rc = check_pyramid_args(fmap1, fmap2, levels, num_levels, B, nq, h, w, D);
+  const bool tiled = out_mode != OUT_ROWMAJOR;
+  int rc = check_pyramid_args(fmap1, fmap2, reinterpret_cast<float* const*>(levels), num_levels, B, nq, h, w, D);
   if (rc != RAFTK_OK) return rc;
   if (B == 0 || nq == 0) return RAFTK_OK;
   if (tiled) {
@@ -830,7 +958,8 @@ static int corr_pyramid_impl(const float* fmap1, const float* fmap2, float* cons
   }
   // Feature widths the tensor-core tiling does not cover (D not a multiple of 64, or an A tile
   // larger than shared memory) take the fp32 FMA kernels: same contract, no scratch.
-  if (!supported(D)) return raftk_corr_pyramid_simt(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, stream);
+  if (!supported(D))
+    return raftk_corr_pyramid_simt(fmap1, fmap2, reinterpret_cast<float* const*>(levels), num_levels, B, nq, h, w, D, stream);
   const size_t need = tc::scratch_bytes(B, nq, h, w, D);
   if (!scratch || scratch_bytes < need) return RAFTK_ERR_SCRATCH;
   if (((uintptr_t)scratch & 255) || ((uintptr_t)fmap1 & 15) || ((uintptr_t)fmap2 & 15)) return RAFTK_ERR_ALIGN;
@@ -894,7 +1023,17 @@ static int corr_pyramid_impl(const float* fmap1, const float* fmap2, float* cons
     p.lty[l] = tiled_tiles_y(h >> l);
     p.lslab[l] = tiled_slab_floats(h >> l, w >> l);
   }
-  if (tiled) {
+  if (out_mode == OUT_TILED_F16) {
+    // level 0 leaves through bulk tensor stores: (32 halves = tile pair, pairs per tile row, tile rows, query, pair),
+    // two pairs (128 B per query) per store
+    const cuuint64_t dims[5] = {32, (cuuint64_t)p.ltx[0] / 2, (cuuint64_t)p.lty[0], (cuuint64_t)nq, (cuuint64_t)B};
+    const cuuint64_t strides[4] = {64, (cuuint64_t)p.ltx[0] * 32, (cuuint64_t)p.lslab[0] * 2, (cuuint64_t)nq * p.lslab[0] * 2};
+    const cuuint32_t box[5] = {32, 2, 1, 32, 1};
+    const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    if (encode(&tmO[0], CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 5, levels[0], dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return RAFTK_ERR_UNSUPPORTED;
+  } else if (tiled) {
     // levels 0 and 1 leave through bulk tensor stores: (32 floats = tile pair, pairs per tile row, tile rows, query, pair)
     for (int l = 0; l < p.L && l < 2; ++l) {
       const cuuint64_t dims[5] = {32, (cuuint64_t)p.ltx[l] / 2, (cuuint64_t)p.lty[l], (cuuint64_t)nq, (cuuint64_t)B};
@@ -940,8 +1079,10 @@ static int corr_pyramid_impl(const float* fmap1, const float* fmap2, float* cons
   const long long max_units = RAFTK_SM_COUNT / CG;
   const long long tiles_per_pair = (long long)p.m_tiles * p.n_tiles;
   const int units = (int)(tiles_per_pair < max_units ? tiles_per_pair : max_units);
-  auto kernel = tiled ? (CG == 2 ? corr_pyramid_tc_kernel<2, true> : corr_pyramid_tc_kernel<1, true>)
-                      : (CG == 2 ? corr_pyramid_tc_kernel<2, false> : corr_pyramid_tc_kernel<1, false>);
+  auto kernel = out_mode == OUT_TILED_F16
+                    ? (CG == 2 ? corr_pyramid_tc_kernel<2, OUT_TILED_F16> : corr_pyramid_tc_kernel<1, OUT_TILED_F16>)
+                    : tiled ? (CG == 2 ? corr_pyramid_tc_kernel<2, OUT_TILED> : corr_pyramid_tc_kernel<1, OUT_TILED>)
+                            : (CG == 2 ? corr_pyramid_tc_kernel<2, OUT_ROWMAJOR> : corr_pyramid_tc_kernel<1, OUT_ROWMAJOR>);
   // per-device attribute; cheap enough to set on every call (keeps the library stateless)
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT) != cudaSuccess)
     return launch_status();
@@ -962,20 +1103,30 @@ static int corr_pyramid_impl(const float* fmap1, const float* fmap2, float* cons
   rc = launch_status();
   if (rc != RAFTK_OK) return rc;
   // levels beyond the 8x32 patch's reach (only if a caller asks for more than 4)
-  if (num_levels > 4) return launch_pool_levels(levels, 4, num_levels, (long long)B * nq, h, w, s);
+  if (num_levels > 4)
+    return launch_pool_levels(reinterpret_cast<float* const*>(levels), 4, num_levels, (long long)B * nq, h, w, s);
   return RAFTK_OK;
 }
 
 extern "C" int raftk_corr_pyramid(const float* fmap1, const float* fmap2, float* const* levels, int num_levels,
                                   int B, int nq, int h, int w, int D, void* scratch, size_t scratch_bytes,
                                   void* stream) {
-  return corr_pyramid_impl(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, scratch, scratch_bytes, stream, false);
+  return corr_pyramid_impl(fmap1, fmap2, reinterpret_cast<void* const*>(levels), num_levels, B, nq, h, w, D, scratch,
+                           scratch_bytes, stream, raftk::tc::OUT_ROWMAJOR);
 }
 
 extern "C" int raftk_corr_pyramid_tiled(const float* fmap1, const float* fmap2, float* const* levels, int num_levels,
                                         int B, int nq, int h, int w, int D, void* scratch, size_t scratch_bytes,
                                         void* stream) {
-  return corr_pyramid_impl(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, scratch, scratch_bytes, stream, true);
+  return corr_pyramid_impl(fmap1, fmap2, reinterpret_cast<void* const*>(levels), num_levels, B, nq, h, w, D, scratch,
+                           scratch_bytes, stream, raftk::tc::OUT_TILED);
+}
+
+extern "C" int raftk_corr_pyramid_tiled_f16(const float* fmap1, const float* fmap2, void* const* levels, int num_levels,
+                                            int B, int nq, int h, int w, int D, void* scratch, size_t scratch_bytes,
+                                            void* stream) {
+  return corr_pyramid_impl(fmap1, fmap2, levels, num_levels, B, nq, h, w, D, scratch, scratch_bytes, stream,
+                           raftk::tc::OUT_TILED_F16);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -2,7 +2,7 @@
 one (raftk_corr_lookup_tiled): 8 coordinate sets in rotation so consecutive launches do not find their footprints
 in L2, (a) back to back in a graph of 8 launches (throughput) and (b) one launch at a time between events
 (the inputs are far larger than L2 from batch 4 up; nothing is written to flush it).
-    python profiles/lookup_time.py [batch ...]        RAFTK_LOOKUP_VARIANT=n selects a tuning variant"""
+    python profiles/lookup_time.py [batch ...]        (fractions on the float32 accounting: 2904 B per query)"""
 import os
 import sys
 
@@ -23,14 +23,15 @@ for b in [int(x) for x in (sys.argv[1:] or ["1", "16"])]:
               for _ in range(8)]
     cb = J.CorrBlock(4, r)
     tiled = TiledPyramid.from_dense(dense)
+    tiled16 = TiledPyramid.from_dense(dense, storage="fp16")
     ref = None
-    for name, pyr in (("row-major", dense), ("tiled", tiled)):
+    for name, pyr in (("row-major", dense), ("tiled", tiled), ("tiled f16", tiled16)):
         for c in coords:
             out = cb.index_pyramid(pyr, c)
         torch.cuda.synchronize()
         if ref is None:
             ref = out.clone()
-        else:
+        elif name != "tiled f16":
             assert bool(((out == ref) | (out.isnan() & ref.isnan())).all()), "tiled and row-major lookups differ"
         graph = torch.cuda.CUDAGraph()
         s = torch.cuda.Stream()
@@ -61,4 +62,4 @@ for b in [int(x) for x in (sys.argv[1:] or ["1", "16"])]:
         print(f"B={b:3d} {name:9s}: back to back {best * 1e3:7.2f} us = {alg / best / 1e6:5.0f} GB/s ({alg / best / 1e6 / PEAK:.3f} of peak);"
               f"  single launch between events {single * 1e3:7.2f} us = {alg / single / 1e6:5.0f} GB/s ({alg / single / 1e6 / PEAK:.3f})",
               flush=True)
-    del dense, tiled
+    del dense, tiled, tiled16
