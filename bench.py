@@ -345,7 +345,15 @@ def lookup_bytes_per_query(r: int = 4, L: int = 4) -> int:
     return L * (2 * r + 2) ** 2 * 4 + 8 + L * (2 * r + 1) ** 2 * 4
 
 
-def lookup_back_to_back(torch, J, dev, hbm_gbs, batch, h=H // 8, w=W // 8):
+def f16_accounting(queries, ms, hbm_gbs, r=4, L=4):
+    """The float16-storage lookup on its OWN bytes (footprints read as 2-byte values: L*(2r+2)^2*2 + 8 read,
+    L*(2r+1)^2*4 written = 2104 B at r = 4); `frac_of_hbm_peak` beside it keeps SURVEY.md §8d's float32 figure, i.e.
+    the traffic of the reference's computation that the launch replaces."""
+    own = queries * (L * (2 * r + 2) ** 2 * 2 + 8 + L * (2 * r + 1) ** 2 * 4)
+    return {"own_algorithmic_bytes": own, "own_hbm_gbs": own / (ms * 1e-3) / 1e9, "own_frac_of_hbm_peak": own / (ms * 1e-3) / 1e9 / hbm_gbs}
+
+
+def lookup_back_to_back(torch, J, dev, hbm_gbs, batch, h=H // 8, w=W // 8, storage="fp32"):
     """The lookup alone with no host or event between launches: one CUDA graph of 8 launches over 8
     different coordinate sets (so a launch does not find its footprints in L2), replayed 4 times between
     two events; best of 5.  Kernel-to-kernel throughput, not latency."""
@@ -354,7 +362,7 @@ def lookup_back_to_back(torch, J, dev, hbm_gbs, batch, h=H // 8, w=W // 8):
     r, L = 4, 4
     g = torch.Generator(device=dev).manual_seed(0)
     q = batch * h * w
-    pyr = TiledPyramid.from_dense([torch.randn((q, h >> l, w >> l, 1), device=dev, generator=g) for l in range(L)])
+    pyr = TiledPyramid.from_dense([torch.randn((q, h >> l, w >> l, 1), device=dev, generator=g) for l in range(L)], storage)
     coords = [J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
               for _ in range(8)]
     cb = J.CorrBlock(L, r)
@@ -380,7 +388,11 @@ def lookup_back_to_back(torch, J, dev, hbm_gbs, batch, h=H // 8, w=W // 8):
         best = min(best, e0.elapsed_time(e1) / 32)
     nbytes = q * lookup_bytes_per_query(r, L)
     gbs = nbytes / (best * 1e-3) / 1e9
-    return {"batch": batch, "ms_per_launch": best, "algorithmic_bytes": nbytes, "hbm_gbs": gbs, "frac_of_hbm_peak": gbs / hbm_gbs}
+    res = {"batch": batch, "storage": storage, "ms_per_launch": best, "algorithmic_bytes": nbytes, "hbm_gbs": gbs,
+           "frac_of_hbm_peak": gbs / hbm_gbs}
+    if storage == "fp16":
+        res.update(f16_accounting(q, best, hbm_gbs, r, L))
+    return res
 
 
 def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=6, with_mask_upsample=False, with_altcorr=False):
@@ -428,6 +440,17 @@ def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=6, with_mask_
     lk_ms, _ = timed(lambda: cb.index_pyramid(pyr, coords))
     res["corr_lookup"] = hbm(lk_ms, nq * lookup_bytes_per_query(r, L))
     del pyr
+    # the same two kernels with float16 slabs (CorrBlock(storage="fp16"): values rounded once, 1e-3 bar; not the default)
+    cb16 = J.CorrBlock(L, r, storage="fp16")
+    pyr_ms16, pyr16 = timed(lambda: cb16.build_pyramid(f1, f2))
+    issued16 = 3 * flops / (pyr_ms16 * 1e-3) / 1e12
+    res["corr_pyramid_f16"] = hbm(pyr_ms16, 4 * 2 * nq * d + 2 * nq * P_l, {
+        "tflops_algorithmic": flops / (pyr_ms16 * 1e-3) / 1e12, "tflops_issued_bf16": issued16,
+        "frac_of_tensor_peak": issued16 / bf16_tf if bf16_tf else None,
+        "includes": "bf16 split pre-pass + tcgen05 GEMM; algorithmic_bytes with 2-byte pyramid values"})
+    lk_ms16, _ = timed(lambda: cb16.index_pyramid(pyr16, coords))
+    res["corr_lookup_f16"] = hbm(lk_ms16, nq * lookup_bytes_per_query(r, L), f16_accounting(nq, lk_ms16, hbm_gbs, r, L))
+    del pyr16
     mask = torch.randn((batch, h, w, 576), device=dev, generator=g)
     up_ms, _ = timed(lambda: J.upsample_flow(flow, mask))
     res["convex_upsample"] = hbm(up_ms, nq * (2304 + 8 + 512))
@@ -769,6 +792,7 @@ def run_b200(args):
         for mb in sorted({args.micro_batch, 64}):
             e = hot_kernels_at(torch, J, dev, flush, pk, H // 8, W // 8, mb, with_mask_upsample=True)
             e["corr_lookup_back_to_back"] = lookup_back_to_back(torch, J, dev, hbm_gbs, mb)
+            e["corr_lookup_f16_back_to_back"] = lookup_back_to_back(torch, J, dev, hbm_gbs, mb, storage="fp16")
             sat[f"batch_{mb}"] = e
             torch.cuda.empty_cache()
         sat["batch_1"] = hot_kernels_at(torch, J, dev, flush, pk, H // 8, W // 8, 1, with_mask_upsample=True)
@@ -776,6 +800,7 @@ def run_b200(args):
         # top-level aliases of the first batch, as in round 1
         first = sat[f"batch_{args.micro_batch}"]
         sat.update({"batch": args.micro_batch, "corr_pyramid": first["corr_pyramid"], "corr_lookup": first["corr_lookup"],
+                    "corr_pyramid_f16": first["corr_pyramid_f16"], "corr_lookup_f16": first["corr_lookup_f16"],
                     "convex_upsample": first["convex_upsample"], "mask_upsample": first["mask_upsample"]})
         line["kernels_saturating"] = sat
         if not args.skip_configs:

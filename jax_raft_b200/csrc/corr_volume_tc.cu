@@ -151,6 +151,16 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, float* v) {
         "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr));
 }
+// 32 lanes x 16 consecutive columns -> 16 registers per thread
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- cluster / CTA-pair (cta_group::2) variants ----------------------------------------------
@@ -358,7 +368,7 @@ __device__ __forceinline__ void tma_store_5d(const CUtensorMap* tm, const void* 
 
 // Stage 32 floats per lane (lane = query: two adjacent 4x4 tiles = 128 contiguous bytes of its slab) in the warp's
 // swizzled staging tile and send them as ONE bulk tensor store: tile pair `pair`, tile row `trow` of queries
-// [m_first, m_first + 32) of pair b.  The tensor map (32 floats, tile pairs, tile rows, query, pair) clips tile
+// [m_first, m_first + 32) of pair b.  The tensor map (32 floats, query, tile pairs, tile rows, pair) clips tile
 // pairs / tile rows / queries that do not exist.
 __device__ __forceinline__ void emit_pair(float* S, const float* v, const CUtensorMap* tm, int b, int m_first, int pair,
                                           int trow, int lane) {
@@ -370,7 +380,7 @@ __device__ __forceinline__ void emit_pair(float* S, const float* v, const CUtens
   fence_async_smem();
   __syncwarp();
   if (lane == 0) {
-    tma_store_5d(tm, S, 0, pair, trow, m_first, b);
+    tma_store_5d(tm, S, 0, m_first, pair, trow, b);
     bulk_commit();
   }
 }
@@ -386,19 +396,20 @@ __device__ __forceinline__ uint4 pack8_f16(const float* v) {
 // float16 slabs: stage 64 values per lane (lane = query: four adjacent 4x4 tiles = 128 contiguous bytes of its slab,
 // v0 = tiles 0-1, v1 = tiles 2-3) in the warp's swizzled staging tile and send them as ONE bulk tensor store: tile
 // pairs `pair`, `pair` + 1 of tile row `trow`, queries [m_first, m_first + 32) of pair b.  The tensor map
-// (32 halves = tile pair, tile pairs, tile rows, query, pair; box {32, 2, 1, 32, 1}) clips what does not exist.
+// (32 halves = tile pair, query, tile pairs, tile rows, pair; box {32, 32, 2, 1, 1}) clips what does not exist.
 __device__ __forceinline__ void emit_quad_f16(float* S, const float* v0, const float* v1, const CUtensorMap* tm, int b,
                                               int m_first, int pair, int trow, int lane) {
   if (lane == 0) bulk_wait_read_all();  // the previous store may still be reading S
   __syncwarp();
-  // dense [query][128 B] (the tensor map is unswizzled: with a 64-byte inner box the 128-byte swizzle does not map to
-  // a per-query XOR); same-chunk stores of 8 lanes share 4 banks, 256 cycles per emit against the ~2400 of its wait
+  // dense, unswizzled (with a 64-byte inner box the 128-byte swizzle does not map to a per-query XOR); the staging
+  // stores of 8 lanes share banks 4 ways: ~100 cycles per emit against the ~2400 of its wait
 #pragma unroll
-  for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(S + lane * 32 + c * 4) = pack8_f16((c < 4 ? v0 : v1) + 8 * (c & 3));
+  for (int c = 0; c < 8; ++c)  // box order: 32 halves, query, tile pair -> [pair][query][64 B]
+    *reinterpret_cast<uint4*>(S + (c >> 2) * 512 + lane * 16 + (c & 3) * 4) = pack8_f16((c < 4 ? v0 : v1) + 8 * (c & 3));
   fence_async_smem();
   __syncwarp();
   if (lane == 0) {
-    tma_store_5d(tm, S, 0, pair, trow, m_first, b);
+    tma_store_5d(tm, S, 0, m_first, pair, trow, b);
     bulk_commit();
   }
 }
@@ -420,9 +431,9 @@ __device__ __forceinline__ void pool_tile(const float* t, float* out, int op) {
 // patch (4 of its 8 rows); the leader CTA issues M = 256 MMAs that read both halves and write
 // each CTA's 128 accumulator lanes.  Per-CTA operand traffic and shared memory per stage halve,
 // which doubles the number of k-block stages in flight.
-// TILED: the accumulator columns are in tile order (target pixel (y, x) of the patch at column
-// (y>>2)*128 + (x>>2)*16 + (y&3)*4 + (x&3)): the producer fetches the patch as 4x4-pixel boxes, one per tile, and
-// the epilogue writes the tiled slabs of pyramid_tiled.cuh.
+// Tiled outputs (pyramid_tiled.cuh): the accumulator keeps the patch's row-major column order (pixel (y, x) at column
+// y*32 + x); an epilogue warp reads its 16 patch columns of four patch rows (four tcgen05.ld.x16 = four 4x4 tiles per
+// query), and the tile order is a compile-time permutation of those registers.
 // OUT_TILED_F16: the tiled slabs hold float16 (round-to-nearest-even of the float32 values; every level is pooled in
 // float32 from the unrounded level below and rounded once).  Level 0 leaves as 32 queries x 128 B (four tiles) per
 // bulk tensor store — two per accumulator and warp instead of four — and the small levels as plain 16/64-byte stores.
@@ -530,20 +541,7 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           const int kcoord = (j & 1) ? p.D + kb * KBLK : kb * KBLK;
           mbar_wait(&b_empty[stage], phase ^ 1);
           if (leader) mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);  // both CTAs' halves
-          if (TILED) {
-            // one 4x4-pixel box per tile (16 rows x 128 B = 2 KB), tile order = accumulator column order
-            uint8_t* dst = smem_b + stage * kBStage;
-            if (CG == 1) {
-#pragma unroll
-              for (int t = 0; t < 16; ++t)
-                tma_load_4d(&tmB, &b_full[stage], dst + t * 2048, kcoord, x0 + 4 * (t & 7), y0 + 4 * (t >> 3), b);
-            } else {
-              const uint32_t bar = mapa_shared(smem_u32(&b_full[stage]), 0);
-#pragma unroll
-              for (int t = 0; t < 8; ++t)  // this CTA's tile row of the patch
-                tma_load_4d_pair(&tmB, bar, dst + t * 2048, kcoord, x0 + 4 * t, y0 + (int)rank * (PH / 2), b);
-            }
-          } else if (CG == 1)
+          if (CG == 1)
             tma_load_4d(&tmB, &b_full[stage], smem_b + stage * kBStage, kcoord, x0, y0, b);
           else  // this CTA's 4 of the patch's 8 rows
             tma_load_4d_pair(&tmB, mapa_shared(smem_u32(&b_full[stage]), 0), smem_b + stage * kBStage, kcoord, x0,
@@ -652,15 +650,15 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       tc_fence_after();
       if (OUT == OUT_TILED_F16) {
         // half = which four tile columns (16 target columns) of the patch this warp owns, both tile rows
-        const uint32_t tcol = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 64);
+        const uint32_t tcol = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 16);
         const bool last_row = y0 + PH >= p.h;
         const int q = m0 + lane;
         float l1t[2][16];  // this warp's two level-1 tiles, [u][cy * 4 + cx]
 #pragma unroll
         for (int ty = 0; ty < 2; ++ty) {
-          float a[2][32];  // tile row ty: tiles 4*half + 0, 1 and + 2, 3
-          tmem_ld_32x32(tcol + ty * 128, a[0]);
-          tmem_ld_32x32(tcol + ty * 128 + 32, a[1]);
+          float a[4][16];  // patch rows 4 ty + r, this warp's 16 columns
+#pragma unroll
+          for (int r = 0; r < 4; ++r) tmem_ld_32x16(tcol + (uint32_t)((4 * ty + r) * PW), a[r]);
           tmem_ld_wait();
           if (ty == 1) {
             tc_fence_before();
@@ -670,13 +668,18 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               else mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[buf]), 0));
             }
           }
+          float v[2][32];  // tiles 0-1 and 2-3 of this warp's four, in slab order
+#pragma unroll
+          for (int u = 0; u < 2; ++u)
+#pragma unroll
+            for (int k = 0; k < 32; ++k) v[u][k] = a[(k >> 2) & 3][8 * u + 4 * (k >> 4) + (k & 3)];
           const int pair0 = (x0 >> 3) + 2 * half, trow = (y0 >> 2) + ty;
-          if (pair0 * 2 < p.ltx[0] && trow < p.lty[0]) emit_quad_f16(S, a[0], a[1], &tmO0, b, m0, pair0, trow, lane);
+          if (pair0 * 2 < p.ltx[0] && trow < p.lty[0]) emit_quad_f16(S, v[0], v[1], &tmO0, b, m0, pair0, trow, lane);
           if (p.L > 1) {
 #pragma unroll
             for (int u = 0; u < 2; ++u)
 #pragma unroll
-              for (int t = 0; t < 2; ++t) pool_tile(a[u] + t * 16, l1t[u] + (2 * ty) * 4 + 2 * t, 4);
+              for (int t = 0; t < 2; ++t) pool_tile(v[u] + t * 16, l1t[u] + (2 * ty) * 4 + 2 * t, 4);
           }
         }
         if (p.L > 1) {
@@ -743,17 +746,17 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         continue;
       }
       if (TILED) {
-        // half = which four tile columns (16 target columns) of the patch this warp owns, both tile rows
-        const uint32_t tcol = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 64);
+        // half = which 16 target columns (four tile columns) of the patch this warp owns, both tile rows
+        const uint32_t tcol = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)buf * BN + (uint32_t)(half * 16);
         const bool last_row = y0 + PH >= p.h;
         float l1t[2][16];  // this warp's two level-1 tiles, [u][cy * 4 + cx]
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          float a[2][32];
-          tmem_ld_32x32(tcol + u * 32, a[0]);        // tile row 0: tiles 4*half + 2u, +1
-          tmem_ld_32x32(tcol + 128 + u * 32, a[1]);  // tile row 1
+        for (int ty = 0; ty < 2; ++ty) {
+          float a[4][16];  // patch rows 4 ty + r, this warp's 16 columns
+#pragma unroll
+          for (int r = 0; r < 4; ++r) tmem_ld_32x16(tcol + (uint32_t)((4 * ty + r) * PW), a[r]);
           tmem_ld_wait();
-          if (u == 1) {
+          if (ty == 1) {
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
@@ -761,16 +764,18 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               else mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[buf]), 0));
             }
           }
-          const int pair0 = (x0 >> 3) + 2 * half + u;
-          if (pair0 * 2 < p.ltx[0]) {
-            emit_pair(S, a[0], &tmO0, b, m0, pair0, (y0 >> 2), lane);
-            if ((y0 >> 2) + 1 < p.lty[0]) emit_pair(S, a[1], &tmO0, b, m0, pair0, (y0 >> 2) + 1, lane);
-          }
-          if (p.L > 1) {
+          const int trow = (y0 >> 2) + ty;
 #pragma unroll
-            for (int ty = 0; ty < 2; ++ty)
+          for (int u = 0; u < 2; ++u) {
+            float v[32];  // tiles 2u, 2u + 1 of this warp's four, in slab order
 #pragma unroll
-              for (int t = 0; t < 2; ++t) pool_tile(a[ty] + t * 16, l1t[u] + (2 * ty) * 4 + 2 * t, 4);
+            for (int k = 0; k < 32; ++k) v[k] = a[(k >> 2) & 3][8 * u + 4 * (k >> 4) + (k & 3)];
+            const int pair0 = (x0 >> 3) + 2 * half + u;
+            if (pair0 * 2 < p.ltx[0] && trow < p.lty[0]) emit_pair(S, v, &tmO0, b, m0, pair0, trow, lane);
+            if (p.L > 1) {
+#pragma unroll
+              for (int t = 0; t < 2; ++t) pool_tile(v + t * 16, l1t[u] + (2 * ty) * 4 + 2 * t, 4);
+            }
           }
         }
         if (p.L > 1) {
@@ -997,8 +1002,8 @@ static int corr_pyramid_impl(const float* fmap1, const float* fmap2, void* const
   {
     const cuuint64_t dims[4] = {(cuuint64_t)(2 * D), (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)B};
     const cuuint64_t strides[3] = {(cuuint64_t)(2 * D) * 2, (cuuint64_t)w * 2 * D * 2, (cuuint64_t)h * w * 2 * D * 2};
-    // row-major: a CTA (pair) loads (half) a patch per stage; tiled: one 4x4-pixel box per tile
-    const cuuint32_t box[4] = {KBLK, tiled ? 4u : (cuuint32_t)PW, tiled ? 4u : (cuuint32_t)(PH / CG), 1};
+    // a CTA (pair) loads (half) a patch per stage
+    const cuuint32_t box[4] = {KBLK, (cuuint32_t)PW, (cuuint32_t)(PH / CG), 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     if (encode(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, b_split, dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1026,20 +1031,22 @@ static int corr_pyramid_impl(const float* fmap1, const float* fmap2, void* const
   if (out_mode == OUT_TILED_F16) {
     // level 0 leaves through bulk tensor stores: (32 halves = tile pair, pairs per tile row, tile rows, query, pair),
     // two pairs (128 B per query) per store
-    const cuuint64_t dims[5] = {32, (cuuint64_t)p.ltx[0] / 2, (cuuint64_t)p.lty[0], (cuuint64_t)nq, (cuuint64_t)B};
-    const cuuint64_t strides[4] = {64, (cuuint64_t)p.ltx[0] * 32, (cuuint64_t)p.lslab[0] * 2, (cuuint64_t)nq * p.lslab[0] * 2};
-    const cuuint32_t box[5] = {32, 2, 1, 32, 1};
+    const cuuint64_t dims[5] = {32, (cuuint64_t)nq, (cuuint64_t)p.ltx[0] / 2, (cuuint64_t)p.lty[0], (cuuint64_t)B};
+    const cuuint64_t strides[4] = {(cuuint64_t)p.lslab[0] * 2, 64, (cuuint64_t)p.ltx[0] * 32, (cuuint64_t)nq * p.lslab[0] * 2};
+    const cuuint32_t box[5] = {32, 32, 2, 1, 1};
     const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
     if (encode(&tmO[0], CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 5, levels[0], dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return RAFTK_ERR_UNSUPPORTED;
   } else if (tiled) {
     // levels 0 and 1 leave through bulk tensor stores: (32 floats = tile pair, pairs per tile row, tile rows, query, pair)
+    // (the query is the SECOND dimension: profiles/layout_bench.cu measures this order 20 % faster per store than
+    // query-last with one staging tile per warp)
     for (int l = 0; l < p.L && l < 2; ++l) {
-      const cuuint64_t dims[5] = {32, (cuuint64_t)p.ltx[l] / 2, (cuuint64_t)p.lty[l], (cuuint64_t)nq, (cuuint64_t)B};
-      const cuuint64_t strides[4] = {128, (cuuint64_t)p.ltx[l] * 64, (cuuint64_t)p.lslab[l] * 4,
+      const cuuint64_t dims[5] = {32, (cuuint64_t)nq, (cuuint64_t)p.ltx[l] / 2, (cuuint64_t)p.lty[l], (cuuint64_t)B};
+      const cuuint64_t strides[4] = {(cuuint64_t)p.lslab[l] * 4, 128, (cuuint64_t)p.ltx[l] * 64,
                                      (cuuint64_t)nq * p.lslab[l] * 4};
-      const cuuint32_t box[5] = {32, 1, 1, 32, 1};
+      const cuuint32_t box[5] = {32, 32, 1, 1, 1};
       const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
       if (encode(&tmO[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 5, levels[l], dims, strides, box, estr,
                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,

@@ -9,14 +9,18 @@
 // output channels are produced in four passes of 144 columns: pass g holds, for the 16 sub-pixels
 // s in [16g, 16g+16), all nine neighbour planes k (column k*16 + s - 16g), so the softmax over k of a
 // sub-pixel is complete inside one pass.  The host permutes the weight rows and the bias into that order.
-//   warp 8   TMA producer: the A tile (128 pixels x K floats, K <= 256, 8 K-blocks, resident) once, then
-//            the weights, one (pass, K-block) slab of 144 rows x 128 B per stage of a 4-stage ring;
+//   warp 8   TMA producer: the A tile (128 pixels x K floats, K <= 256, 8 K-blocks, resident) once — one barrier
+//            per K-block, so the first pass starts on K-block 0 while the rest of the tile is still arriving —
+//            then the weights, one (pass, K-block) slab of 144 rows x 128 B per stage of a 4-stage ring;
 //   warp 9   one thread issues tcgen05.mma.kind::tf32 (K = 8 each) into one of two TMEM accumulators
 //            (columns 0 and 256), so the MMAs of pass g+1 run under the epilogue of pass g;
 //   warps 0-7 epilogue, thread = (pixel, 8 of the pass's 16 sub-pixels; TMEM lane quarter = warp % 4): nine
 //            tcgen05.ld.32x32b.x8 bring all planes of its sub-pixels into registers, the accumulator is
 //            released at once, then max / exp / sum / convex combination (the arithmetic of
 //            convex_upsample.cu) and one 64-byte output row segment per pass.
+// Small batches: the passes are independent (different output rows), so when the pixel tiles alone would leave
+// more than half of the SMs idle (batch 1 at 440x1024: 55 tiles on 148 SMs) the grid gets a second dimension and
+// each CTA runs two of the four passes of its tile (110 CTAs; the A tile is read twice, from L2).
 // Status: DESIGN.md §4.7.
 
 #include <cuda.h>
@@ -64,19 +68,21 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + KB * A_BLOCK_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + STAGES * B_STAGE_BYTES);
-  uint64_t* a_full = bars;               // [1]
-  uint64_t* b_full = bars + 1;           // [STAGES]
+  uint64_t* a_full = bars;               // [8]: one per K-block
+  uint64_t* b_full = bars + 8;           // [STAGES]
   uint64_t* b_empty = b_full + STAGES;   // [STAGES]
   uint64_t* acc_full = b_empty + STAGES; // [2]
   uint64_t* acc_empty = acc_full + 2;    // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  float* smem_bias = reinterpret_cast<float*>(bars + 16);  // [576]
+  float* smem_bias = reinterpret_cast<float*>(bars + 24);  // [576]
+  // this CTA's share of the four passes (gridDim.y = 1: all; 2: two each)
+  const int npass = PASSES / (int)gridDim.y, pass0 = (int)blockIdx.y * npass;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long q0 = (long long)blockIdx.x * TM;
 
   if (warp == EPI_WARPS && lane == 0) {
-    mbar_init(a_full, 1);
+    for (int kb = 0; kb < 8; ++kb) mbar_init(&a_full[kb], 1);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 1);
@@ -100,15 +106,22 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   if (warp == EPI_WARPS) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      mbar_expect_tx(a_full, (uint32_t)(KB * A_BLOCK_BYTES));  // rows past Q are zero-filled and still counted
-      for (int kb = 0; kb < KB; ++kb) tma_load_2d(&tmA, a_full, smem_a + kb * A_BLOCK_BYTES, kb * 32, (int)q0);
+      // the first weight slabs go out between the A blocks, so that the first MMA waits for 16 + 18 KB, not 128 + 18
       int stage = 0;
       uint32_t phase = 0;
-      for (int g = 0; g < PASSES; ++g)
+      for (int g = pass0; g < pass0 + npass; ++g)
         for (int kb = 0; kb < KB; ++kb) {
+          auto load_a = [&](int k) {
+            mbar_expect_tx(&a_full[k], (uint32_t)A_BLOCK_BYTES);  // rows past Q are zero-filled and still counted
+            tma_load_2d(&tmA, &a_full[k], smem_a + k * A_BLOCK_BYTES, k * 32, (int)q0);
+          };
+          const bool first_ring = g == pass0 && kb < STAGES;  // no ring slot to wait for yet
+          if (first_ring) load_a(kb);
           mbar_wait(&b_empty[stage], phase ^ 1);
           mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);
           tma_load_2d(&tmW, &b_full[stage], smem_b + stage * B_STAGE_BYTES, kb * 32, g * NP);
+          if (first_ring && (kb == STAGES - 1 || kb == KB - 1))  // the rest of the A tile, before the ring blocks
+            for (int k = kb + 1; k < KB; ++k) load_a(k);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -120,16 +133,15 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     if (lane == 0) {
       // kind::tf32, D = f32, A = B = tf32, K-major, N = 144, M = 128
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NP >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
-      mbar_wait(a_full, 0);
-      tc_fence_after();
       int stage = 0;
       uint32_t phase = 0;
-      for (int g = 0; g < PASSES; ++g) {
-        const int buf = g & 1;
-        mbar_wait(&acc_empty[buf], ((g >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
+      for (int gi = 0; gi < npass; ++gi) {
+        const int buf = gi & 1;
+        mbar_wait(&acc_empty[buf], ((gi >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)buf * 256;
         for (int kb = 0; kb < KB; ++kb) {
+          if (gi == 0) mbar_wait(&a_full[kb], 0);
           mbar_wait(&b_full[stage], phase);
           tc_fence_after();
           const uint32_t as = smem_u32(smem_a + kb * A_BLOCK_BYTES);
@@ -166,9 +178,9 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       fyk[k] = 8.0f * f.y;
     }
     const long long W8 = 8LL * p.w;
-    for (int g = 0; g < PASSES; ++g) {
-      const int buf = g & 1;
-      mbar_wait(&acc_full[buf], (g >> 1) & 1);
+    for (int gi = 0; gi < npass; ++gi) {
+      const int g = pass0 + gi, buf = gi & 1;
+      mbar_wait(&acc_full[buf], (gi >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * 256 + 8 * half;
       const float* sb = smem_bias + g * NP + 8 * half;
@@ -266,11 +278,13 @@ extern "C" int raftk_mask_upsample(const float* m, const float* weight, const fl
   p.w = w;
   p.K = K;
   p.Q = Q;
-  const size_t smem = 1024 + (size_t)(K / 32) * A_BLOCK_BYTES + (size_t)STAGES * B_STAGE_BYTES + 128 + PASSES * NP * 4;
+  const size_t smem = 1024 + (size_t)(K / 32) * A_BLOCK_BYTES + (size_t)STAGES * B_STAGE_BYTES + 192 + PASSES * NP * 4;
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   cudaError_t e = cudaFuncSetAttribute(mask_upsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   const long long blocks = (Q + TM - 1) / TM;
-  mask_upsample_kernel<<<(unsigned)blocks, NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmW, p);
+  // pixel tiles alone would leave more than half of the SMs idle: two CTAs per tile, two passes each
+  const unsigned split = 2 * blocks <= (long long)sm_count() ? 2u : 1u;
+  mask_upsample_kernel<<<dim3((unsigned)blocks, split), NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmW, p);
   return launch_status();
 }

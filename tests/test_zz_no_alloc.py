@@ -11,7 +11,8 @@ outputs, the entry point may not): on two calls in a row, with different shapes 
 second call runs over what the first left in the shared array, the result equals that of
 raftk_corr_pyramid (caller-provided scratch) within the tolerance the pyramid tests use
 (|d| <= 1e-3 * max(|ref|, rms(ref))); and a problem larger than the array is refused with
-RAFTK_ERR_STATIC_LIMIT before anything is launched.
+RAFTK_ERR_STATIC_LIMIT before anything is launched.  The small second shape is also compared with the
+CPU oracle directly (float64 contraction, same tolerance), so the check does not rest on the other entry point alone.
 
 The file name sorts last on purpose: with ``pytest -x`` every other test has already run if this
 one fails.  It does not depend on them (passes alone in a fresh process too).
@@ -45,7 +46,7 @@ def _rel_err(got, ref):
     return float(((got.double() - ref).abs() / torch.maximum(ref.abs(), rms)).max())
 
 
-def _run_both(lib, b, h, w, d, seed, dev):
+def _run_both(lib, b, h, w, d, seed, dev, against_oracle=False):
     gen = torch.Generator(device=dev).manual_seed(seed)
     f1 = torch.randn((b, h, w, d), device=dev, generator=gen) * 1.45
     f2 = torch.randn((b, h, w, d), device=dev, generator=gen) * 1.45
@@ -69,6 +70,14 @@ def _run_both(lib, b, h, w, d, seed, dev):
     for l in range(4):
         assert torch.isfinite(got[l]).all(), f"level {l} not fully written"
         assert _rel_err(got[l], ref[l]) <= 1e-3, (l, _rel_err(got[l], ref[l]))
+    if against_oracle:
+        import numpy as np
+
+        from oracle import corr_oracle as O
+
+        want = O.build_pyramid(f1.cpu().numpy(), f2.cpu().numpy(), dtype=np.float64)
+        for l in range(4):
+            assert _rel_err(got[l], torch.from_numpy(want[l][..., 0]).to(dev)) <= 1e-3, l
 
 
 def test_static_scratch_variant_matches_on_two_calls_in_a_row(cuda, lib):
@@ -76,7 +85,7 @@ def test_static_scratch_variant_matches_on_two_calls_in_a_row(cuda, lib):
         # call 1: the Sintel shape, which nearly fills the array (14.4 of 16 MiB)
         _run_both(lib, 1, 55, 128, 256, seed=0, dev=cuda)
         # call 2, right after: a smaller, ragged problem over the first call's leftovers
-        _run_both(lib, 2, 19, 24, 128, seed=1, dev=cuda)
+        _run_both(lib, 2, 19, 24, 128, seed=1, dev=cuda, against_oracle=True)
 
 
 def test_static_scratch_variant_refuses_what_does_not_fit(cuda, lib):
