@@ -353,78 +353,58 @@ def f16_accounting(queries, ms, hbm_gbs, r=4, L=4):
     return {"own_algorithmic_bytes": own, "own_hbm_gbs": own / (ms * 1e-3) / 1e9, "own_frac_of_hbm_peak": own / (ms * 1e-3) / 1e9 / hbm_gbs}
 
 
-def lookup_back_to_back(torch, J, dev, hbm_gbs, batch, h=H // 8, w=W // 8, storage="fp32"):
-    """The lookup alone with no host or event between launches: one CUDA graph of 8 launches over 8
-    different coordinate sets (so a launch does not find its footprints in L2), replayed 4 times between
-    two events; best of 5.  Kernel-to-kernel throughput, not latency."""
+L2_BYTES = 126 << 20
+
+
+def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=5, with_mask_upsample=False, with_altcorr=False):
+    """The kernel families alone at 1/8-resolution size h x w, D = 256, `batch` pairs.  Each kernel is captured in a
+    CUDA graph of a few launches over DIFFERENT input sets (8 coordinate sets, 2 mask / feature sets, 2 pyramid
+    outputs), so that no launch finds its inputs in L2 and no host gap sits between an event and its kernel; the
+    graph is replayed between two CUDA events, `iters` times after a warm-up replay; mean per launch.  When the set
+    of inputs is smaller than 4 x L2 the L2 is also flushed (256 MiB write) before each timed replay.
+    Fractions: algorithmic bytes over the measured HBM copy peak; issued bf16 tensor FLOPs (3
+    products per float32 product) over the measured bf16 burst peak."""
     from jax_raft_b200.corr import TiledPyramid
 
-    r, L = 4, 4
-    g = torch.Generator(device=dev).manual_seed(0)
-    q = batch * h * w
-    pyr = TiledPyramid.from_dense([torch.randn((q, h >> l, w >> l, 1), device=dev, generator=g) for l in range(L)], storage)
-    coords = [J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
-              for _ in range(8)]
-    cb = J.CorrBlock(L, r)
-    side = torch.cuda.Stream(device=dev)
-    side.wait_stream(torch.cuda.current_stream(dev))
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.stream(side):
-        for c in coords:
-            cb.index_pyramid(pyr, c)
-        torch.cuda.synchronize(dev)
-        with torch.cuda.graph(graph, stream=side):
-            for c in coords:
-                cb.index_pyramid(pyr, c)
-    torch.cuda.synchronize(dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    best = float("inf")
-    for _ in range(5):
-        e0.record()
-        for _ in range(4):
-            graph.replay()
-        e1.record()
-        torch.cuda.synchronize(dev)
-        best = min(best, e0.elapsed_time(e1) / 32)
-    nbytes = q * lookup_bytes_per_query(r, L)
-    gbs = nbytes / (best * 1e-3) / 1e9
-    res = {"batch": batch, "storage": storage, "ms_per_launch": best, "algorithmic_bytes": nbytes, "hbm_gbs": gbs,
-           "frac_of_hbm_peak": gbs / hbm_gbs}
-    if storage == "fp16":
-        res.update(f16_accounting(q, best, hbm_gbs, r, L))
-    return res
-
-
-def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=6, with_mask_upsample=False, with_altcorr=False):
-    """The kernel families alone at 1/8-resolution size h x w, D = 256, `batch` pairs: CUDA events around each
-    call, L2 flushed before every call, host launch overhead included.  Fractions: algorithmic bytes (SURVEY.md
-    §8d) over the measured HBM copy peak; issued bf16 tensor FLOPs (3 products per float32 product, §4.1) over the
-    measured bf16 burst peak."""
     d, r, L = 256, 4, 4
     hbm_gbs, bf16_tf = peaks
     g = torch.Generator(device=dev).manual_seed(0)
     f1 = torch.randn((batch, h, w, d), device=dev, generator=g) * 1.45
     f2 = torch.randn((batch, h, w, d), device=dev, generator=g) * 1.45
-    coords = J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
+    coords = [J.make_coords_grid(batch, h, w, device=dev) + (torch.rand((batch, h, w, 2), device=dev, generator=g) - 0.5) * 16
+              for _ in range(8)]
     flow = torch.randn((batch, h, w, 2), device=dev, generator=g)
-    cb = J.CorrBlock(L, r)
 
-    def timed(fn):
-        ts, out = [], None
-        for i in range(iters + 2):
-            flush.fill_(i)
+    def timed(fns, input_bytes):
+        for f in fns:
+            f()
+        torch.cuda.synchronize(dev)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side), torch.cuda.graph(graph, stream=side):
+            for f in fns:
+                f()
+        torch.cuda.synchronize(dev)
+        do_flush = input_bytes < 4 * L2_BYTES
+        ts = []
+        for i in range(iters + 1):
+            if do_flush:
+                flush.fill_(i)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            out = fn()
+            graph.replay()
             b.record()
             torch.cuda.synchronize(dev)
-            if i >= 2:
-                ts.append(a.elapsed_time(b))
-        return sum(ts) / len(ts), out
+            if i >= 1:
+                ts.append(a.elapsed_time(b) / len(fns))
+        del graph
+        return sum(ts) / len(ts), min(ts), ("flushed before each replay" if do_flush else "inputs >= 4 x L2, not flushed")
 
-    def hbm(ms, nbytes, extra=None):
-        e = {"mean_ms": ms, "algorithmic_bytes": int(nbytes), "hbm_gbs": nbytes / (ms * 1e-3) / 1e9,
-             "frac_of_hbm_peak": nbytes / (ms * 1e-3) / 1e9 / hbm_gbs}
+    def hbm(t, nbytes, extra=None):
+        ms, best, l2 = t
+        e = {"mean_ms": ms, "min_ms": best, "algorithmic_bytes": int(nbytes), "hbm_gbs": nbytes / (ms * 1e-3) / 1e9,
+             "frac_of_hbm_peak": nbytes / (ms * 1e-3) / 1e9 / hbm_gbs, "l2": l2}
         e.update(extra or {})
         return e
 
@@ -432,54 +412,53 @@ def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=6, with_mask_
     P_l = sum((h >> l) * (w >> l) for l in range(L))
     flops = 2.0 * batch * (h * w) ** 2 * d
     res = {"h": h, "w": w, "batch": batch, "queries": nq}
-    pyr_ms, pyr = timed(lambda: cb.build_pyramid(f1, f2))
-    issued = 3 * flops / (pyr_ms * 1e-3) / 1e12
-    res["corr_pyramid"] = hbm(pyr_ms, 4 * (2 * nq * d + nq * P_l), {
-        "tflops_algorithmic": flops / (pyr_ms * 1e-3) / 1e12, "tflops_issued_bf16": issued,
-        "frac_of_tensor_peak": issued / bf16_tf if bf16_tf else None, "includes": "bf16 split pre-pass + tcgen05 GEMM"})
-    lk_ms, _ = timed(lambda: cb.index_pyramid(pyr, coords))
-    res["corr_lookup"] = hbm(lk_ms, nq * lookup_bytes_per_query(r, L))
-    del pyr
-    # the same two kernels with float16 slabs (CorrBlock(storage="fp16"): values rounded once, 1e-3 bar; not the default)
-    cb16 = J.CorrBlock(L, r, storage="fp16")
-    pyr_ms16, pyr16 = timed(lambda: cb16.build_pyramid(f1, f2))
-    issued16 = 3 * flops / (pyr_ms16 * 1e-3) / 1e12
-    res["corr_pyramid_f16"] = hbm(pyr_ms16, 4 * 2 * nq * d + 2 * nq * P_l, {
-        "tflops_algorithmic": flops / (pyr_ms16 * 1e-3) / 1e12, "tflops_issued_bf16": issued16,
-        "frac_of_tensor_peak": issued16 / bf16_tf if bf16_tf else None,
-        "includes": "bf16 split pre-pass + tcgen05 GEMM; algorithmic_bytes with 2-byte pyramid values"})
-    lk_ms16, _ = timed(lambda: cb16.index_pyramid(pyr16, coords))
-    res["corr_lookup_f16"] = hbm(lk_ms16, nq * lookup_bytes_per_query(r, L), f16_accounting(nq, lk_ms16, hbm_gbs, r, L))
-    del pyr16
-    mask = torch.randn((batch, h, w, 576), device=dev, generator=g)
-    up_ms, _ = timed(lambda: J.upsample_flow(flow, mask))
-    res["convex_upsample"] = hbm(up_ms, nq * (2304 + 8 + 512))
-    del mask
+    for storage, suffix, esize in (("fp32", "", 4), ("fp16", "_f16", 2)):
+        # float16 slabs: CorrBlock(storage="fp16"), the models' default in the tf32 mode (values rounded once, 1e-3 bar)
+        cb = J.CorrBlock(L, r, storage=storage)
+        pyr_bytes = 4 * 2 * nq * d + esize * nq * P_l
+        t = timed([lambda: cb.build_pyramid(f1, f2)] * 2, pyr_bytes)
+        issued = 3 * flops / (t[0] * 1e-3) / 1e12
+        res["corr_pyramid" + suffix] = hbm(t, pyr_bytes, {
+            "tflops_algorithmic": flops / (t[0] * 1e-3) / 1e12, "tflops_issued_bf16": issued,
+            "frac_of_tensor_peak": issued / bf16_tf if bf16_tf else None,
+            "includes": "bf16 split pre-pass + tcgen05 GEMM" + ("; algorithmic_bytes with 2-byte pyramid values" if esize == 2 else "")})
+        pyr = cb.build_pyramid(f1, f2)
+        t = timed([(lambda c=c: cb.index_pyramid(pyr, c)) for c in coords], esize * nq * P_l)
+        res["corr_lookup" + suffix] = hbm(t, nq * lookup_bytes_per_query(r, L),
+                                          f16_accounting(nq, t[0], hbm_gbs, r, L) if esize == 2 else None)
+        del pyr
+        torch.cuda.empty_cache()
+    masks = [torch.randn((batch, h, w, 576), device=dev, generator=g) for _ in range(2)]
+    t = timed([(lambda m=m: J.upsample_flow(flow, m)) for m in masks], 2 * nq * 2304)
+    res["convex_upsample"] = hbm(t, nq * (2304 + 8 + 512))
+    del masks
     if with_mask_upsample:
         k = 256
-        feats = torch.relu(torch.randn((batch, h, w, k), device=dev, generator=g))
+        feats = [torch.relu(torch.randn((batch, h, w, k), device=dev, generator=g)) for _ in range(2)]
         weight = torch.randn((576, k, 1, 1), device=dev, generator=g) / 16
         bias = torch.randn((576,), device=dev, generator=g)
         pw, pb = J.pack_mask_predictor(weight, bias)
-        out = torch.empty((batch, 8 * h, 8 * w, 2), device=dev)
-        mu_ms, _ = timed(lambda: J.mask_upsample(flow, feats, pw, pb, out=out))
+        outs = [torch.empty((batch, 8 * h, 8 * w, 2), device=dev) for _ in range(2)]
+        t = timed([(lambda f=f, o=o: J.mask_upsample(flow, f, pw, pb, out=o)) for f, o in zip(feats, outs)], 2 * nq * k * 4)
         mu_flops = 2.0 * nq * 576 * k
-        tf = mu_flops / (mu_ms * 1e-3) / 1e12
-        res["mask_upsample"] = hbm(mu_ms, nq * (k * 4 + 8 + 512), {
+        tf = mu_flops / (t[0] * 1e-3) / 1e12
+        res["mask_upsample"] = hbm(t, nq * (k * 4 + 8 + 512), {
             "tflops_tf32": tf, "frac_of_tensor_peak": tf / (bf16_tf / 2) if bf16_tf else None,
             "tensor_peak": "TF32 rate taken as the measured bf16 burst peak / 2 (no TF32 peak is measured)"})
-        del feats, out
+        del feats, outs
     if with_altcorr:
         ab = J.AltCorrBlock(L, r)
         # smooth +-8 px flow (what RAFT sees between iterations)
         yy, xx = torch.meshgrid(torch.arange(h, device=dev), torch.arange(w, device=dev), indexing="ij")
         sm = torch.stack([8 * torch.sin(6.28 * (xx / w + 0.3 * yy / h)), 8 * torch.cos(6.28 * (yy / h - 0.2 * xx / w))], -1)[None].float()
         c_s = (J.make_coords_grid(batch, h, w, device=dev) + sm).contiguous()
-        pool_ms, apyr = timed(lambda: ab.build_pyramid(f1, f2))
-        alt_ms, _ = timed(lambda: ab.index_pyramid(apyr, c_s))
+        tp = timed([lambda: ab.build_pyramid(f1, f2)], 4 * nq * d)
+        apyr = ab.build_pyramid(f1, f2)
+        ta = timed([lambda: ab.index_pyramid(apyr, c_s)] * 2, 4 * 2 * nq * d)
         aflops = 2.0 * nq * L * (2 * r + 2) ** 2 * d
-        res["altcorr"] = {"pool_fmap2_ms": pool_ms, "lookup_ms_per_iter": alt_ms, "tflops": aflops / (alt_ms * 1e-3) / 1e12,
+        res["altcorr"] = {"pool_fmap2_ms": tp[0], "lookup_ms_per_iter": ta[0], "tflops": aflops / (ta[0] * 1e-3) / 1e12,
                           "flops_per_iter": aflops}
+    torch.cuda.empty_cache()
     return res
 
 
@@ -740,6 +719,8 @@ def run_b200(args):
             "workload": f"raft_large {H}x{W} batch {B} per GPU, {ITERS} iterations (BASELINE config 2), torchvision random-init weights (seed 0)",
             "global_batch": world * B, "parallelism": f"batch-sharded x{world}, no collective",
             "conv_precision": model.precision + " (cuDNN library path, out of kernel scope)",
+            "pyramid_storage": getattr(model.corr_block, "storage", "fp32") + " (tiled slabs; float16 = each correlation value rounded once, "
+                               "<= 4.9e-4 relative, north-star bar 1e-3; precision='fp32' models keep float32 slabs)",
             "l2": "flushed between timed steps (256 MiB write outside the events); step working set "
                   "(261 MB pyramid + activations) also exceeds the 126 MB L2",
             "timing": "per-step CUDA events on the launching stream, summed; barrier + synchronize both sides; max over ranks",
@@ -754,7 +735,10 @@ def run_b200(args):
         "gpu_launches_per_step": int(per_forward),
         "clocks": clocks,
         "roofline": {
-            "kernel": "lookup_tiled_kernel<4, ...> (raftk_corr_lookup_tiled_update)", "bound": "hbm", "achieved": achieved,
+            "kernel": "lookup_tiled_kernel<4, ...> (raftk_corr_lookup_tiled" + ("_f16" if getattr(model.corr_block, "storage", "") == "fp16" else "") + "_update)",
+            "bound": "hbm", "achieved": achieved,
+            "algorithmic_bytes_basis": "SURVEY.md 8d: 2904 B per query (float32 footprints + float32 output), the traffic of the "
+                                       "reference's computation; with float16 slabs the kernel's own figure is 2104 B per query",
             "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": traffic,
             "traffic_source": traffic_src,
             "peak_source": peak_src, "algorithmic_bytes_per_launch": lookup_bytes,
@@ -787,16 +771,12 @@ def run_b200(args):
         torch.cuda.empty_cache()
     if world == 1 and args.micro_batch > 0:
         pk = (hbm_gbs, bf16_tf)
-        sat = {"how": "events around each call, L2 flushed before each, host launch overhead included; "
-                      "corr_lookup_back_to_back: graph of 8 launches over 8 coordinate sets, no events or host between launches"}
+        sat = {"how": "each kernel in a CUDA graph of 2-8 launches over different input sets (no host gap, no L2 reuse), replayed "
+                      "between two CUDA events, mean of 5 replays after a warm-up; L2 also flushed when the inputs are below 4 x L2"}
         for mb in sorted({args.micro_batch, 64}):
-            e = hot_kernels_at(torch, J, dev, flush, pk, H // 8, W // 8, mb, with_mask_upsample=True)
-            e["corr_lookup_back_to_back"] = lookup_back_to_back(torch, J, dev, hbm_gbs, mb)
-            e["corr_lookup_f16_back_to_back"] = lookup_back_to_back(torch, J, dev, hbm_gbs, mb, storage="fp16")
-            sat[f"batch_{mb}"] = e
+            sat[f"batch_{mb}"] = hot_kernels_at(torch, J, dev, flush, pk, H // 8, W // 8, mb, with_mask_upsample=True)
             torch.cuda.empty_cache()
         sat["batch_1"] = hot_kernels_at(torch, J, dev, flush, pk, H // 8, W // 8, 1, with_mask_upsample=True)
-        sat["batch_1"]["corr_lookup_back_to_back"] = lookup_back_to_back(torch, J, dev, hbm_gbs, 1)
         # top-level aliases of the first batch, as in round 1
         first = sat[f"batch_{args.micro_batch}"]
         sat.update({"batch": args.micro_batch, "corr_pyramid": first["corr_pyramid"], "corr_lookup": first["corr_lookup"],
@@ -807,7 +787,7 @@ def run_b200(args):
             sweep = []
             for (sh, sw) in SWEEP_SIZES:
                 for sb in (1, max(1, round(112640 / (sh * sw)))):
-                    sweep.append(hot_kernels_at(torch, J, dev, flush, pk, sh, sw, sb, iters=4,
+                    sweep.append(hot_kernels_at(torch, J, dev, flush, pk, sh, sw, sb, iters=3,
                                                 with_altcorr=(sb == 1 and (sh, sw) == (136, 240))))
                     torch.cuda.empty_cache()
             configs["c5"] = {"workload": "correlation microbench: pyramid build + lookup + upsampler over 1/8-resolution sizes, D=256, "

@@ -522,9 +522,13 @@ class RAFT:
         self._streams: Dict[str, Any] = {}
         self.config = config
         # the pyramid is opaque to the model (model.py:530-539): tiled slabs, unless the optional lookup+convolution
-        # kernel (which reads row-major levels) is asked for
-        self.corr_block = corr_block or CorrBlock(config.corr_block_num_levels, config.corr_block_radius,
-                                                  layout="rowmajor" if fused_lookup_conv else "tiled")
+        # kernel (which reads row-major levels) is asked for.  In the throughput mode (precision="tf32") the slabs
+        # hold float16 (each correlation value rounded once, <= 4.9e-4 relative against the north-star's 1e-3:
+        # ~1e-3 px of end-to-end EPE where the TF32 convolutions contribute ~9e-3); precision="fp32" keeps
+        # float32 slabs and reproduces the CPU reference to ~2e-5 px.
+        self.corr_block = corr_block or CorrBlock(
+            config.corr_block_num_levels, config.corr_block_radius, layout="rowmajor" if fused_lookup_conv else "tiled",
+            storage="fp16" if precision == "tf32" and not fused_lookup_conv else "fp32")
         expected = config.corr_block_num_levels * (2 * config.corr_block_radius + 1) ** 2
         assert self.corr_block.out_channels == expected, (
             f"corr_block.out_channels={self.corr_block.out_channels} does not match the motion encoder ({expected})")

@@ -23,6 +23,8 @@ ap.add_argument("--batch", type=int, default=1)
 ap.add_argument("--iters", type=int, default=ITERS)
 ap.add_argument("--hot-only", action="store_true")
 ap.add_argument("--kernel", default="tc")
+ap.add_argument("--storage", default="fp32", help="pyramid storage of the hot-only pass: fp32 | fp16 | both")
+ap.add_argument("--extras", action="store_true", help="hot-only: also raftk_mask_upsample and the alt_corr lookup (136x240)")
 args = ap.parse_args()
 
 dev = torch.device("cuda", 0)
@@ -35,16 +37,32 @@ if args.hot_only:
     coords = J.make_coords_grid(b, h, w, device=dev) + (torch.rand((b, h, w, 2), device=dev, generator=g) - 0.5) * 16
     flow = torch.randn((b, h, w, 2), device=dev, generator=g)
     mask = torch.randn((b, h, w, 576), device=dev, generator=g)
-    cb = J.CorrBlock(4, 4, kernel=args.kernel)
+    blocks = [J.CorrBlock(4, 4, kernel=args.kernel, storage=s) for s in (("fp32", "fp16") if args.storage == "both" else (args.storage,))]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    if args.extras:
+        feats = torch.relu(torch.randn((b, h, w, 256), device=dev, generator=g))
+        pw, pb = J.pack_mask_predictor(torch.randn((576, 256, 1, 1), device=dev, generator=g) / 16, torch.randn((576,), device=dev, generator=g))
+        up_out = torch.empty((b, 8 * h, 8 * w, 2), device=dev)
+        ah, aw = 136, 240
+        a1 = torch.randn((1, ah, aw, d), device=dev, generator=g) * 1.45
+        a2 = torch.randn((1, ah, aw, d), device=dev, generator=g) * 1.45
+        yy, xx = torch.meshgrid(torch.arange(ah, device=dev), torch.arange(aw, device=dev), indexing="ij")
+        sm = torch.stack([8 * torch.sin(6.28 * (xx / aw + 0.3 * yy / ah)), 8 * torch.cos(6.28 * (yy / ah - 0.2 * xx / aw))], -1)[None].float()
+        ac = (J.make_coords_grid(1, ah, aw, device=dev) + sm).contiguous()
+        ab = J.AltCorrBlock(4, 4)
     for i in range(3):
         if i == 2:
             torch.cuda.synchronize()
             torch.cuda.profiler.start()
-        pyr = cb.build_pyramid(f1, f2)
-        flush.fill_(0)
-        out = cb.index_pyramid(pyr, coords)
+        for cb in blocks:
+            pyr = cb.build_pyramid(f1, f2)
+            flush.fill_(0)
+            out = cb.index_pyramid(pyr, coords)
+            del pyr
         up = J.upsample_flow(flow, mask)
+        if args.extras:
+            J.mask_upsample(flow, feats, pw, pb, out=up_out)
+            ab.index_pyramid(ab.build_pyramid(a1, a2), ac)
     torch.cuda.synchronize()
     torch.cuda.profiler.stop()
 else:
