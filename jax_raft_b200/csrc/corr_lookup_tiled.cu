@@ -320,10 +320,12 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) lookup_tiled_kernel(const Pa
           float* t = tile + r0 * P + c4;
 #pragma unroll
           for (int rr = 0; rr < 4; ++rr) {  // tile row rr = 4 halves = words 2 rr, 2 rr + 1
-            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v[m][2 * rr]));
-            const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&v[m][2 * rr + 1]));
-            const float4 val = ld ? make_float4(a.x, a.y, b.x, b.y) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            if (need && (unsigned)(r0 + rr) < (unsigned)FP) *reinterpret_cast<float4*>(t + rr * P) = val;
+            // a slot that was not loaded (outside the level) is zero BEFORE the widening: the select then sits on
+            // the load's own predicate (zero-initialised registers), not on every widened value
+            const float w0 = ld ? v[m][2 * rr] : 0.0f, w1 = ld ? v[m][2 * rr + 1] : 0.0f;
+            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&w0));
+            const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&w1));
+            if (need && (unsigned)(r0 + rr) < (unsigned)FP) *reinterpret_cast<float4*>(t + rr * P) = make_float4(a.x, a.y, b.x, b.y);
           }
         }
         continue;
