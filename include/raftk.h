@@ -212,6 +212,21 @@ int raftk_altcorr_pool_fmap2(float* const* f2_levels, int num_levels, int B, int
 int raftk_altcorr_lookup(const float* fmap1, const float* const* f2_levels, int num_levels,
                          const float* coords, float* out, int B, int nq, int h, int w,
                          int D, int radius, void* stream);
+/* The same lookup on the tensor cores (no reference counterpart either; same result contract as
+ * raftk_altcorr_lookup, i.e. index_pyramid of model.py:448-470 over the never-materialised volume).
+ * Every 8 x 8 patch of query pixels at one level is a tcgen05 GEMM against the bounding box of its
+ * windows; operands are bf16 [hi | mid] splits written once per pair by raftk_altcorr_split:
+ *   f1_split     (B, nq, 2D) bf16  = split of fmap1 * 1/sqrt(D)   (scale = 1/sqrt(D))
+ *   f2_split[l]  (B, h>>l, w>>l, 2D) bf16 = split of f2_levels[l] (scale = 1)
+ * Products hi*hi + mid*hi + hi*mid in float32: ~2e-5 relative to the float32 lookup (bar 1e-3).
+ * The float32 maps are still read by the scalar path that serves boxes wider than 32 or taller
+ * than 30 cells and far / non-finite coordinates.  num_levels <= 4, radius in {3, 4}, D % 64 == 0,
+ * D <= 256, queries forming whole rows (nq % w == 0); otherwise RAFTK_ERR_UNSUPPORTED (call
+ * raftk_altcorr_lookup). */
+int raftk_altcorr_split(const float* src, void* dst_bf16, long long rows, int D, float scale, void* stream);
+int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f2_levels, const void* f1_split,
+                            const void* const* f2_split, int num_levels, const float* coords, float* out,
+                            int B, int nq, int h, int w, int D, int radius, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Kernel family 3 — convex 8x flow upsampling.

@@ -47,6 +47,12 @@ SIGNATURES = {
         [c_void_p, _FloatPtrArray, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
          c_int, c_void_p],
     ),
+    "raftk_altcorr_split": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_float, c_void_p]),
+    "raftk_altcorr_lookup_tc": (
+        c_int,
+        [c_void_p, _FloatPtrArray, c_void_p, _FloatPtrArray, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+         c_int, c_void_p],
+    ),
     "raftk_bias_act_nhwc": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_int, c_void_p]),
     "raftk_instance_norm_scratch_bytes": (c_size_t, [c_int, c_int]),
     "raftk_instance_norm_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_size_t, c_void_p]),

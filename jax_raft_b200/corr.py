@@ -350,16 +350,25 @@ class CorrBlock:
 class AltCorrBlock:
     """On-the-fly lookup that never materialises the volume ("alt_corr").
 
-    Same contract as :class:`CorrBlock`; the opaque "pyramid" is ``(fmap1_rows, [fmap2 pooled
-    l times])``.  Not in the reference; equal to the volume path by linearity
-    of the average pool.
+    Same contract as :class:`CorrBlock`; the opaque "pyramid" is ``(fmap1_rows, [fmap2 pooled l times])`` plus,
+    for the tensor-core kernel, the bf16 [hi | mid] splits of those maps.  Not in the reference (SURVEY.md §0.1);
+    equal to the volume path by linearity of the average pool.
+
+    ``kernel="tc"`` (default): ``raftk_altcorr_lookup_tc`` — every 8 x 8 patch of queries is a tcgen05 GEMM against
+    the bounding box of its windows — where it applies (<= 4 levels, radius 3 or 4, D a multiple of 64 up to 256);
+    ``kernel="simt"``: the float32 FMA kernels (``raftk_altcorr_lookup``).
     """
 
-    def __init__(self, num_levels: int = 4, radius: int = 4):
+    def __init__(self, num_levels: int = 4, radius: int = 4, kernel: str = "tc"):
         assert 1 <= num_levels <= _lib.MAX_LEVELS
+        assert kernel in ("tc", "simt")
         self.num_levels = num_levels
         self.radius = radius
+        self.kernel = kernel
         self.out_channels = num_levels * (2 * radius + 1) ** 2
+
+    def _tc_supported(self, d: int) -> bool:
+        return self.kernel == "tc" and self.num_levels <= 4 and self.radius in (3, 4) and d % 64 == 0 and d <= 256
 
     def build_pyramid(self, fmap1: torch.Tensor, fmap2: torch.Tensor,
                       query_rows: Optional[Tuple[int, int]] = None):
@@ -370,15 +379,24 @@ class AltCorrBlock:
             for l in range(1, self.num_levels)
         ]
         lib = _lib.load()
+        stream = _lib.current_stream_ptr(fmap2.device)
         with torch.cuda.device(fmap2.device):
-            rc = lib.raftk_altcorr_pool_fmap2(_lib.ptr_array(f2_levels), self.num_levels, b, h, w, d,
-                                              _lib.current_stream_ptr(fmap2.device))
-        _lib.check("raftk_altcorr_pool_fmap2", rc)
-        _lib.count_launch(self.num_levels - 1)
-        return (fmap1, f2_levels)
+            rc = lib.raftk_altcorr_pool_fmap2(_lib.ptr_array(f2_levels), self.num_levels, b, h, w, d, stream)
+            _lib.check("raftk_altcorr_pool_fmap2", rc)
+            _lib.count_launch(self.num_levels - 1)
+            if not self._tc_supported(d):
+                return (fmap1, f2_levels)
+            # bf16 [hi | mid] operands of the tensor-core lookup, once per pair (1/sqrt(D) rides on fmap1)
+            f1_split = torch.empty(tuple(fmap1.shape[:-1]) + (2 * d,), dtype=torch.bfloat16, device=fmap1.device)
+            f2_split = [torch.empty(tuple(t.shape[:-1]) + (2 * d,), dtype=torch.bfloat16, device=t.device) for t in f2_levels]
+            for src, dst, scale in [(fmap1, f1_split, float(d) ** -0.5)] + [(s_, d_, 1.0) for s_, d_ in zip(f2_levels, f2_split)]:
+                rc = lib.raftk_altcorr_split(src.data_ptr(), dst.data_ptr(), src.numel() // d, d, scale, stream)
+                _lib.check("raftk_altcorr_split", rc)
+            _lib.count_launch(1 + self.num_levels)
+        return (fmap1, f2_levels, f1_split, f2_split)
 
     def index_pyramid(self, corr_pyramid, centroids_coords: torch.Tensor) -> torch.Tensor:
-        fmap1, f2_levels = corr_pyramid
+        fmap1, f2_levels = corr_pyramid[0], corr_pyramid[1]
         assert centroids_coords.shape[-1] == 2
         coords = _check_cuda_f32("centroids_coords", centroids_coords)
         b, hq, wq, _ = coords.shape
@@ -387,9 +405,16 @@ class AltCorrBlock:
         out = torch.empty((b, hq, wq, self.out_channels), dtype=torch.float32, device=coords.device)
         lib = _lib.load()
         with torch.cuda.device(coords.device):
-            rc = lib.raftk_altcorr_lookup(fmap1.data_ptr(), _lib.ptr_array(f2_levels), self.num_levels,
-                                          coords.data_ptr(), out.data_ptr(), b, hq * wq, h, w, d, self.radius,
-                                          _lib.current_stream_ptr(coords.device))
-        _lib.check("raftk_altcorr_lookup", rc)
+            if len(corr_pyramid) == 4 and wq == w:
+                rc = lib.raftk_altcorr_lookup_tc(fmap1.data_ptr(), _lib.ptr_array(f2_levels), corr_pyramid[2].data_ptr(),
+                                                 _lib.ptr_array(corr_pyramid[3]), self.num_levels, coords.data_ptr(),
+                                                 out.data_ptr(), b, hq * wq, h, w, d, self.radius,
+                                                 _lib.current_stream_ptr(coords.device))
+                _lib.check("raftk_altcorr_lookup_tc", rc)
+            else:
+                rc = lib.raftk_altcorr_lookup(fmap1.data_ptr(), _lib.ptr_array(f2_levels), self.num_levels,
+                                              coords.data_ptr(), out.data_ptr(), b, hq * wq, h, w, d, self.radius,
+                                              _lib.current_stream_ptr(coords.device))
+                _lib.check("raftk_altcorr_lookup", rc)
         _lib.count_launch(1)
         return out

@@ -1,0 +1,455 @@
+// Kernel family 2b on the tensor cores: the on-the-fly ("alt_corr") window lookup as small tcgen05 GEMMs.
+// No reference counterpart; by linearity of the average pool
+//   pool_l(f1 . f2^T)[q, Y, X] = f1[q] . pool_l(f2)[Y, X]
+// the taps of level l (model.py:448-470) are bilinear samples of dot products against fmap2 pooled l times.
+//
+// One CTA = one 8 x 8 patch of query pixels at ONE level (UMMA M = 64, cta_group::1).  Neighbouring windows
+// overlap, so the CTA computes the correlations of its 64 queries with every cell of the BOUNDING BOX of their
+// (2r+2)^2 windows — a (64 x box cells x D) GEMM — and each query then picks its own window out of the box:
+//
+//   operands   bf16 [hi | mid] splits of fmap1 (scaled by 1/sqrt(D)) and of every pooled fmap2 level, written once
+//              per pair by raftk_altcorr_split; products hi*hi + mid*hi + hi*mid in float32 (the scheme of the
+//              volume GEMM, corr_volume_tc.cu: ~2e-5 relative).
+//   A          the 64 queries x 2D tile, resident: 2 * D/64 TMA boxes {64 ch, 8 x, 8 y} (64 KB at D = 256).
+//   B          the box, in CHUNKS of 6 box rows; a chunk is up to four column blocks of 8 cells, each one TMA box
+//              {64 ch, 8 cells, 6 rows} = 48 operand rows, so N = 48, 96, 144 or 192 and a box may be up to 32 cells
+//              wide and 30 rows tall (TMA zero-fills cells outside the level: those correlations are 0, which is
+//              what the reference's zero-outside sampling makes of them).  One (chunk, k-block, hi | mid) slab per
+//              stage of a 4-stage ring.
+//   D          float32 in TMEM, two accumulators of 192 columns: the epilogue of chunk c runs under the MMAs of
+//              chunk c + 1.  M = 64: accumulator row m is TMEM lane (m % 16) + 32 * (m / 16).
+//   epilogue   warp w owns queries 16w .. 16w+15.  Per box row: tcgen05.ld.x8 per column block (up to 32 cells in
+//              registers, static indices), and every thread stores the <= 2r+2 cells of that row that belong to its
+//              own window into its footprint F[query][(2r+2)^2] in shared memory (predicated stores; the window
+//              offset is a shared-memory address, never a register index).  When the last chunk is in, the warp
+//              evaluates the taps of its queries with the shared lookup code (lookup_taps.cuh) — the window
+//              indexing and the float32 tap arithmetic are those of the volume lookup.
+//
+// A cell's value depends only on the query's row of A, the cell's row of B and the fixed K order, not on the box or
+// the chunk it was computed in, so row bands reproduce the full result bit for bit.  Queries that read nothing (far or
+// non-finite coordinates, windows entirely outside the level) get a zero footprint and stay out of the box.  Boxes
+// that do not fit (rough flow: wider than 32 or taller than 30 cells) take a scalar fp32 path inside the same kernel
+// (sequential fma chain over D, as altcorr.cu), slower and ~2e-5 away from the split product.
+//
+// Work per iteration at 136 x 240, r = 4, D = 256: 2040 CTAs (510 patches x 4 levels, level 0 first); a level-0 box
+// of ~20 x 20 cells is 4 chunks x 48 MMAs (M64 N144 K16).
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <cstring>
+
+#include "lookup_taps.cuh"
+#include "raftk_common.cuh"
+#include "tc_ptx.cuh"
+
+namespace raftk {
+namespace atc {
+
+using namespace raftk::ptx;
+
+constexpr int TQ = 64;                          // queries per CTA: 8 x 8
+constexpr int ROWS = 6;                         // box rows per chunk
+constexpr int MAX_CB = 4;                       // column blocks of 8 cells: box width <= 32
+constexpr int MAX_CHUNKS = 5;                   // box height <= 30
+constexpr int CB_BYTES = ROWS * 8 * 128;        // one TMA box {64 bf16, 8 cells, 6 rows}
+constexpr int B_STAGE_BYTES = MAX_CB * CB_BYTES;
+constexpr int STAGES = 4;
+constexpr int A_BLOCK_BYTES = TQ * 128;
+constexpr int ACC_COLS = MAX_CB * ROWS * 8;     // 192 accumulator columns per buffer
+constexpr int NUM_THREADS = 192;                // warps 0-3 epilogue, 4 TMA producer, 5 MMA issuer + TMEM
+constexpr int SMEM_LIMIT = 232448;
+
+struct Params {
+  const float* f1;      // float32 sources, used by the scalar path only
+  const float* f2[4];
+  int lh[4], lw[4];
+  const float* coords;
+  float* out;
+  int B, nq, D, L;
+  int rows_q, w_q;
+  float inv_sqrt_d;
+};
+
+struct QInfo {
+  int bx, by, flags, pad;  // flags: bit 0 valid query, bit 1 the query has a window (usable coordinates, inside the level)
+};
+
+// float32 rows -> [hi | mid] bf16 rows (x * scale ~ hi + mid to 2^-17)
+__global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                                         long long rows, int D, float scale) {
+  const int d4 = D >> 2;
+  const long long total = rows * d4;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const long long row = t / d4;
+    const int c = (int)(t - row * d4) * 4;
+    const float4 x = __ldg(reinterpret_cast<const float4*>(src + row * D + c));
+    const float xs[4] = {x.x * scale, x.y * scale, x.z * scale, x.w * scale};
+    __nv_bfloat16 hi[4], mid[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      hi[i] = __float2bfloat16_rn(xs[i]);
+      mid[i] = __float2bfloat16_rn(xs[i] - __bfloat162float(hi[i]));
+    }
+    *reinterpret_cast<uint2*>(dst + row * 2 * D + c) = *reinterpret_cast<const uint2*>(hi);
+    *reinterpret_cast<uint2*>(dst + row * 2 * D + D + c) = *reinterpret_cast<const uint2*>(mid);
+  }
+}
+
+template <int R>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
+                  const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ CUtensorMap tmB2,
+                  const __grid_constant__ CUtensorMap tmB3, const Params p) {
+  constexpr int FP = 2 * R + 2, S = 2 * R + 1, NCELL = FP * FP;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const int KB = p.D / 64;  // k-blocks per plane (hi, mid)
+  uint8_t* smem_a = smem;                                   // [2 KB][A_BLOCK_BYTES]: hi blocks, then mid blocks
+  uint8_t* smem_b = smem_a + 2 * KB * A_BLOCK_BYTES;        // [STAGES][B_STAGE_BYTES]
+  float* F = reinterpret_cast<float*>(smem_b + STAGES * B_STAGE_BYTES);  // [TQ][NCELL]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(F + TQ * NCELL);
+  uint64_t* a_full = bars;                 // [1]
+  uint64_t* b_full = bars + 1;             // [STAGES]
+  uint64_t* b_empty = b_full + STAGES;     // [STAGES]
+  uint64_t* acc_full = b_empty + STAGES;   // [2]
+  uint64_t* acc_empty = acc_full + 2;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  int* red = reinterpret_cast<int*>(bars + 16);             // [5][4] per-warp partial box, then box[5]
+  int* box = red + 20;
+  QInfo* qinfo = reinterpret_cast<QInfo*>(red + 32);        // [TQ]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_x = (p.w_q + 7) >> 3, tiles_y = (p.rows_q + 7) >> 3;
+  const long long tiles = (long long)tiles_x * tiles_y * p.B;
+  const int l = (int)(blockIdx.x / tiles);  // level-major: the large level-0 boxes are scheduled first
+  long long rem = blockIdx.x - (long long)l * tiles;
+  const int txi = (int)(rem % tiles_x);
+  rem /= tiles_x;
+  const int tyi = (int)(rem % tiles_y);
+  const int b = (int)(rem / tiles_y);
+  const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
+  const int lh = l == 0 ? p.lh[0] : l == 1 ? p.lh[1] : l == 2 ? p.lh[2] : p.lh[3];
+  const int lw = l == 0 ? p.lw[0] : l == 1 ? p.lw[1] : l == 2 ? p.lw[2] : p.lw[3];
+  const float* f2l = l == 0 ? p.f2[0] : l == 1 ? p.f2[1] : l == 2 ? p.f2[2] : p.f2[3];
+
+  if (warp == 5 && lane == 0) {
+    mbar_init(a_full, 1);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 5) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+
+  // ---- the queries of this patch, their window origins, and the bounding box of the windows ----
+  // epilogue thread (warp w < 4, lane < 16) owns query m = 16 w + lane = (row m / 8, column m % 8) of the patch:
+  // the accumulator row its TMEM lane holds
+  const int m = 16 * warp + lane;
+  const bool owner = warp < 4 && lane < 16;
+  // haswin: finite, not absurdly far, and the window overlaps the level.  Queries without a window read nothing —
+  // their footprint is all zeros whatever path a patch takes — and stay out of the bounding box, so that one stray
+  // query does not change how its neighbours are computed.
+  bool qvalid = false, haswin = false;
+  long long q = 0;
+  float cx = 0.0f, cy = 0.0f;
+  int bx = 0, by = 0;
+  if (owner) {
+    const int qy = tyi * 8 + (m >> 3), qx = txi * 8 + (m & 7);
+    qvalid = qy < p.rows_q && qx < p.w_q;
+    if (qvalid) {
+      q = (long long)b * p.nq + (long long)qy * p.w_q + qx;
+      cx = __ldg(p.coords + 2 * q);
+      cy = __ldg(p.coords + 2 * q + 1);
+    }
+    const bool normal = fabsf(cx) <= 1.0e6f && fabsf(cy) <= 1.0e6f;
+    const float sc = __int_as_float((127 - l) << 23);
+    bx = clamp_to_int(floorf(cx * sc)) - R;
+    by = clamp_to_int(floorf(cy * sc)) - R;
+    haswin = qvalid && normal && bx < lw && bx + FP > 0 && by < lh && by + FP > 0;
+    qinfo[m] = QInfo{bx, by, (qvalid ? 1 : 0) | (haswin ? 2 : 0), 0};
+    if (qvalid && !haswin)
+      for (int e = 0; e < NCELL; ++e) F[m * NCELL + e] = 0.0f;
+  }
+  {
+    int mnx = haswin ? bx : 0x7fffffff, mxx = haswin ? bx : -0x7fffffff;
+    int mny = haswin ? by : 0x7fffffff, mxy = haswin ? by : -0x7fffffff;
+    int any = haswin ? 1 : 0;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, off));
+      mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, off));
+      mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, off));
+      mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, off));
+      any |= __shfl_xor_sync(0xffffffffu, any, off);
+    }
+    if (warp < 4 && lane == 0) {
+      red[0 * 4 + warp] = mnx;
+      red[1 * 4 + warp] = mxx;
+      red[2 * 4 + warp] = mny;
+      red[3 * 4 + warp] = mxy;
+      red[4 * 4 + warp] = any;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (threadIdx.x == 0) {
+    int mnx = red[0], mxx = red[4], mny = red[8], mxy = red[12], any = red[16];
+    for (int i = 1; i < 4; ++i) {
+      mnx = min(mnx, red[i]);
+      mxx = max(mxx, red[4 + i]);
+      mny = min(mny, red[8 + i]);
+      mxy = max(mxy, red[12 + i]);
+      any |= red[16 + i];
+    }
+    box[0] = any ? mnx : 0;
+    box[1] = any ? mny : 0;
+    box[2] = any ? mxx - mnx + FP : 0;  // width in cells (0: no query of the patch has a window)
+    box[3] = any ? mxy - mny + FP : 0;  // height
+  }
+  __syncthreads();
+  const uint32_t tmem_base = *tmem_slot;
+  const int X0 = box[0], Y0 = box[1], BW = box[2], BH = box[3];
+  const bool tc_path = BW <= 8 * MAX_CB && BH <= ROWS * MAX_CHUNKS;
+  const int ncb = (BW + 7) >> 3, nchunks = (BH + ROWS - 1) / ROWS;
+
+  if (tc_path) {
+    if (warp == 4) {
+      // ===================== TMA producer =====================
+      if (lane == 0) {
+        mbar_expect_tx(a_full, (uint32_t)(2 * KB * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
+        for (int j = 0; j < 2 * KB; ++j)  // [hi | mid] is contiguous in K: block j starts at channel 64 j
+          tma_load_4d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * 64, txi * 8, tyi * 8, b);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int c = 0; c < nchunks; ++c)
+          for (int kb = 0; kb < KB; ++kb)
+            for (int part = 0; part < 2; ++part) {
+              mbar_wait(&b_empty[stage], phase ^ 1);
+              mbar_expect_tx(&b_full[stage], (uint32_t)(ncb * CB_BYTES));
+              for (int cb = 0; cb < ncb; ++cb)
+                tma_load_4d(tmB, &b_full[stage], smem_b + stage * B_STAGE_BYTES + cb * CB_BYTES,
+                            part * p.D + kb * 64, X0 + 8 * cb, Y0 + ROWS * c, b);
+              if (++stage == STAGES) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+      }
+    } else if (warp == 5) {
+      // ===================== MMA issuer =====================
+      if (lane == 0) {
+        const uint32_t idesc = make_idesc_bf16(TQ, ncb * ROWS * 8);
+        mbar_wait(a_full, 0);
+        tc_fence_after();
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int c = 0; c < nchunks; ++c) {
+          const int buf = c & 1;
+          mbar_wait(&acc_empty[buf], ((c >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + (uint32_t)buf * ACC_COLS;
+          for (int kb = 0; kb < KB; ++kb) {
+            const uint32_t a_hi = smem_u32(smem_a + kb * A_BLOCK_BYTES);
+            const uint32_t a_mid = smem_u32(smem_a + (KB + kb) * A_BLOCK_BYTES);
+            // stage holding B_hi[kb]: hi*hi and mid*hi
+            mbar_wait(&b_full[stage], phase);
+            tc_fence_after();
+            uint32_t bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_hi + 32 * k4), umma_desc(bs + 32 * k4), idesc, (kb | k4) != 0);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_mid + 32 * k4), umma_desc(bs + 32 * k4), idesc, 1);
+            tc_commit(&b_empty[stage]);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+            // stage holding B_mid[kb]: hi*mid
+            mbar_wait(&b_full[stage], phase);
+            tc_fence_after();
+            bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_hi + 32 * k4), umma_desc(bs + 32 * k4), idesc, 1);
+            tc_commit(&b_empty[stage]);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+          tc_commit(&acc_full[buf]);
+        }
+      }
+    } else {
+      // ===================== epilogue: window extraction =====================
+      const int ox = bx - X0, oy = by - Y0;  // this query's window origin inside the box
+      float* Fq = F + m * NCELL;
+      for (int c = 0; c < nchunks; ++c) {
+        const int buf = c & 1;
+        mbar_wait(&acc_full[buf], (c >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * ACC_COLS;
+#pragma unroll 1
+        for (int r = 0; r < ROWS; ++r) {
+          const int row = c * ROWS + r;  // box row
+          if (row >= BH) break;
+          float v[8 * MAX_CB];
+#pragma unroll
+          for (int cb = 0; cb < MAX_CB; ++cb)
+            if (cb < ncb) tmem_ld_32x8(taddr + (uint32_t)(cb * ROWS * 8 + r * 8), v + 8 * cb);
+          tmem_ld_wait();
+          const int wr = row - oy;
+          if (haswin && (unsigned)wr < (unsigned)FP) {
+            float* Fr = Fq + wr * FP - ox;
+#pragma unroll
+            for (int i = 0; i < 8 * MAX_CB; ++i)
+              if (i < 8 * ncb && (unsigned)(i - ox) < (unsigned)FP) Fr[i] = v[i];
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      }
+    }
+  } else if (warp < 4) {
+    // ===================== scalar path: the windows of this patch do not fit one box (rough flow) =====================
+    const int t = threadIdx.x, qi = t >> 1, sub = t & 1;
+    const QInfo qi_info = qinfo[qi];
+    const bool v_ok = (qi_info.flags & 1) != 0, n_ok = (qi_info.flags & 2) != 0;  // n_ok implies v_ok
+    const int qy = tyi * 8 + (qi >> 3), qx = txi * 8 + (qi & 7);
+    const long long qq = (long long)b * p.nq + (long long)qy * p.w_q + qx;
+    const float* f1q = p.f1 + (v_ok ? qq : 0) * p.D;
+    const float* f2b = f2l + (long long)b * lh * lw * p.D;
+#pragma unroll 1
+    for (int i = 0; i < NCELL / 2; ++i) {
+      const int e = sub + 2 * i;
+      const int ry = e / FP, rx = e - ry * FP;
+      const int gy = qi_info.by + ry, gx = qi_info.bx + rx;
+      float s = 0.0f;
+      if (v_ok && n_ok && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) {
+        const float4* cp = reinterpret_cast<const float4*>(f2b + ((long long)gy * lw + gx) * p.D);
+        const float4* ap = reinterpret_cast<const float4*>(f1q);
+        for (int k = 0; k < p.D / 4; ++k) {
+          const float4 vv = __ldg(cp + k), a = __ldg(ap + k);
+          s = fmaf(a.x, vv.x, s);
+          s = fmaf(a.y, vv.y, s);
+          s = fmaf(a.z, vv.z, s);
+          s = fmaf(a.w, vv.w, s);
+        }
+      }
+      F[qi * NCELL + e] = s * p.inv_sqrt_d;
+    }
+  }
+
+  // ---- taps of level l: warp w takes its queries 16 w .. 16 w + 15 ----
+  if (warp < 4) {
+    asm volatile("bar.sync 1, 128;" ::: "memory");  // every footprint of the patch is complete
+    const int C = p.L * S * S;
+    for (int k = 0; k < 16; ++k) {
+      const float ccx = __shfl_sync(0xffffffffu, cx, k), ccy = __shfl_sync(0xffffffffu, cy, k);
+      const int ok = __shfl_sync(0xffffffffu, qvalid ? 1 : 0, k);
+      const long long qq = __shfl_sync(0xffffffffu, q, k);
+      if (!ok) continue;
+      lookup_taps_level<R>(F + (16 * warp + k) * NCELL, ccx, ccy, l, p.out + qq * C, lane);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
+static int encode_4d(EncodeTiledFn encode, CUtensorMap* tm, const void* base, int twoD, int w, int h, int B, int box_x, int box_y) {
+  const cuuint64_t dims[4] = {(cuuint64_t)twoD, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)B};
+  const cuuint64_t strides[3] = {(cuuint64_t)twoD * 2, (cuuint64_t)w * twoD * 2, (cuuint64_t)h * w * twoD * 2};
+  const cuuint32_t box[4] = {64, (cuuint32_t)box_x, (cuuint32_t)box_y, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  return encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS
+             ? RAFTK_OK
+             : RAFTK_ERR_UNSUPPORTED;
+}
+
+}  // namespace atc
+}  // namespace raftk
+
+extern "C" int raftk_altcorr_split(const float* src, void* dst, long long rows, int D, float scale, void* stream) {
+  using namespace raftk;
+  if (rows < 0 || D <= 0) return RAFTK_ERR_SHAPE;
+  if (D % 4) return RAFTK_ERR_UNSUPPORTED;
+  if (rows == 0) return RAFTK_OK;
+  if (!src || !dst) return RAFTK_ERR_NULL;
+  if (((uintptr_t)src & 15) || ((uintptr_t)dst & 15)) return RAFTK_ERR_ALIGN;
+  const long long total = rows * (D / 4);
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)sm_count() * 8) blocks = (long long)sm_count() * 8;
+  atc::split_rows_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst), rows, D, scale);
+  return launch_status();
+}
+
+extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f2_levels, const void* f1_split,
+                                       const void* const* f2_split, int num_levels, const float* coords, float* out,
+                                       int B, int nq, int h, int w, int D, int radius, void* stream) {
+  using namespace raftk;
+  using namespace raftk::atc;
+  if (num_levels < 1 || num_levels > RAFTK_MAX_LEVELS || B < 0 || nq < 0 || h <= 0 || w <= 0 || D <= 0 || radius < 0)
+    return RAFTK_ERR_SHAPE;
+  if ((h >> (num_levels - 1)) < 1 || (w >> (num_levels - 1)) < 1) return RAFTK_ERR_TOO_SMALL;
+  if (num_levels > 4 || (radius != 3 && radius != 4) || D % 64 || D > 256 || nq % w) return RAFTK_ERR_UNSUPPORTED;
+  if ((long long)B * nq == 0) return RAFTK_OK;
+  if (!fmap1 || !f2_levels || !f1_split || !f2_split || !coords || !out) return RAFTK_ERR_NULL;
+  if (((uintptr_t)fmap1 & 15) || ((uintptr_t)f1_split & 15)) return RAFTK_ERR_ALIGN;
+  EncodeTiledFn encode = get_encode_fn();
+  if (!encode) return RAFTK_ERR_UNSUPPORTED;
+  Params p{};
+  CUtensorMap tmA, tmB[4];
+  memset(tmB, 0, sizeof(tmB));
+  const int rows_q = nq / w;
+  int rc = encode_4d(encode, &tmA, f1_split, 2 * D, w, rows_q, B, 8, 8);
+  if (rc != RAFTK_OK) return rc;
+  for (int l = 0; l < 4; ++l) {
+    const int ll = l < num_levels ? l : num_levels - 1;  // unused slots repeat the last level
+    if (!f2_levels[ll] || !f2_split[ll]) return RAFTK_ERR_NULL;
+    if (((uintptr_t)f2_levels[ll] & 15) || ((uintptr_t)f2_split[ll] & 15)) return RAFTK_ERR_ALIGN;
+    p.f2[l] = f2_levels[ll];
+    p.lh[l] = h >> ll;
+    p.lw[l] = w >> ll;
+    rc = encode_4d(encode, &tmB[l], f2_split[ll], 2 * D, w >> ll, h >> ll, B, 8, ROWS);
+    if (rc != RAFTK_OK) return rc;
+  }
+  p.f1 = fmap1;
+  p.coords = coords;
+  p.out = out;
+  p.B = B;
+  p.nq = nq;
+  p.D = D;
+  p.L = num_levels;
+  p.rows_q = rows_q;
+  p.w_q = w;
+  p.inv_sqrt_d = 1.0f / (float)sqrt((double)D);
+  const int FP = 2 * radius + 2;
+  const size_t smem = 1024 + (size_t)2 * (D / 64) * A_BLOCK_BYTES + (size_t)STAGES * B_STAGE_BYTES +
+                      (size_t)TQ * FP * FP * sizeof(float) + 128 + 128 + TQ * sizeof(QInfo);
+  if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
+  const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8) * num_levels;
+  if (nblk > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
+  auto kernel = radius == 4 ? altcorr_tc_kernel<4> : altcorr_tc_kernel<3>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  kernel<<<(unsigned)nblk, NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB[0], tmB[1], tmB[2], tmB[3], p);
+  return launch_status();
+}
