@@ -49,14 +49,14 @@ namespace atc {
 using namespace raftk::ptx;
 
 constexpr int TQ = 64;                          // queries per CTA: 8 x 8
-constexpr int ROWS = 6;                         // box rows per chunk
+constexpr int MAX_ROWS = 6;                     // box rows per chunk: 4, 5 or 6, chosen per level on the host
 constexpr int MAX_CB = 4;                       // column blocks of 8 cells: box width <= 32
-constexpr int MAX_CHUNKS = 5;                   // box height <= 30
-constexpr int CB_BYTES = ROWS * 8 * 128;        // one TMA box {64 bf16, 8 cells, 6 rows}
-constexpr int B_STAGE_BYTES = MAX_CB * CB_BYTES;
-constexpr int STAGES = 4;
+constexpr int MAX_CHUNKS = 6;                   // box height <= 6 * rows per chunk
+constexpr int RING_BYTES = 80 * 1024;           // B ring: as many stages as fit (3 of 24 KB ... 8 of 10 KB)
+constexpr int ROWBUF_PITCH = 36;                // floats per lane of the row buffer (+4: 16-byte stores of 8 lanes hit 32 banks)
+constexpr int MAX_STAGES = 8;
 constexpr int A_BLOCK_BYTES = TQ * 128;
-constexpr int ACC_COLS = MAX_CB * ROWS * 8;     // 192 accumulator columns per buffer
+constexpr int ACC_COLS = MAX_CB * MAX_ROWS * 8;  // 192 accumulator columns per buffer
 constexpr int NUM_THREADS = 192;                // warps 0-3 epilogue, 4 TMA producer, 5 MMA issuer + TMEM
 constexpr int SMEM_LIMIT = 232448;
 
@@ -64,6 +64,7 @@ struct Params {
   const float* f1;      // float32 sources, used by the scalar path only
   const float* f2[4];
   int lh[4], lw[4];
+  int rows[4];          // box rows per chunk of each level (= the y extent of that level's TMA box)
   const float* coords;
   float* out;
   int B, nq, D, L;
@@ -96,6 +97,60 @@ __global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict
   }
 }
 
+// The (2r+1)^2 taps of level l for the 16 queries of one warp, as COLUMN TASKS (the schedule of corr_lookup_tiled.cu):
+// a lane owns (query k, x offset i) and walks the 2r+1 y offsets, reusing the two footprint values of row j + 1 as
+// row j of the next tap; x weights once per task.  Arithmetic per tap as the reference evaluates it (jax
+// map_coordinates order 1, float32, no contraction), anchored at the regular cell floor(c_l) + d:
+//   s = c_l + d;  w1 = s - (floor(c_l) + d);  w0 = 1 - w1;  out = ((wy0 wx0) v00 + (wy0 wx1) v01) + (wy1 wx0) v10 + (wy1 wx1) v11
+// (identical to i0 = floor(s) except when fl(c_l + d) rounds up to an integer, where the same products appear with the
+// unit weight on the other corner: corr_lookup_tiled.cu, "Arithmetic").  Fw: the warp's footprints [16][(2r+2)^2],
+// origin floor(c_l) - r; (cx, cy, qvalid, q) are those of the query THIS lane owns (lanes 0-15).
+template <int R>
+__device__ __forceinline__ void column_taps_level(const float* Fw, float cx, float cy, bool qvalid, long long q, int l,
+                                                  float* out, int C, int lane) {
+  constexpr int S = 2 * R + 1, FP = 2 * R + 2, NCELL = FP * FP;
+  const float sc = __int_as_float((127 - l) << 23);  // 2^-l, exact
+#pragma unroll 1
+  for (int base = 0; base < 16 * S; base += 32) {
+    const int T = base + lane;
+    const bool active = T < 16 * S;
+    const int k = active ? T / S : 0, i = T - k * S;
+    const float ccx = __shfl_sync(0xffffffffu, cx, k), ccy = __shfl_sync(0xffffffffu, cy, k);
+    const int ok = __shfl_sync(0xffffffffu, qvalid ? 1 : 0, k);
+    const long long qq = __shfl_sync(0xffffffffu, q, k);
+    if (!active || !ok) continue;
+    const float cxl = ccx * sc, cyl = ccy * sc;
+    const float fcx = floorf(cxl), fcy = floorf(cyl);
+    const float dx = (float)(i - R);
+    const float wx1 = __fadd_rn(__fadd_rn(cxl, dx), -__fadd_rn(fcx, dx));
+    const float wx0 = __fadd_rn(1.0f, -wx1);
+    const float* Fc = Fw + k * NCELL + i;
+    float* orow = out + qq * C + l * S * S + i * S;
+    float fa = Fc[0], fb = Fc[1];
+#pragma unroll
+    for (int j = 0; j < S; ++j) {
+      const float dy = (float)(j - R);
+      const float wy1 = __fadd_rn(__fadd_rn(cyl, dy), -__fadd_rn(fcy, dy));
+      const float wy0 = __fadd_rn(1.0f, -wy1);
+      const float na = Fc[(j + 1) * FP], nb = Fc[(j + 1) * FP + 1];
+      float acc = __fmul_rn(__fmul_rn(wy0, wx0), fa);
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy0, wx1), fb));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx0), na));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(wy1, wx1), nb));
+      orow[j] = acc;
+      fa = na;
+      fb = nb;
+    }
+  }
+}
+
+// what every role needs to know about one level of the patch (shared memory, written once)
+struct LevelBox {
+  int X0, Y0, BW, BH;   // bounding box of the windows (BW = 0: no query of the patch has a window at this level)
+  int tc;               // 1: tensor-core path (the box fits), 0: scalar path
+  int ncb, nchunks, rows;
+};
+
 template <int R>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
@@ -106,36 +161,31 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int KB = p.D / 64;  // k-blocks per plane (hi, mid)
   uint8_t* smem_a = smem;                                   // [2 KB][A_BLOCK_BYTES]: hi blocks, then mid blocks
-  uint8_t* smem_b = smem_a + 2 * KB * A_BLOCK_BYTES;        // [STAGES][B_STAGE_BYTES]
-  float* F = reinterpret_cast<float*>(smem_b + STAGES * B_STAGE_BYTES);  // [TQ][NCELL]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(F + TQ * NCELL);
-  uint64_t* a_full = bars;                 // [1]
-  uint64_t* b_full = bars + 1;             // [STAGES]
-  uint64_t* b_empty = b_full + STAGES;     // [STAGES]
-  uint64_t* acc_full = b_empty + STAGES;   // [2]
-  uint64_t* acc_empty = acc_full + 2;      // [2]
+  uint8_t* smem_b = smem_a + 2 * KB * A_BLOCK_BYTES;        // ring of RING_BYTES
+  float* F = reinterpret_cast<float*>(smem_b + RING_BYTES);  // [2][TQ][NCELL]: footprints of levels l and l + 1
+  float* rowbuf = F + 2 * TQ * NCELL;                        // [4 warps][32 lanes][ROWBUF_PITCH]: one box row per thread
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rowbuf + 4 * 32 * ROWBUF_PITCH);
+  uint64_t* a_full = bars;                      // [1]
+  uint64_t* b_full = bars + 1;                  // [MAX_STAGES]
+  uint64_t* b_empty = b_full + MAX_STAGES;      // [MAX_STAGES]
+  uint64_t* acc_full = b_empty + MAX_STAGES;    // [2]
+  uint64_t* acc_empty = acc_full + 2;           // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  int* red = reinterpret_cast<int*>(bars + 16);             // [5][4] per-warp partial box, then box[5]
-  int* box = red + 20;
-  QInfo* qinfo = reinterpret_cast<QInfo*>(red + 32);        // [TQ]
+  int* red = reinterpret_cast<int*>(bars + 32);             // [4 levels][5][4 warps]
+  LevelBox* lbox = reinterpret_cast<LevelBox*>(red + 80);   // [4]
+  QInfo* qinfo = reinterpret_cast<QInfo*>(lbox + 4);        // [4][TQ]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_x = (p.w_q + 7) >> 3, tiles_y = (p.rows_q + 7) >> 3;
-  const long long tiles = (long long)tiles_x * tiles_y * p.B;
-  const int l = (int)(blockIdx.x / tiles);  // level-major: the large level-0 boxes are scheduled first
-  long long rem = blockIdx.x - (long long)l * tiles;
+  long long rem = blockIdx.x;
   const int txi = (int)(rem % tiles_x);
   rem /= tiles_x;
   const int tyi = (int)(rem % tiles_y);
   const int b = (int)(rem / tiles_y);
-  const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
-  const int lh = l == 0 ? p.lh[0] : l == 1 ? p.lh[1] : l == 2 ? p.lh[2] : p.lh[3];
-  const int lw = l == 0 ? p.lw[0] : l == 1 ? p.lw[1] : l == 2 ? p.lw[2] : p.lw[3];
-  const float* f2l = l == 0 ? p.f2[0] : l == 1 ? p.f2[1] : l == 2 ? p.f2[2] : p.f2[3];
 
   if (warp == 5 && lane == 0) {
     mbar_init(a_full, 1);
-    for (int s = 0; s < STAGES; ++s) {
+    for (int s = 0; s < MAX_STAGES; ++s) {
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 1);
     }
@@ -150,18 +200,19 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
 
-  // ---- the queries of this patch, their window origins, and the bounding box of the windows ----
+  // ---- the queries of this patch, their window origins, and per level the bounding box of the windows ----
   // epilogue thread (warp w < 4, lane < 16) owns query m = 16 w + lane = (row m / 8, column m % 8) of the patch:
-  // the accumulator row its TMEM lane holds
-  const int m = 16 * warp + lane;
-  const bool owner = warp < 4 && lane < 16;
+  // the accumulator row its TMEM lane holds.
   // haswin: finite, not absurdly far, and the window overlaps the level.  Queries without a window read nothing —
   // their footprint is all zeros whatever path a patch takes — and stay out of the bounding box, so that one stray
   // query does not change how its neighbours are computed.
-  bool qvalid = false, haswin = false;
+  const int m = 16 * warp + lane;
+  const bool owner = warp < 4 && lane < 16;
+  bool qvalid = false;
   long long q = 0;
   float cx = 0.0f, cy = 0.0f;
-  int bx = 0, by = 0;
+  int bx[4] = {0, 0, 0, 0}, by[4] = {0, 0, 0, 0};
+  unsigned winmask = 0;  // bit l: this query has a window at level l
   if (owner) {
     const int qy = tyi * 8 + (m >> 3), qx = txi * 8 + (m & 7);
     qvalid = qy < p.rows_q && qx < p.w_q;
@@ -171,91 +222,118 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       cy = __ldg(p.coords + 2 * q + 1);
     }
     const bool normal = fabsf(cx) <= 1.0e6f && fabsf(cy) <= 1.0e6f;
-    const float sc = __int_as_float((127 - l) << 23);
-    bx = clamp_to_int(floorf(cx * sc)) - R;
-    by = clamp_to_int(floorf(cy * sc)) - R;
-    haswin = qvalid && normal && bx < lw && bx + FP > 0 && by < lh && by + FP > 0;
-    qinfo[m] = QInfo{bx, by, (qvalid ? 1 : 0) | (haswin ? 2 : 0), 0};
-    if (qvalid && !haswin)
-      for (int e = 0; e < NCELL; ++e) F[m * NCELL + e] = 0.0f;
-  }
-  {
-    int mnx = haswin ? bx : 0x7fffffff, mxx = haswin ? bx : -0x7fffffff;
-    int mny = haswin ? by : 0x7fffffff, mxy = haswin ? by : -0x7fffffff;
-    int any = haswin ? 1 : 0;
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-      mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, off));
-      mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, off));
-      mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, off));
-      mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, off));
-      any |= __shfl_xor_sync(0xffffffffu, any, off);
+    for (int l = 0; l < 4; ++l) {
+      if (l < p.L) {
+        const float sc = __int_as_float((127 - l) << 23);
+        bx[l] = clamp_to_int(floorf(cx * sc)) - R;
+        by[l] = clamp_to_int(floorf(cy * sc)) - R;
+        const bool hw = qvalid && normal && bx[l] < p.lw[l] && bx[l] + FP > 0 && by[l] < p.lh[l] && by[l] + FP > 0;
+        if (hw) winmask |= 1u << l;
+        qinfo[l * TQ + m] = QInfo{bx[l], by[l], (qvalid ? 1 : 0) | (hw ? 2 : 0), 0};
+      }
     }
-    if (warp < 4 && lane == 0) {
-      red[0 * 4 + warp] = mnx;
-      red[1 * 4 + warp] = mxx;
-      red[2 * 4 + warp] = mny;
-      red[3 * 4 + warp] = mxy;
-      red[4 * 4 + warp] = any;
+  }
+#pragma unroll
+  for (int l = 0; l < 4; ++l) {
+    if (l < p.L) {
+      const bool hw = (winmask >> l) & 1u;
+      int mnx = hw ? bx[l] : 0x7fffffff, mxx = hw ? bx[l] : -0x7fffffff;
+      int mny = hw ? by[l] : 0x7fffffff, mxy = hw ? by[l] : -0x7fffffff;
+      int any = hw ? 1 : 0;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, off));
+        mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, off));
+        mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, off));
+        mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, off));
+        any |= __shfl_xor_sync(0xffffffffu, any, off);
+      }
+      if (warp < 4 && lane == 0) {
+        int* rl = red + l * 20;
+        rl[0 * 4 + warp] = mnx;
+        rl[1 * 4 + warp] = mxx;
+        rl[2 * 4 + warp] = mny;
+        rl[3 * 4 + warp] = mxy;
+        rl[4 * 4 + warp] = any;
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (threadIdx.x == 0) {
-    int mnx = red[0], mxx = red[4], mny = red[8], mxy = red[12], any = red[16];
+  if (threadIdx.x < p.L) {
+    const int l = threadIdx.x;
+    const int* rl = red + l * 20;
+    int mnx = rl[0], mxx = rl[4], mny = rl[8], mxy = rl[12], any = rl[16];
     for (int i = 1; i < 4; ++i) {
-      mnx = min(mnx, red[i]);
-      mxx = max(mxx, red[4 + i]);
-      mny = min(mny, red[8 + i]);
-      mxy = max(mxy, red[12 + i]);
-      any |= red[16 + i];
+      mnx = min(mnx, rl[i]);
+      mxx = max(mxx, rl[4 + i]);
+      mny = min(mny, rl[8 + i]);
+      mxy = max(mxy, rl[12 + i]);
+      any |= rl[16 + i];
     }
-    box[0] = any ? mnx : 0;
-    box[1] = any ? mny : 0;
-    box[2] = any ? mxx - mnx + FP : 0;  // width in cells (0: no query of the patch has a window)
-    box[3] = any ? mxy - mny + FP : 0;  // height
+    LevelBox lb;
+    lb.X0 = any ? mnx : 0;
+    lb.Y0 = any ? mny : 0;
+    lb.BW = any ? mxx - mnx + FP : 0;  // width in cells
+    lb.BH = any ? mxy - mny + FP : 0;  // height
+    lb.rows = p.rows[l];
+    lb.tc = (lb.BW <= 8 * MAX_CB && lb.BH <= lb.rows * MAX_CHUNKS) ? 1 : 0;
+    lb.ncb = (lb.BW + 7) >> 3;
+    lb.nchunks = (lb.BH + lb.rows - 1) / lb.rows;
+    lbox[l] = lb;
   }
   __syncthreads();
   const uint32_t tmem_base = *tmem_slot;
-  const int X0 = box[0], Y0 = box[1], BW = box[2], BH = box[3];
-  const bool tc_path = BW <= 8 * MAX_CB && BH <= ROWS * MAX_CHUNKS;
-  const int ncb = (BW + 7) >> 3, nchunks = (BH + ROWS - 1) / ROWS;
+  // ring geometry: one stage holds the widest chunk of this patch's tensor-core levels
+  int stage_bytes = 8 * 1024;
+  for (int l = 0; l < p.L; ++l)
+    if (lbox[l].tc) stage_bytes = max(stage_bytes, lbox[l].ncb * lbox[l].rows * 1024);
+  const int nstages = min(MAX_STAGES, RING_BYTES / stage_bytes);
 
-  if (tc_path) {
-    if (warp == 4) {
-      // ===================== TMA producer =====================
-      if (lane == 0) {
-        mbar_expect_tx(a_full, (uint32_t)(2 * KB * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
-        for (int j = 0; j < 2 * KB; ++j)  // [hi | mid] is contiguous in K: block j starts at channel 64 j
-          tma_load_4d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * 64, txi * 8, tyi * 8, b);
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int c = 0; c < nchunks; ++c)
+  if (warp == 4) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      mbar_expect_tx(a_full, (uint32_t)(2 * KB * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
+      for (int j = 0; j < 2 * KB; ++j)  // [hi | mid] is contiguous in K: block j starts at channel 64 j
+        tma_load_4d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * 64, txi * 8, tyi * 8, b);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int l = 0; l < p.L; ++l) {
+        const LevelBox lb = lbox[l];
+        if (!lb.tc) continue;
+        const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
+        const int cb_bytes = lb.rows * 1024;
+        for (int c = 0; c < lb.nchunks; ++c)
           for (int kb = 0; kb < KB; ++kb)
             for (int part = 0; part < 2; ++part) {
               mbar_wait(&b_empty[stage], phase ^ 1);
-              mbar_expect_tx(&b_full[stage], (uint32_t)(ncb * CB_BYTES));
-              for (int cb = 0; cb < ncb; ++cb)
-                tma_load_4d(tmB, &b_full[stage], smem_b + stage * B_STAGE_BYTES + cb * CB_BYTES,
-                            part * p.D + kb * 64, X0 + 8 * cb, Y0 + ROWS * c, b);
-              if (++stage == STAGES) {
+              mbar_expect_tx(&b_full[stage], (uint32_t)(lb.ncb * cb_bytes));
+              for (int cb = 0; cb < lb.ncb; ++cb)
+                tma_load_4d(tmB, &b_full[stage], smem_b + stage * stage_bytes + cb * cb_bytes, part * p.D + kb * 64,
+                            lb.X0 + 8 * cb, lb.Y0 + lb.rows * c, b);
+              if (++stage == nstages) {
                 stage = 0;
                 phase ^= 1;
               }
             }
       }
-    } else if (warp == 5) {
-      // ===================== MMA issuer =====================
-      if (lane == 0) {
-        const uint32_t idesc = make_idesc_bf16(TQ, ncb * ROWS * 8);
-        mbar_wait(a_full, 0);
-        tc_fence_after();
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int c = 0; c < nchunks; ++c) {
-          const int buf = c & 1;
-          mbar_wait(&acc_empty[buf], ((c >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      mbar_wait(a_full, 0);
+      tc_fence_after();
+      int stage = 0, g = 0;  // g: chunks issued so far (accumulator g & 1)
+      uint32_t phase = 0;
+      for (int l = 0; l < p.L; ++l) {
+        const LevelBox lb = lbox[l];
+        if (!lb.tc) continue;
+        const uint32_t idesc = make_idesc_bf16(TQ, lb.ncb * lb.rows * 8);
+        for (int c = 0; c < lb.nchunks; ++c, ++g) {
+          const int buf = g & 1;
+          mbar_wait(&acc_empty[buf], ((g >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + (uint32_t)buf * ACC_COLS;
           for (int kb = 0; kb < KB; ++kb) {
@@ -264,24 +342,24 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             // stage holding B_hi[kb]: hi*hi and mid*hi
             mbar_wait(&b_full[stage], phase);
             tc_fence_after();
-            uint32_t bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
+            uint32_t bs = smem_u32(smem_b + stage * stage_bytes);
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_hi + 32 * k4), umma_desc(bs + 32 * k4), idesc, (kb | k4) != 0);
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_mid + 32 * k4), umma_desc(bs + 32 * k4), idesc, 1);
             tc_commit(&b_empty[stage]);
-            if (++stage == STAGES) {
+            if (++stage == nstages) {
               stage = 0;
               phase ^= 1;
             }
             // stage holding B_mid[kb]: hi*mid
             mbar_wait(&b_full[stage], phase);
             tc_fence_after();
-            bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
+            bs = smem_u32(smem_b + stage * stage_bytes);
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_hi + 32 * k4), umma_desc(bs + 32 * k4), idesc, 1);
             tc_commit(&b_empty[stage]);
-            if (++stage == STAGES) {
+            if (++stage == nstages) {
               stage = 0;
               phase ^= 1;
             }
@@ -289,77 +367,91 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           tc_commit(&acc_full[buf]);
         }
       }
-    } else {
-      // ===================== epilogue: window extraction =====================
-      const int ox = bx - X0, oy = by - Y0;  // this query's window origin inside the box
-      float* Fq = F + m * NCELL;
-      for (int c = 0; c < nchunks; ++c) {
-        const int buf = c & 1;
-        mbar_wait(&acc_full[buf], (c >> 1) & 1);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * ACC_COLS;
-#pragma unroll 1
-        for (int r = 0; r < ROWS; ++r) {
-          const int row = c * ROWS + r;  // box row
-          if (row >= BH) break;
-          float v[8 * MAX_CB];
-#pragma unroll
-          for (int cb = 0; cb < MAX_CB; ++cb)
-            if (cb < ncb) tmem_ld_32x8(taddr + (uint32_t)(cb * ROWS * 8 + r * 8), v + 8 * cb);
-          tmem_ld_wait();
-          const int wr = row - oy;
-          if (haswin && (unsigned)wr < (unsigned)FP) {
-            float* Fr = Fq + wr * FP - ox;
-#pragma unroll
-            for (int i = 0; i < 8 * MAX_CB; ++i)
-              if (i < 8 * ncb && (unsigned)(i - ox) < (unsigned)FP) Fr[i] = v[i];
-          }
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[buf]);
-      }
     }
-  } else if (warp < 4) {
-    // ===================== scalar path: the windows of this patch do not fit one box (rough flow) =====================
-    const int t = threadIdx.x, qi = t >> 1, sub = t & 1;
-    const QInfo qi_info = qinfo[qi];
-    const bool v_ok = (qi_info.flags & 1) != 0, n_ok = (qi_info.flags & 2) != 0;  // n_ok implies v_ok
-    const int qy = tyi * 8 + (qi >> 3), qx = txi * 8 + (qi & 7);
-    const long long qq = (long long)b * p.nq + (long long)qy * p.w_q + qx;
-    const float* f1q = p.f1 + (v_ok ? qq : 0) * p.D;
-    const float* f2b = f2l + (long long)b * lh * lw * p.D;
-#pragma unroll 1
-    for (int i = 0; i < NCELL / 2; ++i) {
-      const int e = sub + 2 * i;
-      const int ry = e / FP, rx = e - ry * FP;
-      const int gy = qi_info.by + ry, gx = qi_info.bx + rx;
-      float s = 0.0f;
-      if (v_ok && n_ok && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) {
-        const float4* cp = reinterpret_cast<const float4*>(f2b + ((long long)gy * lw + gx) * p.D);
-        const float4* ap = reinterpret_cast<const float4*>(f1q);
-        for (int k = 0; k < p.D / 4; ++k) {
-          const float4 vv = __ldg(cp + k), a = __ldg(ap + k);
-          s = fmaf(a.x, vv.x, s);
-          s = fmaf(a.y, vv.y, s);
-          s = fmaf(a.z, vv.z, s);
-          s = fmaf(a.w, vv.w, s);
-        }
-      }
-      F[qi * NCELL + e] = s * p.inv_sqrt_d;
-    }
-  }
-
-  // ---- taps of level l: warp w takes its queries 16 w .. 16 w + 15 ----
-  if (warp < 4) {
-    asm volatile("bar.sync 1, 128;" ::: "memory");  // every footprint of the patch is complete
+  } else {
+    // ===================== epilogue warps: window extraction, then the taps, level by level =====================
     const int C = p.L * S * S;
-    for (int k = 0; k < 16; ++k) {
-      const float ccx = __shfl_sync(0xffffffffu, cx, k), ccy = __shfl_sync(0xffffffffu, cy, k);
-      const int ok = __shfl_sync(0xffffffffu, qvalid ? 1 : 0, k);
-      const long long qq = __shfl_sync(0xffffffffu, q, k);
-      if (!ok) continue;
-      lookup_taps_level<R>(F + (16 * warp + k) * NCELL, ccx, ccy, l, p.out + qq * C, lane);
+    int g = 0;
+    for (int l = 0; l < p.L; ++l) {
+      const LevelBox lb = lbox[l];
+      float* Fl = F + (l & 1) * TQ * NCELL;  // level l + 1 fills the other buffer while stragglers still read this one
+      float* Fq = Fl + m * NCELL;
+      const bool haswin = (winmask >> l) & 1u;
+      if (owner && qvalid && !haswin)
+        for (int e = 0; e < NCELL; ++e) Fq[e] = 0.0f;
+      if (lb.tc) {
+        const int ox = (l == 0 ? bx[0] : l == 1 ? bx[1] : l == 2 ? bx[2] : bx[3]) - lb.X0;  // window origin inside the box
+        const int oy = (l == 0 ? by[0] : l == 1 ? by[1] : l == 2 ? by[2] : by[3]) - lb.Y0;
+        for (int c = 0; c < lb.nchunks; ++c, ++g) {
+          const int buf = g & 1;
+          mbar_wait(&acc_full[buf], (g >> 1) & 1);
+          tc_fence_after();
+          const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * ACC_COLS;
+#pragma unroll 1
+          for (int r = 0; r < lb.rows; ++r) {
+            const int row = c * lb.rows + r;  // box row
+            if (row >= lb.BH) break;
+            float v[8 * MAX_CB];
+#pragma unroll
+            for (int cb = 0; cb < MAX_CB; ++cb)
+              if (cb < lb.ncb) tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + r * 8), v + 8 * cb);
+            tmem_ld_wait();
+            // the row goes to this thread's row buffer (16-byte stores, static register indices); the <= 2r+2 cells
+            // of the thread's own window are then copied out at a dynamic shared-memory offset
+            float* rb = rowbuf + (warp * 32 + lane) * ROWBUF_PITCH;
+#pragma unroll
+            for (int cb = 0; cb < MAX_CB; ++cb)
+              if (cb < lb.ncb) {
+                *reinterpret_cast<float4*>(rb + 8 * cb) = make_float4(v[8 * cb], v[8 * cb + 1], v[8 * cb + 2], v[8 * cb + 3]);
+                *reinterpret_cast<float4*>(rb + 8 * cb + 4) = make_float4(v[8 * cb + 4], v[8 * cb + 5], v[8 * cb + 6], v[8 * cb + 7]);
+              }
+            const int wr = row - oy;
+            if (haswin && (unsigned)wr < (unsigned)FP) {
+              float* Fr = Fq + wr * FP;
+              const float* src = rb + ox;
+#pragma unroll
+              for (int wc = 0; wc < FP; ++wc) Fr[wc] = src[wc];
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        }
+      } else {
+        // scalar path: the windows of this patch do not fit one box at this level (rough flow)
+        const int t = threadIdx.x, qi = t >> 1, sub = t & 1;
+        const QInfo qi_info = qinfo[l * TQ + qi];
+        const bool n_ok = (qi_info.flags & 2) != 0;
+        const int qy = tyi * 8 + (qi >> 3), qx = txi * 8 + (qi & 7);
+        const long long qq = (long long)b * p.nq + (long long)qy * p.w_q + qx;
+        const int lh = l == 0 ? p.lh[0] : l == 1 ? p.lh[1] : l == 2 ? p.lh[2] : p.lh[3];
+        const int lw = l == 0 ? p.lw[0] : l == 1 ? p.lw[1] : l == 2 ? p.lw[2] : p.lw[3];
+        const float* f2l = l == 0 ? p.f2[0] : l == 1 ? p.f2[1] : l == 2 ? p.f2[2] : p.f2[3];
+        const float* f1q = p.f1 + (n_ok ? qq : 0) * p.D;
+        const float* f2b = f2l + (long long)b * lh * lw * p.D;
+#pragma unroll 1
+        for (int i = 0; i < NCELL / 2; ++i) {
+          const int e = sub + 2 * i;
+          const int ry = e / FP, rx = e - ry * FP;
+          const int gy = qi_info.by + ry, gx = qi_info.bx + rx;
+          float s = 0.0f;
+          if (n_ok && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) {
+            const float4* cp = reinterpret_cast<const float4*>(f2b + ((long long)gy * lw + gx) * p.D);
+            const float4* ap = reinterpret_cast<const float4*>(f1q);
+            for (int k = 0; k < p.D / 4; ++k) {
+              const float4 vv = __ldg(cp + k), a = __ldg(ap + k);
+              s = fmaf(a.x, vv.x, s);
+              s = fmaf(a.y, vv.y, s);
+              s = fmaf(a.z, vv.z, s);
+              s = fmaf(a.w, vv.w, s);
+            }
+          }
+          Fl[qi * NCELL + e] = s * p.inv_sqrt_d;
+        }
+      }
+      // ---- taps of level l: warp w takes its queries 16 w .. 16 w + 15 (the MMAs of level l + 1 run meanwhile) ----
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // every footprint of the patch at this level is complete
+      column_taps_level<R>(Fl + 16 * warp * NCELL, cx, cy, qvalid, q, l, p.out, C, lane);
     }
   }
 
@@ -428,7 +520,19 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
     p.f2[l] = f2_levels[ll];
     p.lh[l] = h >> ll;
     p.lw[l] = w >> ll;
-    rc = encode_4d(encode, &tmB[l], f2_split[ll], 2 * D, w >> ll, h >> ll, B, 8, ROWS);
+    // box rows per chunk: the typical box of an 8 x 8 patch is FP + (7 >> l) + 2 rows tall; take the chunk height in
+    // {4, 5, 6} that pads it least (ties: the taller chunk)
+    {
+      const int typ = 2 * radius + 2 + (7 >> ll) + 2;
+      int best = 6, waste = (typ + 5) / 6 * 6 - typ;
+      for (int rr = 5; rr >= 4; --rr)
+        if ((typ + rr - 1) / rr * rr - typ < waste) {
+          waste = (typ + rr - 1) / rr * rr - typ;
+          best = rr;
+        }
+      p.rows[l] = best;
+    }
+    rc = encode_4d(encode, &tmB[l], f2_split[ll], 2 * D, w >> ll, h >> ll, B, 8, p.rows[l]);
     if (rc != RAFTK_OK) return rc;
   }
   p.f1 = fmap1;
@@ -442,10 +546,11 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   p.w_q = w;
   p.inv_sqrt_d = 1.0f / (float)sqrt((double)D);
   const int FP = 2 * radius + 2;
-  const size_t smem = 1024 + (size_t)2 * (D / 64) * A_BLOCK_BYTES + (size_t)STAGES * B_STAGE_BYTES +
-                      (size_t)TQ * FP * FP * sizeof(float) + 128 + 128 + TQ * sizeof(QInfo);
+  const size_t smem = 1024 + (size_t)2 * (D / 64) * A_BLOCK_BYTES + (size_t)RING_BYTES +
+                      (size_t)2 * TQ * FP * FP * sizeof(float) + (size_t)4 * 32 * ROWBUF_PITCH * sizeof(float) + 256 + 320 +
+                      4 * sizeof(LevelBox) + 4 * TQ * sizeof(QInfo);
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
-  const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8) * num_levels;
+  const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8);
   if (nblk > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
   auto kernel = radius == 4 ? altcorr_tc_kernel<4> : altcorr_tc_kernel<3>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
