@@ -3,36 +3,45 @@
 //   pool_l(f1 . f2^T)[q, Y, X] = f1[q] . pool_l(f2)[Y, X]
 // the taps of level l (model.py:448-470) are bilinear samples of dot products against fmap2 pooled l times.
 //
-// One CTA = one 8 x 8 patch of query pixels at ONE level (UMMA M = 64, cta_group::1).  Neighbouring windows
-// overlap, so the CTA computes the correlations of its 64 queries with every cell of the BOUNDING BOX of their
-// (2r+2)^2 windows — a (64 x box cells x D) GEMM — and each query then picks its own window out of the box:
+// One CTA = one 8 x 8 patch of query pixels, all levels in turn (UMMA M = 64, cta_group::1).  Neighbouring windows
+// overlap, so per level the CTA computes the correlations of its 64 queries with every cell of the BOUNDING BOX of
+// their (2r+2)^2 windows — a (64 x box cells x D) GEMM — and each query then picks its own window out of the box:
 //
 //   operands   bf16 [hi | mid] splits of fmap1 (scaled by 1/sqrt(D)) and of every pooled fmap2 level, written once
 //              per pair by raftk_altcorr_split; products hi*hi + mid*hi + hi*mid in float32 (the scheme of the
 //              volume GEMM, corr_volume_tc.cu: ~2e-5 relative).
-//   A          the 64 queries x 2D tile, resident: 2 * D/64 TMA boxes {64 ch, 8 x, 8 y} (64 KB at D = 256).
-//   B          the box, in CHUNKS of 6 box rows; a chunk is up to four column blocks of 8 cells, each one TMA box
-//              {64 ch, 8 cells, 6 rows} = 48 operand rows, so N = 48, 96, 144 or 192 and a box may be up to 32 cells
-//              wide and 30 rows tall (TMA zero-fills cells outside the level: those correlations are 0, which is
-//              what the reference's zero-outside sampling makes of them).  One (chunk, k-block, hi | mid) slab per
-//              stage of a 4-stage ring.
+//   A          the 64 queries x 2D tile, resident for all levels: 2 * D/64 TMA boxes {64 ch, 8 x, 8 y} (64 KB at D = 256).
+//   B          the box, in CHUNKS of 4-6 box rows (per level, chosen on the host to pad the typical box least); a chunk
+//              is up to four column blocks of 8 cells, each one TMA box {64 ch, 8 cells, rows}, so N = 8 * rows * (1..4)
+//              <= 192 and a box may be up to 32 cells wide and 6 chunks tall (TMA zero-fills cells outside the level:
+//              those correlations are 0, which is what the reference's zero-outside sampling makes of them).  One
+//              (chunk, k-block, hi | mid) slab per stage of a ring of as many stages as fit 80 KB (4 ... 8).
 //   D          float32 in TMEM, two accumulators of 192 columns: the epilogue of chunk c runs under the MMAs of
-//              chunk c + 1.  M = 64: accumulator row m is TMEM lane (m % 16) + 32 * (m / 16).
-//   epilogue   warp w owns queries 16w .. 16w+15.  Per box row: tcgen05.ld.x8 per column block (up to 32 cells in
-//              registers, static indices), and every thread stores the <= 2r+2 cells of that row that belong to its
-//              own window into its footprint F[query][(2r+2)^2] in shared memory (predicated stores; the window
-//              offset is a shared-memory address, never a register index).  When the last chunk is in, the warp
-//              evaluates the taps of its queries with the shared lookup code (lookup_taps.cuh) — the window
-//              indexing and the float32 tap arithmetic are those of the volume lookup.
+//              chunk c + 1, across level boundaries too.  M = 64: accumulator row m is TMEM lane (m % 16) + 32 * (m / 16).
+//   epilogue   eight warps, two per TMEM lane quarter (its 16 queries); the pair splits the rows of a chunk.  Per box
+//              row: tcgen05.ld.x8 per column block (static register indices), the row goes to the thread's row buffer
+//              in shared memory, and the <= 2r+2 cells of the thread's own window are copied from there into its
+//              footprint F[query][(2r+2)^2] — the window offset is a shared-memory address, never a register index.
+//              Footprints are double-buffered per level: when the last chunk of level l is in, the warps evaluate its
+//              taps as column tasks (the schedule and the float32 arithmetic of corr_lookup_tiled.cu: window indexing
+//              and tap values are those of the volume lookup) while the MMAs of level l + 1 fill the accumulators.
 //
 // A cell's value depends only on the query's row of A, the cell's row of B and the fixed K order, not on the box or
 // the chunk it was computed in, so row bands reproduce the full result bit for bit.  Queries that read nothing (far or
 // non-finite coordinates, windows entirely outside the level) get a zero footprint and stay out of the box.  Boxes
-// that do not fit (rough flow: wider than 32 or taller than 30 cells) take a scalar fp32 path inside the same kernel
-// (sequential fma chain over D, as altcorr.cu), slower and ~2e-5 away from the split product.
+// that do not fit (rough flow: wider than 32 cells or taller than 6 chunks) take a scalar fp32 path inside the same
+// kernel (sequential fma chain over D, as altcorr.cu), slower and ~2e-5 away from the split product.
 //
-// Work per iteration at 136 x 240, r = 4, D = 256: 2040 CTAs (510 patches x 4 levels, level 0 first); a level-0 box
-// of ~20 x 20 cells is 4 chunks x 48 MMAs (M64 N144 K16).
+// Measured, 136 x 240, r = 4, D = 256, smooth +-8 px flow (profiles/altcorr_time.py): 162 us per iteration against
+// 560 us for the float32 FMA kernel (altcorr.cu).  510 CTAs = 3.45 waves of ~40 us.  Phase elimination on the GPU
+// (loads, MMAs, extraction, taps switched off in turn): ~15 us per CTA is fixed cost (launch, TMEM allocation, the
+// coordinate fetch and box reduction, the A tile, 96 stage and 12 accumulator hand-shakes), ~20 us the MMAs — M = 64
+// runs the tensor pipe at half rate, and a stage is only 4-8 MMAs of ~60 cycles — and the window extraction and the
+// taps (~6 and ~8 us) hide under them except at the level boundaries; the TMA loads are not on the critical path.
+// Eight epilogue warps instead of four changed nothing (the epilogue is latency-, not issue-bound).  What would move
+// it further: M = 128 (a CTA pair over a 16 x 8 patch sharing one box: full tensor rate and 1/3 less box traffic;
+// the 128 KB A tile + 51 KB of footprints leave no room for it in one CTA), and persistent CTAs that fetch the next
+// patch's coordinates and A tile under the current patch's MMAs.
 
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -57,7 +66,9 @@ constexpr int ROWBUF_PITCH = 36;                // floats per lane of the row bu
 constexpr int MAX_STAGES = 8;
 constexpr int A_BLOCK_BYTES = TQ * 128;
 constexpr int ACC_COLS = MAX_CB * MAX_ROWS * 8;  // 192 accumulator columns per buffer
-constexpr int NUM_THREADS = 192;                // warps 0-3 epilogue, 4 TMA producer, 5 MMA issuer + TMEM
+constexpr int EPI_WARPS = 8;                    // two per TMEM lane quarter (warp % 4): even / odd box rows, 8 queries of taps each
+constexpr int PRODUCER_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1;
+constexpr int NUM_THREADS = (EPI_WARPS + 2) * 32;
 constexpr int SMEM_LIMIT = 232448;
 
 struct Params {
@@ -107,14 +118,14 @@ __global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict
 // origin floor(c_l) - r; (cx, cy, qvalid, q) are those of the query THIS lane owns (lanes 0-15).
 template <int R>
 __device__ __forceinline__ void column_taps_level(const float* Fw, float cx, float cy, bool qvalid, long long q, int l,
-                                                  float* out, int C, int lane) {
+                                                  float* out, int C, int lane, int half) {
   constexpr int S = 2 * R + 1, FP = 2 * R + 2, NCELL = FP * FP;
   const float sc = __int_as_float((127 - l) << 23);  // 2^-l, exact
 #pragma unroll 1
-  for (int base = 0; base < 16 * S; base += 32) {
+  for (int base = 0; base < 8 * S; base += 32) {  // this warp's 8 of the quarter's 16 queries: k = 8 half .. 8 half + 7
     const int T = base + lane;
-    const bool active = T < 16 * S;
-    const int k = active ? T / S : 0, i = T - k * S;
+    const bool active = T < 8 * S;
+    const int k = 8 * half + (active ? T / S : 0), i = T - (k - 8 * half) * S;
     const float ccx = __shfl_sync(0xffffffffu, cx, k), ccy = __shfl_sync(0xffffffffu, cy, k);
     const int ok = __shfl_sync(0xffffffffu, qvalid ? 1 : 0, k);
     const long long qq = __shfl_sync(0xffffffffu, q, k);
@@ -163,8 +174,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smem_a = smem;                                   // [2 KB][A_BLOCK_BYTES]: hi blocks, then mid blocks
   uint8_t* smem_b = smem_a + 2 * KB * A_BLOCK_BYTES;        // ring of RING_BYTES
   float* F = reinterpret_cast<float*>(smem_b + RING_BYTES);  // [2][TQ][NCELL]: footprints of levels l and l + 1
-  float* rowbuf = F + 2 * TQ * NCELL;                        // [4 warps][32 lanes][ROWBUF_PITCH]: one box row per thread
-  uint64_t* bars = reinterpret_cast<uint64_t*>(rowbuf + 4 * 32 * ROWBUF_PITCH);
+  float* rowbuf = F + 2 * TQ * NCELL;                        // [EPI_WARPS][16 owner lanes][ROWBUF_PITCH]: one box row per thread
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rowbuf + EPI_WARPS * 16 * ROWBUF_PITCH);
   uint64_t* a_full = bars;                      // [1]
   uint64_t* b_full = bars + 1;                  // [MAX_STAGES]
   uint64_t* b_empty = b_full + MAX_STAGES;      // [MAX_STAGES]
@@ -183,7 +194,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int tyi = (int)(rem % tiles_y);
   const int b = (int)(rem / tiles_y);
 
-  if (warp == 5 && lane == 0) {
+  if (warp == MMA_WARP && lane == 0) {
     mbar_init(a_full, 1);
     for (int s = 0; s < MAX_STAGES; ++s) {
       mbar_init(&b_full[s], 1);
@@ -191,23 +202,24 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[i], EPI_WARPS);  // one arrival per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 5) {
+  if (warp == MMA_WARP) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
 
   // ---- the queries of this patch, their window origins, and per level the bounding box of the windows ----
-  // epilogue thread (warp w < 4, lane < 16) owns query m = 16 w + lane = (row m / 8, column m % 8) of the patch:
-  // the accumulator row its TMEM lane holds.
+  // epilogue thread (warp w < 8, lane < 16) owns query m = 16 (w % 4) + lane = (row m / 8, column m % 8) of the
+  // patch: the accumulator row its TMEM lane holds (warps w and w + 4 share a lane quarter and its 16 queries).
   // haswin: finite, not absurdly far, and the window overlaps the level.  Queries without a window read nothing —
   // their footprint is all zeros whatever path a patch takes — and stay out of the bounding box, so that one stray
   // query does not change how its neighbours are computed.
-  const int m = 16 * warp + lane;
-  const bool owner = warp < 4 && lane < 16;
+  const int quarter = warp & 3, half = warp >> 2;
+  const int m = 16 * quarter + lane;
+  const bool owner = warp < EPI_WARPS && lane < 16;
   bool qvalid = false;
   long long q = 0;
   float cx = 0.0f, cy = 0.0f;
@@ -230,7 +242,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         by[l] = clamp_to_int(floorf(cy * sc)) - R;
         const bool hw = qvalid && normal && bx[l] < p.lw[l] && bx[l] + FP > 0 && by[l] < p.lh[l] && by[l] + FP > 0;
         if (hw) winmask |= 1u << l;
-        qinfo[l * TQ + m] = QInfo{bx[l], by[l], (qvalid ? 1 : 0) | (hw ? 2 : 0), 0};
+        if (half == 0) qinfo[l * TQ + m] = QInfo{bx[l], by[l], (qvalid ? 1 : 0) | (hw ? 2 : 0), 0};
       }
     }
   }
@@ -292,7 +304,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (lbox[l].tc) stage_bytes = max(stage_bytes, lbox[l].ncb * lbox[l].rows * 1024);
   const int nstages = min(MAX_STAGES, RING_BYTES / stage_bytes);
 
-  if (warp == 4) {
+  if (warp == PRODUCER_WARP) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       mbar_expect_tx(a_full, (uint32_t)(2 * KB * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
@@ -320,7 +332,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == MMA_WARP) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       mbar_wait(a_full, 0);
@@ -377,7 +389,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       float* Fl = F + (l & 1) * TQ * NCELL;  // level l + 1 fills the other buffer while stragglers still read this one
       float* Fq = Fl + m * NCELL;
       const bool haswin = (winmask >> l) & 1u;
-      if (owner && qvalid && !haswin)
+      if (owner && half == 0 && qvalid && !haswin)
         for (int e = 0; e < NCELL; ++e) Fq[e] = 0.0f;
       if (lb.tc) {
         const int ox = (l == 0 ? bx[0] : l == 1 ? bx[1] : l == 2 ? bx[2] : bx[3]) - lb.X0;  // window origin inside the box
@@ -386,9 +398,9 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const int buf = g & 1;
           mbar_wait(&acc_full[buf], (g >> 1) & 1);
           tc_fence_after();
-          const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16) + (uint32_t)buf * ACC_COLS;
+          const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * ACC_COLS;
 #pragma unroll 1
-          for (int r = 0; r < lb.rows; ++r) {
+          for (int r = half; r < lb.rows; r += 2) {  // this warp's rows of the chunk (its partner takes the others)
             const int row = c * lb.rows + r;  // box row
             if (row >= lb.BH) break;
             float v[8 * MAX_CB];
@@ -398,10 +410,10 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             tmem_ld_wait();
             // the row goes to this thread's row buffer (16-byte stores, static register indices); the <= 2r+2 cells
             // of the thread's own window are then copied out at a dynamic shared-memory offset
-            float* rb = rowbuf + (warp * 32 + lane) * ROWBUF_PITCH;
+            float* rb = rowbuf + (warp * 16 + (lane & 15)) * ROWBUF_PITCH;
 #pragma unroll
             for (int cb = 0; cb < MAX_CB; ++cb)
-              if (cb < lb.ncb) {
+              if (cb < lb.ncb && lane < 16) {
                 *reinterpret_cast<float4*>(rb + 8 * cb) = make_float4(v[8 * cb], v[8 * cb + 1], v[8 * cb + 2], v[8 * cb + 3]);
                 *reinterpret_cast<float4*>(rb + 8 * cb + 4) = make_float4(v[8 * cb + 4], v[8 * cb + 5], v[8 * cb + 6], v[8 * cb + 7]);
               }
@@ -419,7 +431,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
       } else {
         // scalar path: the windows of this patch do not fit one box at this level (rough flow)
-        const int t = threadIdx.x, qi = t >> 1, sub = t & 1;
+        const int t = threadIdx.x, qi = t >> 2, sub = t & 3;
         const QInfo qi_info = qinfo[l * TQ + qi];
         const bool n_ok = (qi_info.flags & 2) != 0;
         const int qy = tyi * 8 + (qi >> 3), qx = txi * 8 + (qi & 7);
@@ -430,8 +442,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const float* f1q = p.f1 + (n_ok ? qq : 0) * p.D;
         const float* f2b = f2l + (long long)b * lh * lw * p.D;
 #pragma unroll 1
-        for (int i = 0; i < NCELL / 2; ++i) {
-          const int e = sub + 2 * i;
+        for (int i = 0; i < NCELL / 4; ++i) {
+          const int e = sub + 4 * i;
           const int ry = e / FP, rx = e - ry * FP;
           const int gy = qi_info.by + ry, gx = qi_info.bx + rx;
           float s = 0.0f;
@@ -450,14 +462,14 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
       }
       // ---- taps of level l: warp w takes its queries 16 w .. 16 w + 15 (the MMAs of level l + 1 run meanwhile) ----
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // every footprint of the patch at this level is complete
-      column_taps_level<R>(Fl + 16 * warp * NCELL, cx, cy, qvalid, q, l, p.out, C, lane);
+      asm volatile("bar.sync 1, 256;" ::: "memory");  // every footprint of the patch at this level is complete
+      column_taps_level<R>(Fl + 16 * quarter * NCELL, cx, cy, qvalid, q, l, p.out, C, lane, half);
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == MMA_WARP) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
   }
@@ -547,7 +559,7 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   p.inv_sqrt_d = 1.0f / (float)sqrt((double)D);
   const int FP = 2 * radius + 2;
   const size_t smem = 1024 + (size_t)2 * (D / 64) * A_BLOCK_BYTES + (size_t)RING_BYTES +
-                      (size_t)2 * TQ * FP * FP * sizeof(float) + (size_t)4 * 32 * ROWBUF_PITCH * sizeof(float) + 256 + 320 +
+                      (size_t)2 * TQ * FP * FP * sizeof(float) + (size_t)EPI_WARPS * 16 * ROWBUF_PITCH * sizeof(float) + 256 + 320 +
                       4 * sizeof(LevelBox) + 4 * TQ * sizeof(QInfo);
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8);

@@ -78,12 +78,21 @@ def test_lookup_and_altcorr_writes_stay_inside(cuda, lib, shape, r):
     f1 = torch.randn((b, h, w, d), device=cuda, generator=gen)
     f2 = torch.randn((b, h, w, d), device=cuda, generator=gen)
     alt = J.AltCorrBlock(4, r)
-    _, f2_levels = alt.build_pyramid(f1, f2)
+    _, f2_levels, f1_split, f2_split = alt.build_pyramid(f1, f2)
     buf, out = _carve(q * c, cuda)
     with torch.cuda.device(cuda):
         rc = lib.raftk_altcorr_lookup(f1.data_ptr(), _lib.ptr_array(f2_levels), 4, coords.data_ptr(), out.data_ptr(),
                                       b, h * w, h, w, d, r, stream)
         _lib.check("raftk_altcorr_lookup", rc)
+        torch.cuda.synchronize(cuda)
+    assert _intact(buf, q * c) and bool((out != SENTINEL).all())
+    # the tensor-core entry point (+-15 px per-pixel flow: box and scalar paths both occur)
+    buf, out = _carve(q * c, cuda)
+    with torch.cuda.device(cuda):
+        rc = lib.raftk_altcorr_lookup_tc(f1.data_ptr(), _lib.ptr_array(f2_levels), f1_split.data_ptr(),
+                                         _lib.ptr_array(f2_split), 4, coords.data_ptr(), out.data_ptr(), b, h * w, h, w, d, r,
+                                         stream)
+        _lib.check("raftk_altcorr_lookup_tc", rc)
         torch.cuda.synchronize(cuda)
     assert _intact(buf, q * c) and bool((out != SENTINEL).all())
 
