@@ -412,22 +412,21 @@ def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=5, with_mask_
     P_l = sum((h >> l) * (w >> l) for l in range(L))
     flops = 2.0 * batch * (h * w) ** 2 * d
     res = {"h": h, "w": w, "batch": batch, "queries": nq}
+    # the HBM-bound kernels first, the GEMMs last: a kernel timed right after seconds of back-to-back tensor-core work
+    # runs on a power-capped clock (MEASURED_PEAKS.json: 1282 MHz median under load against 1965 MHz)
+    gemm_jobs = []
     for storage, suffix, esize in (("fp32", "", 4), ("fp16", "_f16", 2)):
         # float16 slabs: CorrBlock(storage="fp16"), the models' default in the tf32 mode (values rounded once, 1e-3 bar)
         cb = J.CorrBlock(L, r, storage=storage)
-        pyr_bytes = 4 * 2 * nq * d + esize * nq * P_l
-        t = timed([lambda: cb.build_pyramid(f1, f2)] * 2, pyr_bytes)
-        issued = 3 * flops / (t[0] * 1e-3) / 1e12
-        res["corr_pyramid" + suffix] = hbm(t, pyr_bytes, {
-            "tflops_algorithmic": flops / (t[0] * 1e-3) / 1e12, "tflops_issued_bf16": issued,
-            "frac_of_tensor_peak": issued / bf16_tf if bf16_tf else None,
-            "includes": "bf16 split pre-pass + tcgen05 GEMM" + ("; algorithmic_bytes with 2-byte pyramid values" if esize == 2 else "")})
         pyr = cb.build_pyramid(f1, f2)
+        torch.cuda.synchronize(dev)
+        time.sleep(0.05)
         t = timed([(lambda c=c: cb.index_pyramid(pyr, c)) for c in coords], esize * nq * P_l)
         res["corr_lookup" + suffix] = hbm(t, nq * lookup_bytes_per_query(r, L),
                                           f16_accounting(nq, t[0], hbm_gbs, r, L) if esize == 2 else None)
         del pyr
         torch.cuda.empty_cache()
+        gemm_jobs.append((cb, suffix, esize))
     masks = [torch.randn((batch, h, w, 576), device=dev, generator=g) for _ in range(2)]
     t = timed([(lambda m=m: J.upsample_flow(flow, m)) for m in masks], 2 * nq * 2304)
     res["convex_upsample"] = hbm(t, nq * (2304 + 8 + 512))
@@ -457,7 +456,20 @@ def hot_kernels_at(torch, J, dev, flush, peaks, h, w, batch, iters=5, with_mask_
         ta = timed([lambda: ab.index_pyramid(apyr, c_s)] * 2, 4 * 2 * nq * d)
         aflops = 2.0 * nq * L * (2 * r + 2) ** 2 * d
         res["altcorr"] = {"pool_fmap2_ms": tp[0], "lookup_ms_per_iter": ta[0], "tflops": aflops / (ta[0] * 1e-3) / 1e12,
-                          "flops_per_iter": aflops}
+                          "flops_per_iter": aflops, "kernel": "raftk_altcorr_lookup_tc (tcgen05); pool_fmap2_ms includes the bf16 splits"}
+        ab_s = J.AltCorrBlock(L, r, kernel="simt")
+        spyr = ab_s.build_pyramid(f1, f2)
+        ts = timed([lambda: ab_s.index_pyramid(spyr, c_s)] * 2, 4 * 2 * nq * d)
+        res["altcorr"]["simt_lookup_ms_per_iter"] = ts[0]
+    for cb, suffix, esize in gemm_jobs:
+        pyr_bytes = 4 * 2 * nq * d + esize * nq * P_l
+        t = timed([lambda: cb.build_pyramid(f1, f2)] * 2, pyr_bytes)
+        issued = 3 * flops / (t[0] * 1e-3) / 1e12
+        res["corr_pyramid" + suffix] = hbm(t, pyr_bytes, {
+            "tflops_algorithmic": flops / (t[0] * 1e-3) / 1e12, "tflops_issued_bf16": issued,
+            "frac_of_tensor_peak": issued / bf16_tf if bf16_tf else None,
+            "includes": "bf16 split pre-pass + tcgen05 GEMM" + ("; algorithmic_bytes with 2-byte pyramid values" if esize == 2 else "")})
+        torch.cuda.empty_cache()
     torch.cuda.empty_cache()
     return res
 

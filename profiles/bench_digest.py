@@ -25,7 +25,8 @@ def show(e, indent="  "):
                 extra += "  own-bytes %.3f" % x["own_frac_of_hbm_peak"]
             print("%s%-22s %9.2f us  hbm %.3f%s" % (indent, k, x["mean_ms"] * 1e3, x["frac_of_hbm_peak"], extra))
         elif k == "altcorr":
-            print("%saltcorr: pool %.1f us, lookup %.1f us/iter, %.1f TFLOP/s" % (indent, x["pool_fmap2_ms"] * 1e3, x["lookup_ms_per_iter"] * 1e3, x["tflops"]))
+            print("%saltcorr: pool+split %.1f us, lookup %.1f us/iter (%.1f TFLOP/s useful); simt %.1f us/iter" % (
+                indent, x["pool_fmap2_ms"] * 1e3, x["lookup_ms_per_iter"] * 1e3, x["tflops"], x.get("simt_lookup_ms_per_iter", 0) * 1e3))
 
 
 ks = d.get("kernels_saturating", {})
