@@ -720,7 +720,10 @@ def run_b200(args):
     P_l = sum((H // 8 >> l) * (W // 8 >> l) for l in range(L))
     pyr_bytes = 4 * (2 * B * N * 256 + B * N * P_l)
 
-    traffic, traffic_src = ncu_traffic_per_launch("lookup_tiled") if B == 1 else (None, None)
+    # the batch-1 ncu capture holds the no-update variants <R, G, WARPS, MINB, PIPE, UPDATE = 0, HALF>
+    half = getattr(model.corr_block, "storage", "") == "fp16"
+    traffic, traffic_src = (ncu_traffic_per_launch("lookup_tiled_kernel<4, 2, 4, 4, 1, 0, %d>" % (1 if half else 0))
+                            if B == 1 else (None, None))
     pairs = world * B * args.steps
     line = {
         "metric": METRIC, "value": pairs / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
