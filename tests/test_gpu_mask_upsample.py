@@ -57,3 +57,31 @@ def test_equals_separate_kernels_and_out_buffer(cuda, lib):
     empty = J.mask_upsample(torch.zeros((0, 4, 4, 2), device=cuda), torch.zeros((0, 4, 4, k), device=cuda), pw, pb)
     assert empty.shape == (0, 32, 32, 2)
     assert lib.raftk_mask_upsample(feats.data_ptr(), pw.data_ptr(), pb.data_ptr(), flow.data_ptr(), buf.data_ptr(), b, h, w, 48, None) == -4
+
+
+@pytest.mark.parametrize("b,h,w", [(3, 55, 128), (1, 139, 137)])
+def test_more_tiles_than_sms(cuda, lib, b, h, w):
+    """More 128-pixel tiles than SMs (several waves of CTAs, no pass split): (3, 55, 128) = 165 tiles, (1, 139, 137) =
+    149 tiles with a ragged last one.  Checked against the float64 product of the TF32-truncated operands on the first
+    and last image rows (tight bar) and everywhere against the stand-alone upsampler on float32 logits (TF32 bar)."""
+    k = 256
+    gen = torch.Generator(device=cuda).manual_seed(b + h)
+    feats = torch.relu(torch.randn((b, h, w, k), device=cuda, generator=gen))
+    weight = torch.randn((576, k), device=cuda, generator=gen) * (2.0 / 16)
+    bias = torch.randn((576,), device=cuda, generator=gen)
+    flow = torch.randn((b, h, w, 2), device=cuda, generator=gen) * 4
+    assert (b * h * w + 127) // 128 >= torch.cuda.get_device_properties(cuda).multi_processor_count
+    pw, pb = J.pack_mask_predictor(weight, bias)
+    got = J.mask_upsample(flow, feats, pw, pb)
+    mask32 = (feats.reshape(-1, k).double() @ weight.double().T + bias).float().reshape(b, h, w, 576)
+    ref32 = J.upsample_flow(flow, mask32)
+    scale = max(1.0, float(ref32.abs().max()))
+    assert float((got - ref32).abs().max()) <= 2e-2 * scale
+    # tight check on the first and the last image rows of every pair (covers the first tiles and the ragged end)
+    f_np, w_np = feats.cpu().numpy(), weight.cpu().numpy()
+    mask_tf = (_tf32_trunc(f_np).reshape(-1, k).astype(np.float64) @ _tf32_trunc(w_np).astype(np.float64).T
+               + bias.cpu().numpy()).reshape(b, h, w, 576).astype(F32)
+    ref_tf = O.upsample_flow(flow.cpu().numpy(), mask_tf)
+    g = got.cpu().numpy()
+    for rows in (slice(0, 16), slice(8 * h - 16, 8 * h)):
+        assert np.abs(g[:, rows] - ref_tf[:, rows]).max() <= 2e-5 * scale
