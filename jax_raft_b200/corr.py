@@ -37,7 +37,11 @@ def _check_fmaps(fmap1, fmap2, num_levels, query_rows):
     if query_rows is not None:
         y0, y1 = query_rows
         assert 0 <= y0 <= y1 <= h, f"query_rows {query_rows} outside [0, {h}]"
-        presliced = fmap1.shape[-3] == y1 - y0 and fmap1.shape[-3] != h
+        rows = fmap1.shape[-3]
+        assert rows in (h, y1 - y0), (
+            f"fmap1 has {rows} rows: with query_rows={query_rows} it must be the full map ({h} rows, sliced here) "
+            f"or exactly the band ({y1 - y0} rows)")
+        presliced = rows == y1 - y0 and rows != h  # (0, h) on a full map: slicing is the identity either way
     if presliced:
         assert fmap1.shape[0] == fmap2.shape[0] and fmap1.shape[2:] == fmap2.shape[2:], \
             "Input feature maps should have the same shapes"

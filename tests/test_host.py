@@ -211,3 +211,34 @@ def test_weight_packing_for_the_fused_kernels():
             assert torch.equal(packed[:, l * kl:l * kl + ss], wc[:, l * ss:(l + 1) * ss, 0, 0])
             assert not packed[:, l * kl + ss:(l + 1) * kl].any()
     assert not J.CorrBlock(3, 4).fused_conv_supported and not J.CorrBlock(4, 2).fused_conv_supported
+
+
+def test_pyramid_layout_and_storage_options():
+    """The round-2 host options, without a GPU: tiled slab shapes, storage / layout / kernel argument checks, and the
+    models' defaults (float16 slabs in the tf32 mode, float32 slabs in the fp32 mode, row-major float32 for f1)."""
+    from jax_raft_b200.corr import TiledPyramid
+
+    # (Q, tiles_y, tiles_x, 4, 4): tiles_y = ceil(lh / 4), tiles_x = 2 * ceil(lw / 8)
+    assert TiledPyramid.level_shape(7, 55, 128, 0) == (7, 14, 32, 4, 4)
+    assert TiledPyramid.level_shape(7, 55, 128, 3) == (7, 2, 4, 4, 4)
+    assert TiledPyramid.level_shape(1, 46, 62, 1) == (1, 6, 8, 4, 4)   # 23 x 31
+    assert TiledPyramid.level_shape(1, 136, 240, 2) == (1, 9, 16, 4, 4)  # 34 x 60
+    with pytest.raises(AssertionError):
+        J.CorrBlock(4, 4, storage="bf16")
+    with pytest.raises(AssertionError):
+        J.CorrBlock(4, 4, layout="rowmajor", storage="fp16")
+    with pytest.raises(AssertionError):
+        J.AltCorrBlock(4, 4, kernel="wmma")
+    assert J.CorrBlock(4, 4).storage == "fp32" and J.CorrBlock(4, 4).layout == "tiled"
+    assert J.raft_large()[0].corr_block.storage == "fp16"
+    assert J.raft_large(precision="fp32")[0].corr_block.storage == "fp32"
+    f1 = J.raft_large(fused_lookup_conv=True)[0].corr_block
+    assert f1.layout == "rowmajor" and f1.storage == "fp32"
+    alt = J.AltCorrBlock(4, 4)
+    assert alt._tc_supported(256) and alt._tc_supported(128) and not alt._tc_supported(96) and not alt._tc_supported(512)
+    assert not J.AltCorrBlock(5, 4)._tc_supported(256) and not J.AltCorrBlock(4, 2)._tc_supported(256)
+    assert not J.AltCorrBlock(4, 4, kernel="simt")._tc_supported(256)
+    # unsupported factory keywords of the reference (model.py:636-670) are refused, corr_block= is accepted
+    with pytest.raises(TypeError):
+        J.raft_large(update_block=object())
+    assert J.raft_large(corr_block=alt)[0].corr_block is alt
