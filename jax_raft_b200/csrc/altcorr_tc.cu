@@ -80,6 +80,7 @@ struct Params {
   float* out;
   int B, nq, D, L;
   int rows_q, w_q;
+  int levels_per_cta;   // L: one CTA per patch; 1: one CTA per (patch, level), blockIdx.y = level (few patches: fill the SMs)
   float inv_sqrt_d;
 };
 
@@ -193,6 +194,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   rem /= tiles_x;
   const int tyi = (int)(rem % tiles_y);
   const int b = (int)(rem / tiles_y);
+  const int l_begin = (int)blockIdx.y * p.levels_per_cta, l_end = min(p.L, l_begin + p.levels_per_cta);
 
   if (warp == MMA_WARP && lane == 0) {
     mbar_init(a_full, 1);
@@ -300,7 +302,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const uint32_t tmem_base = *tmem_slot;
   // ring geometry: one stage holds the widest chunk of this patch's tensor-core levels
   int stage_bytes = 8 * 1024;
-  for (int l = 0; l < p.L; ++l)
+  for (int l = l_begin; l < l_end; ++l)
     if (lbox[l].tc) stage_bytes = max(stage_bytes, lbox[l].ncb * lbox[l].rows * 1024);
   const int nstages = min(MAX_STAGES, RING_BYTES / stage_bytes);
 
@@ -312,7 +314,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         tma_load_4d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * 64, txi * 8, tyi * 8, b);
       int stage = 0;
       uint32_t phase = 0;
-      for (int l = 0; l < p.L; ++l) {
+      for (int l = l_begin; l < l_end; ++l) {
         const LevelBox lb = lbox[l];
         if (!lb.tc) continue;
         const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
@@ -339,7 +341,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tc_fence_after();
       int stage = 0, g = 0;  // g: chunks issued so far (accumulator g & 1)
       uint32_t phase = 0;
-      for (int l = 0; l < p.L; ++l) {
+      for (int l = l_begin; l < l_end; ++l) {
         const LevelBox lb = lbox[l];
         if (!lb.tc) continue;
         const uint32_t idesc = make_idesc_bf16(TQ, lb.ncb * lb.rows * 8);
@@ -384,7 +386,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===================== epilogue warps: window extraction, then the taps, level by level =====================
     const int C = p.L * S * S;
     int g = 0;
-    for (int l = 0; l < p.L; ++l) {
+    for (int l = l_begin; l < l_end; ++l) {
       const LevelBox lb = lbox[l];
       float* Fl = F + (l & 1) * TQ * NCELL;  // level l + 1 fills the other buffer while stragglers still read this one
       float* Fq = Fl + m * NCELL;
@@ -564,9 +566,14 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8);
   if (nblk > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
+  // fewer than two waves of patches (a row band of a sharded image, a small image): one CTA per (patch, level), level 0
+  // first, so that the SMs fill and the last wave is short (17 x 240: 43 us against 60); otherwise one CTA per patch,
+  // which loads the A tile and sets up once for all levels
+  p.levels_per_cta = nblk <= 2LL * sm_count() ? 1 : num_levels;
+  const unsigned grid_y = (unsigned)((num_levels + p.levels_per_cta - 1) / p.levels_per_cta);
   auto kernel = radius == 4 ? altcorr_tc_kernel<4> : altcorr_tc_kernel<3>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  kernel<<<(unsigned)nblk, NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB[0], tmB[1], tmB[2], tmB[3], p);
+  kernel<<<dim3((unsigned)nblk, grid_y), NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB[0], tmB[1], tmB[2], tmB[3], p);
   return launch_status();
 }
