@@ -1,5 +1,6 @@
-"""raftk_corr_lookup_conv1x1 against raftk_corr_lookup + the library's fused 1x1 convolution (TF32), at
-the Sintel 1/8 shape: graphs of 8 launches over 8 coordinate sets, best of 5."""
+"""raftk_corr_lookup_conv1x1 (f1, row-major float32 pyramid) against the lookup + the library's fused 1x1 convolution
+(TF32) — with the row-major lookup of round 1 and with the tiled float16 lookup the models use since round 2 — at the
+Sintel 1/8 shape: graphs of 8 launches over 8 coordinate sets, best of 5."""
 import os
 import sys
 
@@ -48,6 +49,13 @@ for b in [int(x) for x in (sys.argv[1:] or ["1", "2", "4", "16"])]:
     bias = torch.randn((n,), device=dev, generator=gen)
     cb = J.CorrBlock(4, r)
     packed = cb.pack_conv_weight(weight)
+    from jax_raft_b200.corr import TiledPyramid  # noqa: E402
+
+    tiled16 = TiledPyramid.from_dense(pyr, storage="fp16")
+
+    def separate_tiled(c):
+        f = cb.index_pyramid(tiled16, c).permute(0, 3, 1, 2)
+        return torch.cudnn_convolution_relu(f, weight, bias, (1, 1), (0, 0), (1, 1), 1)
 
     def separate(c):
         f = cb.index_pyramid(pyr, c).permute(0, 3, 1, 2)
@@ -56,4 +64,6 @@ for b in [int(x) for x in (sys.argv[1:] or ["1", "2", "4", "16"])]:
     def fused(c):
         return cb.index_pyramid_conv(pyr, c, packed, bias)
 
-    print(f"B={b}: lookup + conv1x1 {timed(separate, coords):.1f} us, fused {timed(fused, coords):.1f} us per call")
+    print(f"B={b}: row-major lookup + conv1x1 {timed(separate, coords):.1f} us, tiled float16 lookup + conv1x1 "
+          f"{timed(separate_tiled, coords):.1f} us, fused (f1) {timed(fused, coords):.1f} us per call", flush=True)
+    del tiled16, pyr
