@@ -66,7 +66,7 @@ constexpr int ROWBUF_PITCH = 36;                // floats per lane of the row bu
 constexpr int MAX_STAGES = 8;
 constexpr int A_BLOCK_BYTES = TQ * 128;
 constexpr int ACC_COLS = MAX_CB * MAX_ROWS * 8;  // 192 accumulator columns per buffer
-constexpr int EPI_WARPS = 8;                    // two per TMEM lane quarter (warp % 4): even / odd box rows, 8 queries of taps each
+constexpr int EPI_WARPS = 8;                    // warps 0-3: window extraction (TMEM lane quarter = warp); warps 4-7: taps of quarter warp - 4
 constexpr int PRODUCER_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1;
 constexpr int NUM_THREADS = (EPI_WARPS + 2) * 32;
 constexpr int SMEM_LIMIT = 232448;
@@ -119,14 +119,14 @@ __global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict
 // origin floor(c_l) - r; (cx, cy, qvalid, q) are those of the query THIS lane owns (lanes 0-15).
 template <int R>
 __device__ __forceinline__ void column_taps_level(const float* Fw, float cx, float cy, bool qvalid, long long q, int l,
-                                                  float* out, int C, int lane, int half) {
+                                                  float* out, int C, int lane) {
   constexpr int S = 2 * R + 1, FP = 2 * R + 2, NCELL = FP * FP;
   const float sc = __int_as_float((127 - l) << 23);  // 2^-l, exact
 #pragma unroll 1
-  for (int base = 0; base < 8 * S; base += 32) {  // this warp's 8 of the quarter's 16 queries: k = 8 half .. 8 half + 7
+  for (int base = 0; base < 16 * S; base += 32) {
     const int T = base + lane;
-    const bool active = T < 8 * S;
-    const int k = 8 * half + (active ? T / S : 0), i = T - (k - 8 * half) * S;
+    const bool active = T < 16 * S;
+    const int k = active ? T / S : 0, i = T - k * S;
     const float ccx = __shfl_sync(0xffffffffu, cx, k), ccy = __shfl_sync(0xffffffffu, cy, k);
     const int ok = __shfl_sync(0xffffffffu, qvalid ? 1 : 0, k);
     const long long qq = __shfl_sync(0xffffffffu, q, k);
@@ -175,8 +175,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smem_a = smem;                                   // [2 KB][A_BLOCK_BYTES]: hi blocks, then mid blocks
   uint8_t* smem_b = smem_a + 2 * KB * A_BLOCK_BYTES;        // ring of RING_BYTES
   float* F = reinterpret_cast<float*>(smem_b + RING_BYTES);  // [2][TQ][NCELL]: footprints of levels l and l + 1
-  float* rowbuf = F + 2 * TQ * NCELL;                        // [EPI_WARPS][16 owner lanes][ROWBUF_PITCH]: one box row per thread
-  uint64_t* bars = reinterpret_cast<uint64_t*>(rowbuf + EPI_WARPS * 16 * ROWBUF_PITCH);
+  float* rowbuf = F + 2 * TQ * NCELL;                        // [4 warps][16 owner lanes][2 rows][ROWBUF_PITCH]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rowbuf + 4 * 16 * 2 * ROWBUF_PITCH);
   uint64_t* a_full = bars;                      // [1]
   uint64_t* b_full = bars + 1;                  // [MAX_STAGES]
   uint64_t* b_empty = b_full + MAX_STAGES;      // [MAX_STAGES]
@@ -204,7 +204,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], EPI_WARPS);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[i], 4);  // one arrival per extraction warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -335,96 +335,113 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
     }
   } else if (warp == MMA_WARP) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      mbar_wait(a_full, 0);
-      tc_fence_after();
-      int stage = 0, g = 0;  // g: chunks issued so far (accumulator g & 1)
-      uint32_t phase = 0;
-      for (int l = l_begin; l < l_end; ++l) {
-        const LevelBox lb = lbox[l];
-        if (!lb.tc) continue;
-        const uint32_t idesc = make_idesc_bf16(TQ, lb.ncb * lb.rows * 8);
-        for (int c = 0; c < lb.nchunks; ++c, ++g) {
-          const int buf = g & 1;
-          mbar_wait(&acc_empty[buf], ((g >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
+    // ===================== MMA issuer: the whole warp walks the loops, one elected lane issues =====================
+    mbar_wait(a_full, 0);
+    tc_fence_after();
+    const uint64_t a_desc0 = umma_desc(smem_u32(smem_a)), b_desc0 = umma_desc(smem_u32(smem_b));
+    int stage = 0, g = 0;  // g: chunks issued so far (accumulator g & 1)
+    uint32_t phase = 0;
+    for (int l = l_begin; l < l_end; ++l) {
+      const LevelBox lb = lbox[l];
+      if (!lb.tc) continue;
+      const uint32_t idesc = make_idesc_bf16(TQ, lb.ncb * lb.rows * 8);
+      for (int c = 0; c < lb.nchunks; ++c, ++g) {
+        const int buf = g & 1;
+        mbar_wait(&acc_empty[buf], ((g >> 1) & 1) ^ 1);  // the extraction has drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)buf * ACC_COLS;
+        for (int kb = 0; kb < KB; ++kb) {
+          // descriptors differ from their base only in the address field (bytes >> 4, no carry out of it below 256 KB)
+          const uint64_t a_hi = a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4));
+          const uint64_t a_mid = a_desc0 + (uint64_t)((KB + kb) * (A_BLOCK_BYTES >> 4));
+          // stage holding B_hi[kb]: hi*hi and mid*hi
+          mbar_wait(&b_full[stage], phase);
           tc_fence_after();
-          const uint32_t tmem_d = tmem_base + (uint32_t)buf * ACC_COLS;
-          for (int kb = 0; kb < KB; ++kb) {
-            const uint32_t a_hi = smem_u32(smem_a + kb * A_BLOCK_BYTES);
-            const uint32_t a_mid = smem_u32(smem_a + (KB + kb) * A_BLOCK_BYTES);
-            // stage holding B_hi[kb]: hi*hi and mid*hi
-            mbar_wait(&b_full[stage], phase);
-            tc_fence_after();
-            uint32_t bs = smem_u32(smem_b + stage * stage_bytes);
-#pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_hi + 32 * k4), umma_desc(bs + 32 * k4), idesc, (kb | k4) != 0);
-#pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_mid + 32 * k4), umma_desc(bs + 32 * k4), idesc, 1);
+          uint64_t bs = b_desc0 + (uint64_t)(stage * (stage_bytes >> 4));
+          if (elect_one()) {
+            tc_mma_f16_x4(tmem_d, a_hi, bs, idesc, kb != 0);
+            tc_mma_f16_x4(tmem_d, a_mid, bs, idesc, 1);
             tc_commit(&b_empty[stage]);
-            if (++stage == nstages) {
-              stage = 0;
-              phase ^= 1;
-            }
-            // stage holding B_mid[kb]: hi*mid
-            mbar_wait(&b_full[stage], phase);
-            tc_fence_after();
-            bs = smem_u32(smem_b + stage * stage_bytes);
-#pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4) tc_mma_f16(tmem_d, umma_desc(a_hi + 32 * k4), umma_desc(bs + 32 * k4), idesc, 1);
-            tc_commit(&b_empty[stage]);
-            if (++stage == nstages) {
-              stage = 0;
-              phase ^= 1;
-            }
           }
-          tc_commit(&acc_full[buf]);
+          __syncwarp();
+          if (++stage == nstages) {
+            stage = 0;
+            phase ^= 1;
+          }
+          // stage holding B_mid[kb]: hi*mid
+          mbar_wait(&b_full[stage], phase);
+          tc_fence_after();
+          bs = b_desc0 + (uint64_t)(stage * (stage_bytes >> 4));
+          if (elect_one()) {
+            tc_mma_f16_x4(tmem_d, a_hi, bs, idesc, 1);
+            tc_commit(&b_empty[stage]);
+          }
+          __syncwarp();
+          if (++stage == nstages) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
+        if (elect_one()) tc_commit(&acc_full[buf]);
+        __syncwarp();
       }
     }
-  } else {
-    // ===================== epilogue warps: window extraction, then the taps, level by level =====================
-    const int C = p.L * S * S;
+  } else if (half == 0) {
+    // ===================== extraction warps 0-3: accumulators -> footprints, level by level =====================
+    // F is double-buffered per level and handed to the tap warps through named barriers: 2 + buf "footprints of a
+    // level complete" (extraction arrives, taps wait), 4 + buf "buffer free again" (taps arrive, extraction waits).
     int g = 0;
     for (int l = l_begin; l < l_end; ++l) {
       const LevelBox lb = lbox[l];
-      float* Fl = F + (l & 1) * TQ * NCELL;  // level l + 1 fills the other buffer while stragglers still read this one
+      const int fb = (l - l_begin) & 1;
+      float* Fl = F + fb * TQ * NCELL;
       float* Fq = Fl + m * NCELL;
       const bool haswin = (winmask >> l) & 1u;
-      if (owner && half == 0 && qvalid && !haswin)
+      if (l - l_begin >= 2) asm volatile("bar.sync %0, 256;" ::"r"(4 + fb) : "memory");  // the taps of level l - 2 are done with it
+      if (owner && qvalid && !haswin)
         for (int e = 0; e < NCELL; ++e) Fq[e] = 0.0f;
       if (lb.tc) {
         const int ox = (l == 0 ? bx[0] : l == 1 ? bx[1] : l == 2 ? bx[2] : bx[3]) - lb.X0;  // window origin inside the box
         const int oy = (l == 0 ? by[0] : l == 1 ? by[1] : l == 2 ? by[2] : by[3]) - lb.Y0;
+        float* rb = rowbuf + (warp * 16 + (lane & 15)) * 2 * ROWBUF_PITCH;  // two box rows per thread
         for (int c = 0; c < lb.nchunks; ++c, ++g) {
           const int buf = g & 1;
           mbar_wait(&acc_full[buf], (g >> 1) & 1);
           tc_fence_after();
           const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * ACC_COLS;
 #pragma unroll 1
-          for (int r = half; r < lb.rows; r += 2) {  // this warp's rows of the chunk (its partner takes the others)
-            const int row = c * lb.rows + r;  // box row
+          for (int r = 0; r < lb.rows; r += 2) {  // two box rows per TMEM round trip
+            const int row = c * lb.rows + r;
             if (row >= lb.BH) break;
-            float v[8 * MAX_CB];
+            const bool two = r + 1 < lb.rows && row + 1 < lb.BH;
+            float v[2][8 * MAX_CB];
 #pragma unroll
             for (int cb = 0; cb < MAX_CB; ++cb)
-              if (cb < lb.ncb) tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + r * 8), v + 8 * cb);
-            tmem_ld_wait();
-            // the row goes to this thread's row buffer (16-byte stores, static register indices); the <= 2r+2 cells
-            // of the thread's own window are then copied out at a dynamic shared-memory offset
-            float* rb = rowbuf + (warp * 16 + (lane & 15)) * ROWBUF_PITCH;
-#pragma unroll
-            for (int cb = 0; cb < MAX_CB; ++cb)
-              if (cb < lb.ncb && lane < 16) {
-                *reinterpret_cast<float4*>(rb + 8 * cb) = make_float4(v[8 * cb], v[8 * cb + 1], v[8 * cb + 2], v[8 * cb + 3]);
-                *reinterpret_cast<float4*>(rb + 8 * cb + 4) = make_float4(v[8 * cb + 4], v[8 * cb + 5], v[8 * cb + 6], v[8 * cb + 7]);
+              if (cb < lb.ncb) {
+                tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + r * 8), v[0] + 8 * cb);
+                if (two) tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + (r + 1) * 8), v[1] + 8 * cb);
               }
-            const int wr = row - oy;
-            if (haswin && (unsigned)wr < (unsigned)FP) {
-              float* Fr = Fq + wr * FP;
-              const float* src = rb + ox;
+            tmem_ld_wait();
+            // the rows go to this thread's row buffer (16-byte stores, static register indices); the <= 2r+2 cells
+            // of the thread's own window are then copied out at a dynamic shared-memory offset
 #pragma unroll
-              for (int wc = 0; wc < FP; ++wc) Fr[wc] = src[wc];
+            for (int rr = 0; rr < 2; ++rr)
+#pragma unroll
+              for (int cb = 0; cb < MAX_CB; ++cb)
+                if (cb < lb.ncb && lane < 16 && (rr == 0 || two)) {
+                  float* d = rb + rr * ROWBUF_PITCH + 8 * cb;
+                  *reinterpret_cast<float4*>(d) = make_float4(v[rr][8 * cb], v[rr][8 * cb + 1], v[rr][8 * cb + 2], v[rr][8 * cb + 3]);
+                  *reinterpret_cast<float4*>(d + 4) = make_float4(v[rr][8 * cb + 4], v[rr][8 * cb + 5], v[rr][8 * cb + 6], v[rr][8 * cb + 7]);
+                }
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+              const int wr = row + rr - oy;
+              if (haswin && (rr == 0 || two) && (unsigned)wr < (unsigned)FP) {
+                float* Fr = Fq + wr * FP;
+                const float* src = rb + rr * ROWBUF_PITCH + ox;
+#pragma unroll
+                for (int wc = 0; wc < FP; ++wc) Fr[wc] = src[wc];
+              }
             }
           }
           tc_fence_before();
@@ -433,7 +450,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
       } else {
         // scalar path: the windows of this patch do not fit one box at this level (rough flow)
-        const int t = threadIdx.x, qi = t >> 2, sub = t & 3;
+        const int t = threadIdx.x, qi = t >> 1, sub = t & 1;
         const QInfo qi_info = qinfo[l * TQ + qi];
         const bool n_ok = (qi_info.flags & 2) != 0;
         const int qy = tyi * 8 + (qi >> 3), qx = txi * 8 + (qi & 7);
@@ -444,8 +461,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const float* f1q = p.f1 + (n_ok ? qq : 0) * p.D;
         const float* f2b = f2l + (long long)b * lh * lw * p.D;
 #pragma unroll 1
-        for (int i = 0; i < NCELL / 4; ++i) {
-          const int e = sub + 4 * i;
+        for (int i = 0; i < NCELL / 2; ++i) {
+          const int e = sub + 2 * i;
           const int ry = e / FP, rx = e - ry * FP;
           const int gy = qi_info.by + ry, gx = qi_info.bx + rx;
           float s = 0.0f;
@@ -463,9 +480,18 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           Fl[qi * NCELL + e] = s * p.inv_sqrt_d;
         }
       }
-      // ---- taps of level l: warp w takes its queries 16 w .. 16 w + 15 (the MMAs of level l + 1 run meanwhile) ----
-      asm volatile("bar.sync 1, 256;" ::: "memory");  // every footprint of the patch at this level is complete
-      column_taps_level<R>(Fl + 16 * quarter * NCELL, cx, cy, qvalid, q, l, p.out, C, lane, half);
+      __threadfence_block();
+      asm volatile("bar.arrive %0, 256;" ::"r"(2 + fb) : "memory");  // every footprint of the patch at this level is complete
+    }
+  } else {
+    // ===================== tap warps 4-7: warp 4 + k evaluates the 16 queries of lane quarter k =====================
+    // (under the extraction of the next level and the MMAs of the one after)
+    const int C = p.L * S * S;
+    for (int l = l_begin; l < l_end; ++l) {
+      const int fb = (l - l_begin) & 1;
+      asm volatile("bar.sync %0, 256;" ::"r"(2 + fb) : "memory");
+      column_taps_level<R>(F + fb * TQ * NCELL + 16 * quarter * NCELL, cx, cy, qvalid, q, l, p.out, C, lane);
+      if (l + 2 < l_end) asm volatile("bar.arrive %0, 256;" ::"r"(4 + fb) : "memory");
     }
   }
 
@@ -561,7 +587,7 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   p.inv_sqrt_d = 1.0f / (float)sqrt((double)D);
   const int FP = 2 * radius + 2;
   const size_t smem = 1024 + (size_t)2 * (D / 64) * A_BLOCK_BYTES + (size_t)RING_BYTES +
-                      (size_t)2 * TQ * FP * FP * sizeof(float) + (size_t)EPI_WARPS * 16 * ROWBUF_PITCH * sizeof(float) + 256 + 320 +
+                      (size_t)2 * TQ * FP * FP * sizeof(float) + (size_t)4 * 16 * 2 * ROWBUF_PITCH * sizeof(float) + 256 + 320 +
                       4 * sizeof(LevelBox) + 4 * TQ * sizeof(QInfo);
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8);

@@ -71,6 +71,45 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uin
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// One lane of a converged warp.  Issuing tcgen05 instructions under `if (elect_one())` inside warp-uniform control flow
+// lets the compiler keep descriptors and addresses in uniform registers; under `if (lane == 0)` it treats them as
+// divergent and wraps every MMA in a vote-and-broadcast loop (~13 extra instructions per MMA).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// Four kind::f16 MMAs over one 64-element K block (k = 0, 16, 32, 48: +32 B = +2 in the descriptors' address field)
+// issued from ONE asm statement: one predicate set-up and two 64-bit adds per MMA instead of a descriptor rebuild —
+// the issuing thread's instruction count matters when an MMA is only ~60 cycles long (M = 64, N <= 192).
+// acc_first: whether the first of the four accumulates (the other three always do).
+__device__ __forceinline__ void tc_mma_f16_x4(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t acc_first) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      ".reg .b64 a1, b1, a2, b2, a3, b3;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.b32 q, 0, 0;\n\t"
+      "add.s64 a1, %1, 2;\n\t"
+      "add.s64 b1, %2, 2;\n\t"
+      "add.s64 a2, %1, 4;\n\t"
+      "add.s64 b2, %2, 4;\n\t"
+      "add.s64 a3, %1, 6;\n\t"
+      "add.s64 b3, %2, 6;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %3, q;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, q;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc_first)
+      : "memory");
+}
 // kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major
 __device__ __forceinline__ uint32_t make_idesc_bf16(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
