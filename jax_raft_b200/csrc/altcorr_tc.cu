@@ -307,32 +307,36 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int nstages = min(MAX_STAGES, RING_BYTES / stage_bytes);
 
   if (warp == PRODUCER_WARP) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer: the whole warp walks the loops, one elected lane issues =====================
+    if (elect_one()) {
       mbar_expect_tx(a_full, (uint32_t)(2 * KB * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
       for (int j = 0; j < 2 * KB; ++j)  // [hi | mid] is contiguous in K: block j starts at channel 64 j
         tma_load_4d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * 64, txi * 8, tyi * 8, b);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int l = l_begin; l < l_end; ++l) {
-        const LevelBox lb = lbox[l];
-        if (!lb.tc) continue;
-        const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
-        const int cb_bytes = lb.rows * 1024;
-        for (int c = 0; c < lb.nchunks; ++c)
-          for (int kb = 0; kb < KB; ++kb)
-            for (int part = 0; part < 2; ++part) {
-              mbar_wait(&b_empty[stage], phase ^ 1);
+    }
+    __syncwarp();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int l = l_begin; l < l_end; ++l) {
+      const LevelBox lb = lbox[l];
+      if (!lb.tc) continue;
+      const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
+      const int cb_bytes = lb.rows * 1024;
+      for (int c = 0; c < lb.nchunks; ++c)
+        for (int kb = 0; kb < KB; ++kb)
+          for (int part = 0; part < 2; ++part) {
+            mbar_wait(&b_empty[stage], phase ^ 1);
+            if (elect_one()) {
               mbar_expect_tx(&b_full[stage], (uint32_t)(lb.ncb * cb_bytes));
               for (int cb = 0; cb < lb.ncb; ++cb)
                 tma_load_4d(tmB, &b_full[stage], smem_b + stage * stage_bytes + cb * cb_bytes, part * p.D + kb * 64,
                             lb.X0 + 8 * cb, lb.Y0 + lb.rows * c, b);
-              if (++stage == nstages) {
-                stage = 0;
-                phase ^= 1;
-              }
             }
-      }
+            __syncwarp();
+            if (++stage == nstages) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
     }
   } else if (warp == MMA_WARP) {
     // ===================== MMA issuer: the whole warp walks the loops, one elected lane issues =====================

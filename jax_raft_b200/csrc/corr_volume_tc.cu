@@ -221,6 +221,68 @@ __device__ __forceinline__ void tc_mma_bf16_pair(uint32_t tmem_d, uint64_t desc_
       : "memory");
 }
 
+// One lane of a converged warp.  tcgen05 / TMA instructions issued under `if (elect_one())` inside warp-uniform
+// control flow keep their descriptors and addresses in uniform registers; under `if (lane == 0)` the compiler treats
+// them as divergent and wraps every instruction in a vote-and-broadcast loop (~13 extra instructions per MMA).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// Four kind::f16 MMAs over one 64-element K block (k = 0, 16, 32, 48: +32 B = +2 in the descriptors' address field)
+// from ONE asm statement; acc_first: whether the first of the four accumulates (the other three always do).
+template <int CG>
+__device__ __forceinline__ void tc_mma_bf16_x4(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                               uint32_t acc_first) {
+  if (CG == 1) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        ".reg .b64 a1, b1, a2, b2, a3, b3;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.eq.b32 q, 0, 0;\n\t"
+        "add.s64 a1, %1, 2;\n\t"
+        "add.s64 b1, %2, 2;\n\t"
+        "add.s64 a2, %1, 4;\n\t"
+        "add.s64 b2, %2, 4;\n\t"
+        "add.s64 a3, %1, 6;\n\t"
+        "add.s64 b3, %2, 6;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %3, q;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, q;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc_first)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        ".reg .b64 a1, b1, a2, b2, a3, b3;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.eq.b32 q, 0, 0;\n\t"
+        "add.s64 a1, %1, 2;\n\t"
+        "add.s64 b1, %2, 2;\n\t"
+        "add.s64 a2, %1, 4;\n\t"
+        "add.s64 b2, %2, 4;\n\t"
+        "add.s64 a3, %1, 6;\n\t"
+        "add.s64 b3, %2, 6;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], a1, b1, %3, q;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], a2, b2, %3, q;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], a3, b3, %3, q;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc_first)
+        : "memory");
+  }
+}
+
 // K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart.
 // start address >> 4 | LBO (unused for swizzled K-major, canonical 1) | SBO = 1024 B | version 1
 // (Blackwell) | layout type 2 (SWIZZLE_128B).  Advancing K by 16 bf16 = +32 B on the start address.
@@ -511,8 +573,8 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const uint32_t a_full_lead = CG == 2 ? mapa_shared(smem_u32(a_full), 0) : 0u;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer: the whole warp walks the loops, one elected lane issues =====================
+    {
       int stage = 0;
       uint32_t phase = 0, a_phase = 0;
       long long cur_bm = -1;
@@ -525,13 +587,16 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           cur_bm = bm;
           const int m0 = (int)(bm - (long long)b * p.m_tiles) * (BM * CG) + (int)rank * BM;
           mbar_wait(a_empty, a_phase ^ 1);  // MMAs of the previous A tile have drained
-          if (leader) mbar_expect_tx(a_full, CG * a_blocks * A_BLOCK_BYTES);
-          for (int j = 0; j < a_blocks; ++j) {
-            if (CG == 1)
-              tma_load_3d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * KBLK, m0, b);
-            else
-              tma_load_3d_pair(&tmA, a_full_lead, smem_a + j * A_BLOCK_BYTES, j * KBLK, m0, b);
+          if (elect_one()) {
+            if (leader) mbar_expect_tx(a_full, CG * a_blocks * A_BLOCK_BYTES);
+            for (int j = 0; j < a_blocks; ++j) {
+              if (CG == 1)
+                tma_load_3d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * KBLK, m0, b);
+              else
+                tma_load_3d_pair(&tmA, a_full_lead, smem_a + j * A_BLOCK_BYTES, j * KBLK, m0, b);
+            }
           }
+          __syncwarp();
           a_phase ^= 1;
         }
         const int x0 = (nt % p.px_tiles) * PW, y0 = (nt / p.px_tiles) * PH;
@@ -540,12 +605,15 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           const int kb = j >> 1;
           const int kcoord = (j & 1) ? p.D + kb * KBLK : kb * KBLK;
           mbar_wait(&b_empty[stage], phase ^ 1);
-          if (leader) mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);  // both CTAs' halves
-          if (CG == 1)
-            tma_load_4d(&tmB, &b_full[stage], smem_b + stage * kBStage, kcoord, x0, y0, b);
-          else  // this CTA's 4 of the patch's 8 rows
-            tma_load_4d_pair(&tmB, mapa_shared(smem_u32(&b_full[stage]), 0), smem_b + stage * kBStage, kcoord, x0,
-                             y0 + (int)rank * (PH / 2), b);
+          if (elect_one()) {
+            if (leader) mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);  // both CTAs' halves
+            if (CG == 1)
+              tma_load_4d(&tmB, &b_full[stage], smem_b + stage * kBStage, kcoord, x0, y0, b);
+            else  // this CTA's 4 of the patch's 8 rows
+              tma_load_4d_pair(&tmB, mapa_shared(smem_u32(&b_full[stage]), 0), smem_b + stage * kBStage, kcoord, x0,
+                               y0 + (int)rank * (PH / 2), b);
+          }
+          __syncwarp();
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1;
@@ -554,15 +622,14 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (leader CTA only) =====================
-    if (lane == 0 && leader) {
+    // ===================== MMA issuer (leader CTA only): the whole warp walks the loops, one elected lane issues ====
+    if (leader) {
       constexpr uint32_t kIdesc = make_idesc(BM * CG);
       auto commit = [](uint64_t* bar) {
         if (CG == 1) tc_commit(bar); else tc_commit_pair(bar);
       };
-      auto mma = [](uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
-        if (CG == 1) tc_mma_bf16(d, da, db, idesc, acc); else tc_mma_bf16_pair(d, da, db, idesc, acc);
-      };
+      // descriptors differ from their base only in the address field (bytes >> 4; no carry out of it below 256 KB)
+      const uint64_t a_desc0 = umma_desc(smem_u32(smem_a)), b_desc0 = umma_desc(smem_u32(smem_b));
       int stage = 0, buf = 0;
       uint32_t phase = 0, a_phase = 0, acc_phase = 0;
       long long cur_bm = -1;
@@ -571,7 +638,10 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       for (long long t = t_begin; t < t_end; ++t) {
         const long long bm = (long long)pair_b * p.m_tiles + t / p.n_tiles;
         if (bm != cur_bm) {
-          if (have_a) commit(a_empty);  // everything issued so far has finished reading A
+          if (have_a) {
+            if (elect_one()) commit(a_empty);  // everything issued so far has finished reading A
+            __syncwarp();
+          }
           cur_bm = bm;
           have_a = true;
           mbar_wait(a_full, a_phase);
@@ -582,19 +652,18 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)buf * BN;
         for (int kb = 0; kb < kblocks; ++kb) {
-          const uint32_t a_hi = smem_u32(smem_a + kb * A_BLOCK_BYTES);
-          const uint32_t a_mid = smem_u32(smem_a + (kblocks + kb) * A_BLOCK_BYTES);
+          const uint64_t a_hi = a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4));
+          const uint64_t a_mid = a_desc0 + (uint64_t)((kblocks + kb) * (A_BLOCK_BYTES >> 4));
           // stage holding B_hi[kb]: hi*hi and mid*hi
           mbar_wait(&b_full[stage], phase);
           tc_fence_after();
-          uint32_t bs = smem_u32(smem_b + stage * kBStage);
-#pragma unroll
-          for (int k4 = 0; k4 < KBLK / 16; ++k4)
-            mma(tmem_d, umma_desc(a_hi + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, (kb | k4) != 0);
-#pragma unroll
-          for (int k4 = 0; k4 < KBLK / 16; ++k4)
-            mma(tmem_d, umma_desc(a_mid + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, 1);
-          commit(&b_empty[stage]);
+          uint64_t bs = b_desc0 + (uint64_t)(stage * (kBStage >> 4));
+          if (elect_one()) {
+            tc_mma_bf16_x4<CG>(tmem_d, a_hi, bs, kIdesc, kb != 0);
+            tc_mma_bf16_x4<CG>(tmem_d, a_mid, bs, kIdesc, 1);
+            commit(&b_empty[stage]);
+          }
+          __syncwarp();
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1;
@@ -602,17 +671,19 @@ corr_pyramid_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           // stage holding B_mid[kb]: hi*mid
           mbar_wait(&b_full[stage], phase);
           tc_fence_after();
-          bs = smem_u32(smem_b + stage * kBStage);
-#pragma unroll
-          for (int k4 = 0; k4 < KBLK / 16; ++k4)
-            mma(tmem_d, umma_desc(a_hi + k4 * 32), umma_desc(bs + k4 * 32), kIdesc, 1);
-          commit(&b_empty[stage]);
+          bs = b_desc0 + (uint64_t)(stage * (kBStage >> 4));
+          if (elect_one()) {
+            tc_mma_bf16_x4<CG>(tmem_d, a_hi, bs, kIdesc, 1);
+            commit(&b_empty[stage]);
+          }
+          __syncwarp();
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        commit(&acc_full[buf]);
+        if (elect_one()) commit(&acc_full[buf]);
+        __syncwarp();
         if (++buf == 2) {
           buf = 0;
           acc_phase ^= 1;

@@ -97,59 +97,62 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == EPI_WARPS) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      // the first weight slabs go out between the A blocks, so that the first MMA waits for 16 + 18 KB, not 128 + 18
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int g = pass0; g < pass0 + npass; ++g)
-        for (int kb = 0; kb < KB; ++kb) {
-          auto load_a = [&](int k) {
-            mbar_expect_tx(&a_full[k], (uint32_t)A_BLOCK_BYTES);  // rows past Q are zero-filled and still counted
-            tma_load_2d(&tmA, &a_full[k], smem_a + k * A_BLOCK_BYTES, k * 32, (int)q0);
-          };
-          const bool first_ring = g == pass0 && kb < STAGES;  // no ring slot to wait for yet
+    // ===================== TMA producer: the whole warp walks the loops, one elected lane issues =====================
+    // (uniform control flow keeps tensor-map pointers, barriers and coordinates in uniform registers: tc_ptx.cuh)
+    // the first weight slabs go out between the A blocks, so that the first MMA waits for 16 + 18 KB, not 128 + 18
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int g = pass0; g < pass0 + npass; ++g)
+      for (int kb = 0; kb < KB; ++kb) {
+        auto load_a = [&](int k) {
+          mbar_expect_tx(&a_full[k], (uint32_t)A_BLOCK_BYTES);  // rows past Q are zero-filled and still counted
+          tma_load_2d(&tmA, &a_full[k], smem_a + k * A_BLOCK_BYTES, k * 32, (int)q0);
+        };
+        const bool first_ring = g == pass0 && kb < STAGES;  // no ring slot to wait for yet
+        mbar_wait(&b_empty[stage], phase ^ 1);
+        if (elect_one()) {
           if (first_ring) load_a(kb);
-          mbar_wait(&b_empty[stage], phase ^ 1);
           mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);
           tma_load_2d(&tmW, &b_full[stage], smem_b + stage * B_STAGE_BYTES, kb * 32, g * NP);
           if (first_ring && (kb == STAGES - 1 || kb == KB - 1))  // the rest of the A tile, before the ring blocks
             for (int k = kb + 1; k < KB; ++k) load_a(k);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
         }
-    }
-  } else if (warp == EPI_WARPS + 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      // kind::tf32, D = f32, A = B = tf32, K-major, N = 144, M = 128
-      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NP >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int gi = 0; gi < npass; ++gi) {
-        const int buf = gi & 1;
-        mbar_wait(&acc_empty[buf], ((gi >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
-        tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)buf * 256;
-        for (int kb = 0; kb < KB; ++kb) {
-          if (gi == 0) mbar_wait(&a_full[kb], 0);
-          mbar_wait(&b_full[stage], phase);
-          tc_fence_after();
-          const uint32_t as = smem_u32(smem_a + kb * A_BLOCK_BYTES);
-          const uint32_t bs = smem_u32(smem_b + stage * B_STAGE_BYTES);
-#pragma unroll
-          for (int k8 = 0; k8 < 4; ++k8)
-            tc_mma_tf32(tmem_d, umma_desc(as + 32 * k8), umma_desc(bs + 32 * k8), idesc, (kb | k8) != 0);
-          tc_commit(&b_empty[stage]);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
         }
-        tc_commit(&acc_full[buf]);
       }
+  } else if (warp == EPI_WARPS + 1) {
+    // ===================== MMA issuer: the whole warp walks the loops, one elected lane issues =====================
+    // kind::tf32, D = f32, A = B = tf32, K-major, N = 144, M = 128
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(NP >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+    // descriptors differ from their base only in the address field (bytes >> 4; no carry out of it below 256 KB)
+    const uint64_t a_desc0 = umma_desc(smem_u32(smem_a)), b_desc0 = umma_desc(smem_u32(smem_b));
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int gi = 0; gi < npass; ++gi) {
+      const int buf = gi & 1;
+      mbar_wait(&acc_empty[buf], ((gi >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)buf * 256;
+      for (int kb = 0; kb < KB; ++kb) {
+        if (gi == 0) mbar_wait(&a_full[kb], 0);
+        mbar_wait(&b_full[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          tc_mma_tf32_x4(tmem_d, a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4)), b_desc0 + (uint64_t)(stage * (B_STAGE_BYTES >> 4)),
+                         idesc, kb != 0);
+          tc_commit(&b_empty[stage]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (elect_one()) tc_commit(&acc_full[buf]);
+      __syncwarp();
     }
   } else {
     // ===================== epilogue: thread = (pixel, half of the pass's 16 sub-pixels) =====================

@@ -110,6 +110,28 @@ __device__ __forceinline__ void tc_mma_f16_x4(uint32_t tmem_d, uint64_t desc_a, 
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc_first)
       : "memory");
 }
+// The same for kind::tf32 (four K = 8 steps of a 32-float K block: +32 B each)
+__device__ __forceinline__ void tc_mma_tf32_x4(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t acc_first) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      ".reg .b64 a1, b1, a2, b2, a3, b3;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.b32 q, 0, 0;\n\t"
+      "add.s64 a1, %1, 2;\n\t"
+      "add.s64 b1, %2, 2;\n\t"
+      "add.s64 a2, %1, 4;\n\t"
+      "add.s64 b2, %2, 4;\n\t"
+      "add.s64 a3, %1, 6;\n\t"
+      "add.s64 b3, %2, 6;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], a1, b1, %3, q;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], a2, b2, %3, q;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], a3, b3, %3, q;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc_first)
+      : "memory");
+}
 // kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major
 __device__ __forceinline__ uint32_t make_idesc_bf16(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
