@@ -18,13 +18,14 @@
 //              (chunk, k-block, hi | mid) slab per stage of a ring of as many stages as fit 80 KB (4 ... 8).
 //   D          float32 in TMEM, two accumulators of 192 columns: the epilogue of chunk c runs under the MMAs of
 //              chunk c + 1, across level boundaries too.  M = 64: accumulator row m is TMEM lane (m % 16) + 32 * (m / 16).
-//   epilogue   eight warps, two per TMEM lane quarter (its 16 queries); the pair splits the rows of a chunk.  Per box
-//              row: tcgen05.ld.x8 per column block (static register indices), the row goes to the thread's row buffer
-//              in shared memory, and the <= 2r+2 cells of the thread's own window are copied from there into its
+//   epilogue   extraction warps 0-3 (TMEM lane quarter = warp: its 16 queries).  Two box rows per TMEM round trip:
+//              tcgen05.ld.x8 per column block (static register indices), the rows go to the thread's row buffer in
+//              shared memory, and the <= 2r+2 cells of the thread's own window are copied from there into its
 //              footprint F[query][(2r+2)^2] — the window offset is a shared-memory address, never a register index.
-//              Footprints are double-buffered per level: when the last chunk of level l is in, the warps evaluate its
-//              taps as column tasks (the schedule and the float32 arithmetic of corr_lookup_tiled.cu: window indexing
-//              and tap values are those of the volume lookup) while the MMAs of level l + 1 fill the accumulators.
+//   taps       warps 4-7.  Footprints are double-buffered per level and handed over through named barriers: when the
+//              last chunk of level l is in, warp 4 + k evaluates the taps of quarter k as column tasks (the schedule
+//              and the float32 arithmetic of corr_lookup_tiled.cu: window indexing and tap values are those of the
+//              volume lookup) while the extraction warps drain level l + 1 and the MMAs fill the accumulators.
 //
 // A cell's value depends only on the query's row of A, the cell's row of B and the fixed K order, not on the box or
 // the chunk it was computed in, so row bands reproduce the full result bit for bit.  Queries that read nothing (far or
@@ -32,15 +33,13 @@
 // that do not fit (rough flow: wider than 32 cells or taller than 6 chunks) take a scalar fp32 path inside the same
 // kernel (sequential fma chain over D, as altcorr.cu), slower and ~2e-5 away from the split product.
 //
-// Measured, 136 x 240, r = 4, D = 256, smooth +-8 px flow (profiles/altcorr_time.py): 162 us per iteration against
-// 560 us for the float32 FMA kernel (altcorr.cu).  510 CTAs = 3.45 waves of ~40 us.  Phase elimination on the GPU
-// (loads, MMAs, extraction, taps switched off in turn): ~15 us per CTA is fixed cost (launch, TMEM allocation, the
-// coordinate fetch and box reduction, the A tile, 96 stage and 12 accumulator hand-shakes), ~20 us the MMAs — M = 64
-// runs the tensor pipe at half rate, and a stage is only 4-8 MMAs of ~60 cycles — and the window extraction and the
-// taps (~6 and ~8 us) hide under them except at the level boundaries; the TMA loads are not on the critical path.
-// Eight epilogue warps instead of four changed nothing (the epilogue is latency-, not issue-bound).  What would move
-// it further: M = 128 (a CTA pair over a 16 x 8 patch sharing one box: full tensor rate and 1/3 less box traffic;
-// the 128 KB A tile + 51 KB of footprints leave no room for it in one CTA), and persistent CTAs that fetch the next
+// Measured, 136 x 240, r = 4, D = 256, smooth +-8 px flow (profiles/altcorr_time.py): 137 us per iteration against
+// 560 us for the float32 FMA kernel (altcorr.cu).  510 CTAs = 3.45 waves.  History and phase elimination: DESIGN.md
+// §4.4.  The last 25 us came from the ISSUE path: with `if (lane == 0)` around the MMA / TMA loops the compiler wraps
+// every tcgen05.mma in a vote-and-broadcast loop (~23 instructions of the one issuing thread per ~60-cycle MMA); the
+// loops now run warp-uniformly and issue under elect.sync, four MMAs per asm statement (tc_ptx.cuh).  What would move
+// it further: M = 128 (a CTA pair over a 16 x 8 patch sharing one box: full tensor rate and 1/3 less box traffic; the
+// 128 KB A tile + 51 KB of footprints leave no room for it in one CTA), and persistent CTAs that fetch the next
 // patch's coordinates and A tile under the current patch's MMAs.
 
 #include <cuda.h>
