@@ -79,7 +79,8 @@ struct Params {
   float* out;
   int B, nq, D, L;
   int rows_q, w_q;
-  int levels_per_cta;   // L: one CTA per patch; 1: one CTA per (patch, level), blockIdx.y = level (few patches: fill the SMs)
+  int npatch;           // 8 x 8 query patches
+  int split_from;       // patches [0, split_from): one CTA per patch, all levels; the rest: one CTA per (patch, level)
   float inv_sqrt_d;
 };
 
@@ -176,8 +177,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   float* F = reinterpret_cast<float*>(smem_b + RING_BYTES);  // [2][TQ][NCELL]: footprints of levels l and l + 1
   float* rowbuf = F + 2 * TQ * NCELL;                        // [4 warps][16 owner lanes][2 rows][ROWBUF_PITCH]
   uint64_t* bars = reinterpret_cast<uint64_t*>(rowbuf + 4 * 16 * 2 * ROWBUF_PITCH);
-  uint64_t* a_full = bars;                      // [1]
-  uint64_t* b_full = bars + 1;                  // [MAX_STAGES]
+  uint64_t* a_full = bars;                      // [4]: one per k-block (its hi and mid tiles)
+  uint64_t* b_full = bars + 4;                  // [MAX_STAGES]
   uint64_t* b_empty = b_full + MAX_STAGES;      // [MAX_STAGES]
   uint64_t* acc_full = b_empty + MAX_STAGES;    // [2]
   uint64_t* acc_empty = acc_full + 2;           // [2]
@@ -188,15 +189,40 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_x = (p.w_q + 7) >> 3, tiles_y = (p.rows_q + 7) >> 3;
-  long long rem = blockIdx.x;
+  // CTAs [0, split_from) take one patch each and all its levels; the CTAs after them take one (patch, level) each,
+  // level 0 first: the short tail work items fill the last, partial wave of patches (and all of a small problem)
+  long long rem;
+  int l_begin, l_end;
+  if ((long long)blockIdx.x < p.split_from) {
+    rem = blockIdx.x;
+    l_begin = 0;
+    l_end = p.L;
+  } else {
+    const long long k = (long long)blockIdx.x - p.split_from, ntail = p.npatch - p.split_from;
+    l_begin = (int)(k / ntail);
+    l_end = l_begin + 1;
+    rem = p.split_from + k % ntail;
+  }
   const int txi = (int)(rem % tiles_x);
   rem /= tiles_x;
   const int tyi = (int)(rem % tiles_y);
   const int b = (int)(rem / tiles_y);
-  const int l_begin = (int)blockIdx.y * p.levels_per_cta, l_end = min(p.L, l_begin + p.levels_per_cta);
 
+  // the A tile depends on nothing but the patch: its loads go out first, one barrier per k-block, so that the first
+  // MMAs wait for 16 KB and the rest arrives under the coordinate fetch and the box reduction
+  if (warp == PRODUCER_WARP) {
+    if (elect_one()) {
+      for (int kb = 0; kb < KB; ++kb) mbar_init(&a_full[kb], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      for (int kb = 0; kb < KB; ++kb) {
+        mbar_expect_tx(&a_full[kb], (uint32_t)(2 * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
+        tma_load_4d(&tmA, &a_full[kb], smem_a + kb * A_BLOCK_BYTES, kb * 64, txi * 8, tyi * 8, b);              // hi
+        tma_load_4d(&tmA, &a_full[kb], smem_a + (KB + kb) * A_BLOCK_BYTES, p.D + kb * 64, txi * 8, tyi * 8, b);  // mid
+      }
+    }
+    __syncwarp();
+  }
   if (warp == MMA_WARP && lane == 0) {
-    mbar_init(a_full, 1);
     for (int s = 0; s < MAX_STAGES; ++s) {
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 1);
@@ -307,12 +333,6 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp == PRODUCER_WARP) {
     // ===================== TMA producer: the whole warp walks the loops, one elected lane issues =====================
-    if (elect_one()) {
-      mbar_expect_tx(a_full, (uint32_t)(2 * KB * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
-      for (int j = 0; j < 2 * KB; ++j)  // [hi | mid] is contiguous in K: block j starts at channel 64 j
-        tma_load_4d(&tmA, a_full, smem_a + j * A_BLOCK_BYTES, j * 64, txi * 8, tyi * 8, b);
-    }
-    __syncwarp();
     int stage = 0;
     uint32_t phase = 0;
     for (int l = l_begin; l < l_end; ++l) {
@@ -339,8 +359,6 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp == MMA_WARP) {
     // ===================== MMA issuer: the whole warp walks the loops, one elected lane issues =====================
-    mbar_wait(a_full, 0);
-    tc_fence_after();
     const uint64_t a_desc0 = umma_desc(smem_u32(smem_a)), b_desc0 = umma_desc(smem_u32(smem_b));
     int stage = 0, g = 0;  // g: chunks issued so far (accumulator g & 1)
     uint32_t phase = 0;
@@ -358,6 +376,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const uint64_t a_hi = a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4));
           const uint64_t a_mid = a_desc0 + (uint64_t)((KB + kb) * (A_BLOCK_BYTES >> 4));
           // stage holding B_hi[kb]: hi*hi and mid*hi
+          if (g == 0) mbar_wait(&a_full[kb], 0);  // first chunk: the A tile may still be arriving
           mbar_wait(&b_full[stage], phase);
           tc_fence_after();
           uint64_t bs = b_desc0 + (uint64_t)(stage * (stage_bytes >> 4));
@@ -389,6 +408,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         __syncwarp();
       }
     }
+    if (g == 0)  // no tensor-core level in this CTA: the A tile must still have landed before the CTA may exit
+      for (int kb = 0; kb < KB; ++kb) mbar_wait(&a_full[kb], 0);
   } else if (half == 0) {
     // ===================== extraction warps 0-3: accumulators -> footprints, level by level =====================
     // F is double-buffered per level and handed to the tap warps through named barriers: 2 + buf "footprints of a
@@ -595,14 +616,22 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8);
   if (nblk > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
-  // fewer than two waves of patches (a row band of a sharded image, a small image): one CTA per (patch, level), level 0
-  // first, so that the SMs fill and the last wave is short (17 x 240: 43 us against 60); otherwise one CTA per patch,
-  // which loads the A tile and sets up once for all levels
-  p.levels_per_cta = nblk <= 2LL * sm_count() ? 1 : num_levels;
-  const unsigned grid_y = (unsigned)((num_levels + p.levels_per_cta - 1) / p.levels_per_cta);
+  // Work items.  One CTA per patch for whole waves of patches (the A tile and the set-up once for all levels); the
+  // patches of a last, partial wave — and all of a problem smaller than two waves (a row band of a sharded image) —
+  // as one CTA per (patch, level), level 0 first, so that the tail fills the SMs with short items.
+  {
+    const long long S_ = sm_count();
+    const long long full = nblk / S_, tail = nblk - full * S_;
+    if (nblk <= 2 * S_) p.split_from = 0;
+    else if (tail == 0 || 4 * tail >= 3 * S_) p.split_from = (int)nblk;
+    else p.split_from = (int)(full * S_);
+  }
+  p.npatch = (int)nblk;
+  const long long ncta = p.split_from + (nblk - p.split_from) * num_levels;
+  if (ncta > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
   auto kernel = radius == 4 ? altcorr_tc_kernel<4> : altcorr_tc_kernel<3>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  kernel<<<dim3((unsigned)nblk, grid_y), NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB[0], tmB[1], tmB[2], tmB[3], p);
+  kernel<<<(unsigned)ncta, NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB[0], tmB[1], tmB[2], tmB[3], p);
   return launch_status();
 }
