@@ -33,7 +33,7 @@
 // that do not fit (rough flow: wider than 32 cells or taller than 6 chunks) take a scalar fp32 path inside the same
 // kernel (sequential fma chain over D, as altcorr.cu), slower and ~2e-5 away from the split product.
 //
-// Measured, 136 x 240, r = 4, D = 256, smooth +-8 px flow (profiles/altcorr_time.py): 137 us per iteration against
+// Measured, 136 x 240, r = 4, D = 256, smooth +-8 px flow (profiles/altcorr_time.py): 128 us per iteration against
 // 560 us for the float32 FMA kernel (altcorr.cu).  510 CTAs = 3.45 waves.  History and phase elimination: DESIGN.md
 // §4.4.  The last 25 us came from the ISSUE path: with `if (lane == 0)` around the MMA / TMA loops the compiler wraps
 // every tcgen05.mma in a vote-and-broadcast loop (~23 instructions of the one issuing thread per ~60-cycle MMA); the
