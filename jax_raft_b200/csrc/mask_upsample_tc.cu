@@ -90,7 +90,6 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-  for (int i = threadIdx.x; i < PASSES * NP; i += NUM_THREADS) smem_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -174,6 +173,10 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       fyk[k] = 8.0f * f.y;
     }
     const long long W8 = 8LL * p.w;
+    // the bias of this CTA's passes -> shared memory, by the epilogue warps alone and after the common barrier: the
+    // producer and the MMA issuer do not wait for these global loads (they complete under the first pass's MMAs)
+    for (int i = threadIdx.x; i < npass * NP; i += EPI_WARPS * 32) smem_bias[pass0 * NP + i] = __ldg(p.bias + pass0 * NP + i);
+    asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
     for (int gi = 0; gi < npass; ++gi) {
       const int g = pass0 + gi, buf = gi & 1;
       mbar_wait(&acc_full[buf], (gi >> 1) & 1);
