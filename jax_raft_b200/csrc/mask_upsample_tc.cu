@@ -18,6 +18,10 @@
 //            tcgen05.ld.32x32b.x8 bring all planes of its sub-pixels into registers, the accumulator is
 //            released at once, then max / exp / sum / convex combination (the arithmetic of
 //            convex_upsample.cu) and one 64-byte output row segment per pass.
+// The CTAs are persistent (one per SM at most, tiles blockIdx.x, + gridDim.x, ...): weight ring, accumulator pair and
+// barrier phases carry over the tile boundary, and the NEXT tile's A blocks are loaded K-block by K-block as the last
+// pass of the current tile releases them (a_empty barriers), so that the 128 KB A tile — which comes from HBM at large
+// batch — arrives under MMAs instead of in front of them; TMEM allocation and the bias staging happen once per CTA.
 // Small batches: the passes are independent (different output rows), so when the pixel tiles alone would leave
 // more than half of the SMs idle (batch 1 at 440x1024: 55 tiles on 148 SMs) the grid gets a second dimension and
 // each CTA runs two of the four passes of its tile (110 CTAs; the A tile is read twice, from L2).
@@ -61,21 +65,28 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + KB * A_BLOCK_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + STAGES * B_STAGE_BYTES);
-  uint64_t* a_full = bars;               // [8]: one per K-block
-  uint64_t* b_full = bars + 8;           // [STAGES]
-  uint64_t* b_empty = b_full + STAGES;   // [STAGES]
-  uint64_t* acc_full = b_empty + STAGES; // [2]
-  uint64_t* acc_empty = acc_full + 2;    // [2]
+  uint64_t* a_full = bars;                // [8]: one per K-block
+  uint64_t* a_empty = bars + 8;           // [8]: the last pass of a tile is done with this K-block of A
+  uint64_t* b_full = bars + 16;           // [STAGES]
+  uint64_t* b_empty = b_full + STAGES;    // [STAGES]
+  uint64_t* acc_full = b_empty + STAGES;  // [2]
+  uint64_t* acc_empty = acc_full + 2;     // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  float* smem_bias = reinterpret_cast<float*>(bars + 24);  // [576]
+  float* smem_bias = reinterpret_cast<float*>(bars + 32);  // [576]
   // this CTA's share of the four passes (gridDim.y = 1: all; 2: two each)
   const int npass = PASSES / (int)gridDim.y, pass0 = (int)blockIdx.y * npass;
+  // persistent over the pixel tiles blockIdx.x, blockIdx.x + gridDim.x, ...: the roles below run one continuous
+  // pipeline across tile boundaries (weight ring, accumulator pair and barrier phases carry over), and the A tile
+  // of the NEXT tile arrives K-block by K-block under the last pass of the current one
+  const long long ntiles = (p.Q + TM - 1) / TM;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long q0 = (long long)blockIdx.x * TM;
 
   if (warp == EPI_WARPS && lane == 0) {
-    for (int kb = 0; kb < 8; ++kb) mbar_init(&a_full[kb], 1);
+    for (int kb = 0; kb < 8; ++kb) {
+      mbar_init(&a_full[kb], 1);
+      mbar_init(&a_empty[kb], 1);
+    }
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 1);
@@ -98,30 +109,39 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   if (warp == EPI_WARPS) {
     // ===================== TMA producer: the whole warp walks the loops, one elected lane issues =====================
     // (uniform control flow keeps tensor-map pointers, barriers and coordinates in uniform registers: tc_ptx.cuh)
-    // the first weight slabs go out between the A blocks, so that the first MMA waits for 16 + 18 KB, not 128 + 18
     int stage = 0;
-    uint32_t phase = 0;
-    for (int g = pass0; g < pass0 + npass; ++g)
-      for (int kb = 0; kb < KB; ++kb) {
-        auto load_a = [&](int k) {
-          mbar_expect_tx(&a_full[k], (uint32_t)A_BLOCK_BYTES);  // rows past Q are zero-filled and still counted
-          tma_load_2d(&tmA, &a_full[k], smem_a + k * A_BLOCK_BYTES, k * 32, (int)q0);
-        };
-        const bool first_ring = g == pass0 && kb < STAGES;  // no ring slot to wait for yet
-        mbar_wait(&b_empty[stage], phase ^ 1);
-        if (elect_one()) {
-          if (first_ring) load_a(kb);
-          mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);
-          tma_load_2d(&tmW, &b_full[stage], smem_b + stage * B_STAGE_BYTES, kb * 32, g * NP);
-          if (first_ring && (kb == STAGES - 1 || kb == KB - 1))  // the rest of the A tile, before the ring blocks
-            for (int k = kb + 1; k < KB; ++k) load_a(k);
+    uint32_t phase = 0, tile_par = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, tile_par ^= 1) {
+      const int q0 = (int)(tile * TM);
+      const bool first_tile = tile == (long long)blockIdx.x;
+      for (int gi = 0; gi < npass; ++gi)
+        for (int kb = 0; kb < KB; ++kb) {
+          if (gi == 0 && kb < STAGES) {
+            // this tile's A blocks: block kb just ahead of the first weight slab that needs it and, once the ring is
+            // primed (kb = STAGES - 1), all the remaining ones, so that they do not queue behind ring slots.  A
+            // block's buffer is free once the previous tile's last pass has consumed it.
+            const int k_end = (kb == STAGES - 1) ? KB : kb + 1;
+            for (int k = kb; k < k_end; ++k) {
+              if (!first_tile) mbar_wait(&a_empty[k], tile_par ^ 1);
+              if (elect_one()) {
+                mbar_expect_tx(&a_full[k], (uint32_t)A_BLOCK_BYTES);  // rows past Q are zero-filled and still counted
+                tma_load_2d(&tmA, &a_full[k], smem_a + k * A_BLOCK_BYTES, k * 32, q0);
+              }
+              __syncwarp();
+            }
+          }
+          mbar_wait(&b_empty[stage], phase ^ 1);
+          if (elect_one()) {
+            mbar_expect_tx(&b_full[stage], B_STAGE_BYTES);
+            tma_load_2d(&tmW, &b_full[stage], smem_b + stage * B_STAGE_BYTES, kb * 32, (pass0 + gi) * NP);
+          }
+          __syncwarp();
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
-        __syncwarp();
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
+    }
   } else if (warp == EPI_WARPS + 1) {
     // ===================== MMA issuer: the whole warp walks the loops, one elected lane issues =====================
     // kind::tf32, D = f32, A = B = tf32, K-major, N = 144, M = 128
@@ -129,95 +149,104 @@ mask_upsample_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     // descriptors differ from their base only in the address field (bytes >> 4; no carry out of it below 256 KB)
     const uint64_t a_desc0 = umma_desc(smem_u32(smem_a)), b_desc0 = umma_desc(smem_u32(smem_b));
     int stage = 0;
-    uint32_t phase = 0;
-    for (int gi = 0; gi < npass; ++gi) {
-      const int buf = gi & 1;
-      mbar_wait(&acc_empty[buf], ((gi >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
-      tc_fence_after();
-      const uint32_t tmem_d = tmem_base + (uint32_t)buf * 256;
-      for (int kb = 0; kb < KB; ++kb) {
-        if (gi == 0) mbar_wait(&a_full[kb], 0);
-        mbar_wait(&b_full[stage], phase);
+    uint32_t phase = 0, tile_par = 0;
+    int gp = 0;  // passes issued so far (accumulator gp & 1)
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, tile_par ^= 1)
+      for (int gi = 0; gi < npass; ++gi, ++gp) {
+        const int buf = gp & 1;
+        mbar_wait(&acc_empty[buf], ((gp >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
         tc_fence_after();
-        if (elect_one()) {
-          tc_mma_tf32_x4(tmem_d, a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4)), b_desc0 + (uint64_t)(stage * (B_STAGE_BYTES >> 4)),
-                         idesc, kb != 0);
-          tc_commit(&b_empty[stage]);
+        const uint32_t tmem_d = tmem_base + (uint32_t)buf * 256;
+        for (int kb = 0; kb < KB; ++kb) {
+          if (gi == 0) mbar_wait(&a_full[kb], tile_par);
+          mbar_wait(&b_full[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            tc_mma_tf32_x4(tmem_d, a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4)), b_desc0 + (uint64_t)(stage * (B_STAGE_BYTES >> 4)),
+                           idesc, kb != 0);
+            tc_commit(&b_empty[stage]);
+            if (gi == npass - 1 && tile + gridDim.x < ntiles) tc_commit(&a_empty[kb]);  // the next tile's A block may land here
+          }
+          __syncwarp();
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
+        if (elect_one()) tc_commit(&acc_full[buf]);
         __syncwarp();
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
       }
-      if (elect_one()) tc_commit(&acc_full[buf]);
-      __syncwarp();
-    }
   } else {
     // ===================== epilogue: thread = (pixel, half of the pass's 16 sub-pixels) =====================
     const int quarter = warp & 3, half = warp >> 2;
-    const long long pix = q0 + 32 * quarter + lane;
-    const bool valid = pix < p.Q;
-    const int x = valid ? (int)(pix % p.w) : 0;
-    const int y = valid ? (int)((pix / p.w) % p.h) : 0;
-    const int b = valid ? (int)(pix / ((long long)p.w * p.h)) : 0;
-    // 8 * flow of the nine neighbours, zero outside the image (SAME padding, model.py:91-92)
-    float fxk[9], fyk[9];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      const int yy = y + k / 3 - 1, xx = x + k % 3 - 1;
-      float2 f = make_float2(0.0f, 0.0f);
-      if (valid && (unsigned)yy < (unsigned)p.h && (unsigned)xx < (unsigned)p.w)
-        f = __ldg(reinterpret_cast<const float2*>(p.flow) + ((long long)b * p.h + yy) * p.w + xx);
-      fxk[k] = 8.0f * f.x;
-      fyk[k] = 8.0f * f.y;
-    }
     const long long W8 = 8LL * p.w;
-    // the bias of this CTA's passes -> shared memory, by the epilogue warps alone and after the common barrier: the
-    // producer and the MMA issuer do not wait for these global loads (they complete under the first pass's MMAs)
-    for (int i = threadIdx.x; i < npass * NP; i += EPI_WARPS * 32) smem_bias[pass0 * NP + i] = __ldg(p.bias + pass0 * NP + i);
-    asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
-    for (int gi = 0; gi < npass; ++gi) {
-      const int g = pass0 + gi, buf = gi & 1;
-      mbar_wait(&acc_full[buf], (gi >> 1) & 1);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * 256 + 8 * half;
-      const float* sb = smem_bias + g * NP + 8 * half;
-      // all nine planes of this thread's eight sub-pixels: 72 registers, one wait
-      float v[9][8];
+    int gp = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long pix = tile * TM + 32 * quarter + lane;
+      const bool valid = pix < p.Q;
+      const int x = valid ? (int)(pix % p.w) : 0;
+      const int y = valid ? (int)((pix / p.w) % p.h) : 0;
+      const int b = valid ? (int)(pix / ((long long)p.w * p.h)) : 0;
+      // 8 * flow of the nine neighbours, zero outside the image (SAME padding, model.py:91-92)
+      float fxk[9], fyk[9];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) tmem_ld_32x8(taddr + k * 16, v[k]);
-      tmem_ld_wait();
-      // the accumulator has been read: hand it back to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[buf]);
-      float o[16];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        float mx = -INFINITY;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) {
-          v[k][i] += sb[k * 16 + i];
-          mx = fmaxf(mx, v[k][i]);
-        }
-        float s = 0.0f, ax = 0.0f, ay = 0.0f;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) {
-          const float e = __expf(v[k][i] - mx);
-          s += e;
-          ax = fmaf(e, fxk[k], ax);
-          ay = fmaf(e, fyk[k], ay);
-        }
-        const float inv = 1.0f / s;
-        o[2 * i] = ax * inv;
-        o[2 * i + 1] = ay * inv;
+      for (int k = 0; k < 9; ++k) {
+        const int yy = y + k / 3 - 1, xx = x + k % 3 - 1;
+        float2 f = make_float2(0.0f, 0.0f);
+        if (valid && (unsigned)yy < (unsigned)p.h && (unsigned)xx < (unsigned)p.w)
+          f = __ldg(reinterpret_cast<const float2*>(p.flow) + ((long long)b * p.h + yy) * p.w + xx);
+        fxk[k] = 8.0f * f.x;
+        fyk[k] = 8.0f * f.y;
       }
-      if (valid) {
-        // sub-pixels 16g + 8*half + i -> output row fy = 2g + half, fx = i: 8 pixels x 2 channels = 64 bytes
-        float* orow = p.out + (((long long)b * 8 * p.h + 8 * y + 2 * g + half) * W8 + 8 * x) * 2;
+      if (tile == (long long)blockIdx.x) {
+        // the bias of this CTA's passes -> shared memory, once, by the epilogue warps alone and after the common
+        // barrier: the producer and the MMA issuer do not wait for these global loads, which complete (like the flow
+        // loads above) under the first pass's MMAs
+        for (int i = threadIdx.x; i < npass * NP; i += EPI_WARPS * 32) smem_bias[pass0 * NP + i] = __ldg(p.bias + pass0 * NP + i);
+        asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+      }
+      for (int gi = 0; gi < npass; ++gi, ++gp) {
+        const int g = pass0 + gi, buf = gp & 1;
+        mbar_wait(&acc_full[buf], (gp >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * 256 + 8 * half;
+        const float* sb = smem_bias + g * NP + 8 * half;
+        // all nine planes of this thread's eight sub-pixels: 72 registers, one wait
+        float v[9][8];
 #pragma unroll
-        for (int j = 0; j < 16; j += 4) st_na_f4(orow + j, make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]));
+        for (int k = 0; k < 9; ++k) tmem_ld_32x8(taddr + k * 16, v[k]);
+        tmem_ld_wait();
+        // the accumulator has been read: hand it back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        float o[16];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float mx = -INFINITY;
+#pragma unroll
+          for (int k = 0; k < 9; ++k) {
+            v[k][i] += sb[k * 16 + i];
+            mx = fmaxf(mx, v[k][i]);
+          }
+          float s = 0.0f, ax = 0.0f, ay = 0.0f;
+#pragma unroll
+          for (int k = 0; k < 9; ++k) {
+            const float e = __expf(v[k][i] - mx);
+            s += e;
+            ax = fmaf(e, fxk[k], ax);
+            ay = fmaf(e, fyk[k], ay);
+          }
+          const float inv = 1.0f / s;
+          o[2 * i] = ax * inv;
+          o[2 * i + 1] = ay * inv;
+        }
+        if (valid) {
+          // sub-pixels 16g + 8*half + i -> output row fy = 2g + half, fx = i: 8 pixels x 2 channels = 64 bytes
+          float* orow = p.out + (((long long)b * 8 * p.h + 8 * y + 2 * g + half) * W8 + 8 * x) * 2;
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) st_na_f4(orow + j, make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]));
+        }
       }
     }
   }
@@ -277,13 +306,15 @@ extern "C" int raftk_mask_upsample(const float* m, const float* weight, const fl
   p.w = w;
   p.K = K;
   p.Q = Q;
-  const size_t smem = 1024 + (size_t)(K / 32) * A_BLOCK_BYTES + (size_t)STAGES * B_STAGE_BYTES + 192 + PASSES * NP * 4;
+  const size_t smem = 1024 + (size_t)(K / 32) * A_BLOCK_BYTES + (size_t)STAGES * B_STAGE_BYTES + 256 + PASSES * NP * 4;
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   cudaError_t e = cudaFuncSetAttribute(mask_upsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   const long long blocks = (Q + TM - 1) / TM;
   // pixel tiles alone would leave more than half of the SMs idle: two CTAs per tile, two passes each
   const unsigned split = 2 * blocks <= (long long)sm_count() ? 2u : 1u;
-  mask_upsample_kernel<<<dim3((unsigned)blocks, split), NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmW, p);
+  // persistent: one CTA per SM at most, each walking the tiles blockIdx.x, blockIdx.x + gridDim.x, ...
+  const long long grid_x = blocks < (long long)sm_count() ? blocks : (long long)sm_count();
+  mask_upsample_kernel<<<dim3((unsigned)grid_x, split), NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmW, p);
   return launch_status();
 }
