@@ -156,12 +156,55 @@ __device__ __forceinline__ void column_taps_level(const float* Fw, float cx, flo
   }
 }
 
-// what every role needs to know about one level of the patch (shared memory, written once)
+// what every role needs to know about one level of a patch
 struct LevelBox {
   int X0, Y0, BW, BH;   // bounding box of the windows (BW = 0: no query of the patch has a window at this level)
   int tc;               // 1: tensor-core path (the box fits), 0: scalar path
   int ncb, nchunks, rows;
 };
+
+// One work item's description, written by the producer warp one item ahead of the other roles (two slots).
+struct ItemInfo {
+  LevelBox lbox[4];
+  QInfo qinfo[4][TQ];
+  float2 coord[TQ];
+  long long qidx[TQ];
+  int valid[TQ];
+};
+
+struct Item {
+  int txi, tyi, b, l_begin, l_end;
+};
+
+// Work items [0, split_from): one patch, all levels; the items after them: one (patch, level), level 0 first — the
+// short items fill what would be a last, partial wave of patches (and all of a small problem).
+__device__ __forceinline__ Item decode_item(const Params& p, long long i, int tiles_x, int tiles_y) {
+  Item it;
+  long long rem;
+  if (i < p.split_from) {
+    rem = i;
+    it.l_begin = 0;
+    it.l_end = p.L;
+  } else {
+    const long long k = i - p.split_from, ntail = p.npatch - p.split_from;
+    it.l_begin = (int)(k / ntail);
+    it.l_end = it.l_begin + 1;
+    rem = p.split_from + k % ntail;
+  }
+  it.txi = (int)(rem % tiles_x);
+  rem /= tiles_x;
+  it.tyi = (int)(rem % tiles_y);
+  it.b = (int)(rem / tiles_y);
+  return it;
+}
+
+// Ring geometry of one item: a stage holds the widest chunk of the item's tensor-core levels; as many stages as fit.
+__device__ __forceinline__ int item_stage_bytes(const ItemInfo& nf, const Item& it) {
+  int sb = 8 * 1024;
+  for (int l = it.l_begin; l < it.l_end; ++l)
+    if (nf.lbox[l].tc) sb = max(sb, nf.lbox[l].ncb * nf.lbox[l].rows * 1024);
+  return sb;
+}
 
 template <int R>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -174,55 +217,34 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int KB = p.D / 64;  // k-blocks per plane (hi, mid)
   uint8_t* smem_a = smem;                                   // [2 KB][A_BLOCK_BYTES]: hi blocks, then mid blocks
   uint8_t* smem_b = smem_a + 2 * KB * A_BLOCK_BYTES;        // ring of RING_BYTES
-  float* F = reinterpret_cast<float*>(smem_b + RING_BYTES);  // [2][TQ][NCELL]: footprints of levels l and l + 1
+  float* F = reinterpret_cast<float*>(smem_b + RING_BYTES);  // [2][TQ][NCELL]: footprints of two consecutive levels
   float* rowbuf = F + 2 * TQ * NCELL;                        // [4 warps][16 owner lanes][2 rows][ROWBUF_PITCH]
   uint64_t* bars = reinterpret_cast<uint64_t*>(rowbuf + 4 * 16 * 2 * ROWBUF_PITCH);
   uint64_t* a_full = bars;                      // [4]: one per k-block (its hi and mid tiles)
-  uint64_t* b_full = bars + 4;                  // [MAX_STAGES]
+  uint64_t* a_empty = bars + 4;                 // [4]: the item's last MMAs are done with this k-block of A
+  uint64_t* b_full = bars + 8;                  // [MAX_STAGES]
   uint64_t* b_empty = b_full + MAX_STAGES;      // [MAX_STAGES]
   uint64_t* acc_full = b_empty + MAX_STAGES;    // [2]
   uint64_t* acc_empty = acc_full + 2;           // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  int* red = reinterpret_cast<int*>(bars + 32);             // [4 levels][5][4 warps]
-  LevelBox* lbox = reinterpret_cast<LevelBox*>(red + 80);   // [4]
-  QInfo* qinfo = reinterpret_cast<QInfo*>(lbox + 4);        // [4][TQ]
+  uint64_t* info_full = acc_empty + 2;          // [2]: the producer has described the item in this slot
+  uint64_t* info_empty = info_full + 2;         // [2]: MMA issuer + 4 extraction + 4 tap warps are done with it
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(info_empty + 2);
+  ItemInfo* info = reinterpret_cast<ItemInfo*>(bars + 40);  // [2]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_x = (p.w_q + 7) >> 3, tiles_y = (p.rows_q + 7) >> 3;
-  // CTAs [0, split_from) take one patch each and all its levels; the CTAs after them take one (patch, level) each,
-  // level 0 first: the short tail work items fill the last, partial wave of patches (and all of a small problem)
-  long long rem;
-  int l_begin, l_end;
-  if ((long long)blockIdx.x < p.split_from) {
-    rem = blockIdx.x;
-    l_begin = 0;
-    l_end = p.L;
-  } else {
-    const long long k = (long long)blockIdx.x - p.split_from, ntail = p.npatch - p.split_from;
-    l_begin = (int)(k / ntail);
-    l_end = l_begin + 1;
-    rem = p.split_from + k % ntail;
-  }
-  const int txi = (int)(rem % tiles_x);
-  rem /= tiles_x;
-  const int tyi = (int)(rem % tiles_y);
-  const int b = (int)(rem / tiles_y);
+  const long long nitems = p.split_from + (long long)(p.npatch - p.split_from) * p.L;
+  // persistent: this CTA walks the items blockIdx.x, blockIdx.x + gridDim.x, ...; the roles below run one continuous
+  // pipeline across items (B ring, accumulators, footprint buffers and barrier phases carry over), the producer
+  // describes item j + 1 and fetches its A tile while item j is being multiplied
+  int my_levels = 0;  // levels this CTA will process in total (the tap warps' hand-back of a footprint buffer needs it)
+  for (long long i = blockIdx.x; i < nitems; i += gridDim.x) my_levels += i < p.split_from ? p.L : 1;
 
-  // the A tile depends on nothing but the patch: its loads go out first, one barrier per k-block, so that the first
-  // MMAs wait for 16 KB and the rest arrives under the coordinate fetch and the box reduction
-  if (warp == PRODUCER_WARP) {
-    if (elect_one()) {
-      for (int kb = 0; kb < KB; ++kb) mbar_init(&a_full[kb], 1);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      for (int kb = 0; kb < KB; ++kb) {
-        mbar_expect_tx(&a_full[kb], (uint32_t)(2 * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
-        tma_load_4d(&tmA, &a_full[kb], smem_a + kb * A_BLOCK_BYTES, kb * 64, txi * 8, tyi * 8, b);              // hi
-        tma_load_4d(&tmA, &a_full[kb], smem_a + (KB + kb) * A_BLOCK_BYTES, p.D + kb * 64, txi * 8, tyi * 8, b);  // mid
-      }
-    }
-    __syncwarp();
-  }
   if (warp == MMA_WARP && lane == 0) {
+    for (int kb = 0; kb < 4; ++kb) {
+      mbar_init(&a_full[kb], 1);
+      mbar_init(&a_empty[kb], 1);
+    }
     for (int s = 0; s < MAX_STAGES; ++s) {
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 1);
@@ -230,6 +252,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_empty[i], 4);  // one arrival per extraction warp
+      mbar_init(&info_full[i], 1);
+      mbar_init(&info_empty[i], 9);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -237,285 +261,342 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-
-  // ---- the queries of this patch, their window origins, and per level the bounding box of the windows ----
-  // epilogue thread (warp w < 8, lane < 16) owns query m = 16 (w % 4) + lane = (row m / 8, column m % 8) of the
-  // patch: the accumulator row its TMEM lane holds (warps w and w + 4 share a lane quarter and its 16 queries).
-  // haswin: finite, not absurdly far, and the window overlaps the level.  Queries without a window read nothing —
-  // their footprint is all zeros whatever path a patch takes — and stay out of the bounding box, so that one stray
-  // query does not change how its neighbours are computed.
-  const int quarter = warp & 3, half = warp >> 2;
-  const int m = 16 * quarter + lane;
-  const bool owner = warp < EPI_WARPS && lane < 16;
-  bool qvalid = false;
-  long long q = 0;
-  float cx = 0.0f, cy = 0.0f;
-  int bx[4] = {0, 0, 0, 0}, by[4] = {0, 0, 0, 0};
-  unsigned winmask = 0;  // bit l: this query has a window at level l
-  if (owner) {
-    const int qy = tyi * 8 + (m >> 3), qx = txi * 8 + (m & 7);
-    qvalid = qy < p.rows_q && qx < p.w_q;
-    if (qvalid) {
-      q = (long long)b * p.nq + (long long)qy * p.w_q + qx;
-      cx = __ldg(p.coords + 2 * q);
-      cy = __ldg(p.coords + 2 * q + 1);
-    }
-    const bool normal = fabsf(cx) <= 1.0e6f && fabsf(cy) <= 1.0e6f;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) {
-      if (l < p.L) {
-        const float sc = __int_as_float((127 - l) << 23);
-        bx[l] = clamp_to_int(floorf(cx * sc)) - R;
-        by[l] = clamp_to_int(floorf(cy * sc)) - R;
-        const bool hw = qvalid && normal && bx[l] < p.lw[l] && bx[l] + FP > 0 && by[l] < p.lh[l] && by[l] + FP > 0;
-        if (hw) winmask |= 1u << l;
-        if (half == 0) qinfo[l * TQ + m] = QInfo{bx[l], by[l], (qvalid ? 1 : 0) | (hw ? 2 : 0), 0};
-      }
-    }
-  }
-#pragma unroll
-  for (int l = 0; l < 4; ++l) {
-    if (l < p.L) {
-      const bool hw = (winmask >> l) & 1u;
-      int mnx = hw ? bx[l] : 0x7fffffff, mxx = hw ? bx[l] : -0x7fffffff;
-      int mny = hw ? by[l] : 0x7fffffff, mxy = hw ? by[l] : -0x7fffffff;
-      int any = hw ? 1 : 0;
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) {
-        mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, off));
-        mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, off));
-        mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, off));
-        mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, off));
-        any |= __shfl_xor_sync(0xffffffffu, any, off);
-      }
-      if (warp < 4 && lane == 0) {
-        int* rl = red + l * 20;
-        rl[0 * 4 + warp] = mnx;
-        rl[1 * 4 + warp] = mxx;
-        rl[2 * 4 + warp] = mny;
-        rl[3 * 4 + warp] = mxy;
-        rl[4 * 4 + warp] = any;
-      }
-    }
-  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (threadIdx.x < p.L) {
-    const int l = threadIdx.x;
-    const int* rl = red + l * 20;
-    int mnx = rl[0], mxx = rl[4], mny = rl[8], mxy = rl[12], any = rl[16];
-    for (int i = 1; i < 4; ++i) {
-      mnx = min(mnx, rl[i]);
-      mxx = max(mxx, rl[4 + i]);
-      mny = min(mny, rl[8 + i]);
-      mxy = max(mxy, rl[12 + i]);
-      any |= rl[16 + i];
-    }
-    LevelBox lb;
-    lb.X0 = any ? mnx : 0;
-    lb.Y0 = any ? mny : 0;
-    lb.BW = any ? mxx - mnx + FP : 0;  // width in cells
-    lb.BH = any ? mxy - mny + FP : 0;  // height
-    lb.rows = p.rows[l];
-    lb.tc = (lb.BW <= 8 * MAX_CB && lb.BH <= lb.rows * MAX_CHUNKS) ? 1 : 0;
-    lb.ncb = (lb.BW + 7) >> 3;
-    lb.nchunks = (lb.BH + lb.rows - 1) / lb.rows;
-    lbox[l] = lb;
-  }
-  __syncthreads();
   const uint32_t tmem_base = *tmem_slot;
-  // ring geometry: one stage holds the widest chunk of this patch's tensor-core levels
-  int stage_bytes = 8 * 1024;
-  for (int l = l_begin; l < l_end; ++l)
-    if (lbox[l].tc) stage_bytes = max(stage_bytes, lbox[l].ncb * lbox[l].rows * 1024);
-  const int nstages = min(MAX_STAGES, RING_BYTES / stage_bytes);
+  const int quarter = warp & 3;
 
   if (warp == PRODUCER_WARP) {
-    // ===================== TMA producer: the whole warp walks the loops, one elected lane issues =====================
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int l = l_begin; l < l_end; ++l) {
-      const LevelBox lb = lbox[l];
-      if (!lb.tc) continue;
-      const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
-      const int cb_bytes = lb.rows * 1024;
-      for (int c = 0; c < lb.nchunks; ++c)
-        for (int kb = 0; kb < KB; ++kb)
-          for (int part = 0; part < 2; ++part) {
-            mbar_wait(&b_empty[stage], phase ^ 1);
-            if (elect_one()) {
-              mbar_expect_tx(&b_full[stage], (uint32_t)(lb.ncb * cb_bytes));
-              for (int cb = 0; cb < lb.ncb; ++cb)
-                tma_load_4d(tmB, &b_full[stage], smem_b + stage * stage_bytes + cb * cb_bytes, part * p.D + kb * 64,
-                            lb.X0 + 8 * cb, lb.Y0 + lb.rows * c, b);
-            }
-            __syncwarp();
-            if (++stage == nstages) {
-              stage = 0;
-              phase ^= 1;
-            }
+    // ===================== producer: item descriptions, the A tile, the B ring =====================
+    // (the whole warp walks the loops, one elected lane issues: tc_ptx.cuh)
+    // B ring bookkeeping: every slot has its own full / empty barrier; `used`: the slot holds a stage whose release
+    // has not been awaited yet, `epar`: phase bit of its empty barrier.  Consecutive items almost always share the
+    // ring geometry; when it changes the ring is drained first.
+    int cur = 0, j = 0, sbytes = 0, nst = 1;
+    uint32_t used = 0, epar = 0;
+    for (long long i = blockIdx.x; i < nitems; i += gridDim.x, ++j) {
+      const Item it = decode_item(p, i, tiles_x, tiles_y);
+      ItemInfo& nf = info[j & 1];
+      if (j >= 2) mbar_wait(&info_empty[j & 1], (uint32_t)(((j >> 1) - 1) & 1));
+      // ---- the queries of this patch, their window origins, and per level the bounding box of the windows ----
+      // haswin: finite, not absurdly far, and the window overlaps the level.  Queries without a window read nothing —
+      // their footprint is all zeros whatever path a patch takes — and stay out of the bounding box, so that one
+      // stray query does not change how its neighbours are computed.  Lane t describes queries t and t + 32.
+      float cx[2], cy[2];
+      bool qv[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int m = lane + 32 * u;
+        const int qy = it.tyi * 8 + (m >> 3), qx = it.txi * 8 + (m & 7);
+        qv[u] = qy < p.rows_q && qx < p.w_q;
+        const long long q = (long long)it.b * p.nq + (long long)qy * p.w_q + qx;
+        cx[u] = cy[u] = 0.0f;
+        if (qv[u]) {
+          cx[u] = __ldg(p.coords + 2 * q);
+          cy[u] = __ldg(p.coords + 2 * q + 1);
+        }
+        nf.coord[m] = make_float2(cx[u], cy[u]);
+        nf.qidx[m] = q;
+        nf.valid[m] = qv[u] ? 1 : 0;
+      }
+      for (int l = it.l_begin; l < it.l_end; ++l) {
+        const int lh = l == 0 ? p.lh[0] : l == 1 ? p.lh[1] : l == 2 ? p.lh[2] : p.lh[3];
+        const int lw = l == 0 ? p.lw[0] : l == 1 ? p.lw[1] : l == 2 ? p.lw[2] : p.lw[3];
+        const float sc = __int_as_float((127 - l) << 23);
+        int mnx = 0x7fffffff, mxx = -0x7fffffff, mny = 0x7fffffff, mxy = -0x7fffffff, any = 0;
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const bool normal = fabsf(cx[u]) <= 1.0e6f && fabsf(cy[u]) <= 1.0e6f;
+          const int bx = clamp_to_int(floorf(cx[u] * sc)) - R, by = clamp_to_int(floorf(cy[u] * sc)) - R;
+          const bool hw = qv[u] && normal && bx < lw && bx + FP > 0 && by < lh && by + FP > 0;
+          nf.qinfo[l][lane + 32 * u] = QInfo{bx, by, (qv[u] ? 1 : 0) | (hw ? 2 : 0), 0};
+          if (hw) {
+            mnx = min(mnx, bx);
+            mxx = max(mxx, bx);
+            mny = min(mny, by);
+            mxy = max(mxy, by);
+            any = 1;
           }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, off));
+          mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, off));
+          mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, off));
+          mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, off));
+          any |= __shfl_xor_sync(0xffffffffu, any, off);
+        }
+        if (lane == 0) {
+          LevelBox lb;
+          lb.X0 = any ? mnx : 0;
+          lb.Y0 = any ? mny : 0;
+          lb.BW = any ? mxx - mnx + FP : 0;  // width in cells
+          lb.BH = any ? mxy - mny + FP : 0;  // height
+          lb.rows = p.rows[l];
+          lb.tc = (lb.BW <= 8 * MAX_CB && lb.BH <= lb.rows * MAX_CHUNKS) ? 1 : 0;
+          lb.ncb = (lb.BW + 7) >> 3;
+          lb.nchunks = (lb.BH + lb.rows - 1) / lb.rows;
+          nf.lbox[l] = lb;
+        }
+      }
+      __threadfence_block();
+      __syncwarp();
+      if (elect_one()) mbar_arrive(&info_full[j & 1]);
+      __syncwarp();
+      // ---- the A tile, one barrier per k-block; its buffer is free once the previous item's last MMAs have read it ----
+      for (int kb = 0; kb < KB; ++kb) {
+        if (j >= 1) mbar_wait(&a_empty[kb], (uint32_t)((j - 1) & 1));
+        if (elect_one()) {
+          mbar_expect_tx(&a_full[kb], (uint32_t)(2 * A_BLOCK_BYTES));  // rows outside the image are zero-filled and counted
+          tma_load_4d(&tmA, &a_full[kb], smem_a + kb * A_BLOCK_BYTES, kb * 64, it.txi * 8, it.tyi * 8, it.b);              // hi
+          tma_load_4d(&tmA, &a_full[kb], smem_a + (KB + kb) * A_BLOCK_BYTES, p.D + kb * 64, it.txi * 8, it.tyi * 8, it.b);  // mid
+        }
+        __syncwarp();
+      }
+      // ---- the B ring: one (chunk, k-block, hi | mid) slab per stage ----
+      {
+        const int sb = item_stage_bytes(nf, it);
+        if (sb != sbytes) {  // new geometry: every stage in flight must have been consumed before slots move
+          for (int sl = 0; sl < MAX_STAGES; ++sl)
+            if (used & (1u << sl)) {
+              mbar_wait(&b_empty[sl], (epar >> sl) & 1u);
+              epar ^= 1u << sl;
+            }
+          used = 0;
+          cur = 0;
+          sbytes = sb;
+          nst = min(MAX_STAGES, RING_BYTES / sb);
+        }
+      }
+      for (int l = it.l_begin; l < it.l_end; ++l) {
+        const LevelBox lb = nf.lbox[l];
+        if (!lb.tc) continue;
+        const CUtensorMap* tmB = l == 0 ? &tmB0 : l == 1 ? &tmB1 : l == 2 ? &tmB2 : &tmB3;
+        const int cb_bytes = lb.rows * 1024;
+        for (int c = 0; c < lb.nchunks; ++c)
+          for (int kb = 0; kb < KB; ++kb)
+            for (int part = 0; part < 2; ++part) {
+              const uint32_t bit = 1u << cur;
+              if (used & bit) {
+                mbar_wait(&b_empty[cur], (epar >> cur) & 1u);
+                epar ^= bit;
+              }
+              used |= bit;
+              if (elect_one()) {
+                mbar_expect_tx(&b_full[cur], (uint32_t)(lb.ncb * cb_bytes));
+                for (int cb = 0; cb < lb.ncb; ++cb)
+                  tma_load_4d(tmB, &b_full[cur], smem_b + cur * sbytes + cb * cb_bytes, part * p.D + kb * 64,
+                              lb.X0 + 8 * cb, lb.Y0 + lb.rows * c, it.b);
+              }
+              __syncwarp();
+              if (++cur == nst) cur = 0;
+            }
+      }
     }
   } else if (warp == MMA_WARP) {
     // ===================== MMA issuer: the whole warp walks the loops, one elected lane issues =====================
     const uint64_t a_desc0 = umma_desc(smem_u32(smem_a)), b_desc0 = umma_desc(smem_u32(smem_b));
-    int stage = 0, g = 0;  // g: chunks issued so far (accumulator g & 1)
-    uint32_t phase = 0;
-    for (int l = l_begin; l < l_end; ++l) {
-      const LevelBox lb = lbox[l];
-      if (!lb.tc) continue;
-      const uint32_t idesc = make_idesc_bf16(TQ, lb.ncb * lb.rows * 8);
-      for (int c = 0; c < lb.nchunks; ++c, ++g) {
-        const int buf = g & 1;
-        mbar_wait(&acc_empty[buf], ((g >> 1) & 1) ^ 1);  // the extraction has drained this accumulator
-        tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)buf * ACC_COLS;
-        for (int kb = 0; kb < KB; ++kb) {
-          // descriptors differ from their base only in the address field (bytes >> 4, no carry out of it below 256 KB)
-          const uint64_t a_hi = a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4));
-          const uint64_t a_mid = a_desc0 + (uint64_t)((KB + kb) * (A_BLOCK_BYTES >> 4));
-          // stage holding B_hi[kb]: hi*hi and mid*hi
-          if (g == 0) mbar_wait(&a_full[kb], 0);  // first chunk: the A tile may still be arriving
-          mbar_wait(&b_full[stage], phase);
-          tc_fence_after();
-          uint64_t bs = b_desc0 + (uint64_t)(stage * (stage_bytes >> 4));
-          if (elect_one()) {
-            tc_mma_f16_x4(tmem_d, a_hi, bs, idesc, kb != 0);
-            tc_mma_f16_x4(tmem_d, a_mid, bs, idesc, 1);
-            tc_commit(&b_empty[stage]);
-          }
-          __syncwarp();
-          if (++stage == nstages) {
-            stage = 0;
-            phase ^= 1;
-          }
-          // stage holding B_mid[kb]: hi*mid
-          mbar_wait(&b_full[stage], phase);
-          tc_fence_after();
-          bs = b_desc0 + (uint64_t)(stage * (stage_bytes >> 4));
-          if (elect_one()) {
-            tc_mma_f16_x4(tmem_d, a_hi, bs, idesc, 1);
-            tc_commit(&b_empty[stage]);
-          }
-          __syncwarp();
-          if (++stage == nstages) {
-            stage = 0;
-            phase ^= 1;
-          }
+    int cur = 0, g = 0, j = 0, sbytes = 0, nst = 1;  // g: chunks issued so far (accumulator g & 1)
+    uint32_t fpar = 0;                               // per ring slot: phase bit of its full barrier
+    for (long long i = blockIdx.x; i < nitems; i += gridDim.x, ++j) {
+      const Item it = decode_item(p, i, tiles_x, tiles_y);
+      const ItemInfo& nf = info[j & 1];
+      mbar_wait(&info_full[j & 1], (uint32_t)((j >> 1) & 1));
+      {
+        const int sb = item_stage_bytes(nf, it);  // the producer's ring geometry for this item
+        if (sb != sbytes) {
+          cur = 0;
+          sbytes = sb;
+          nst = min(MAX_STAGES, RING_BYTES / sb);
         }
-        if (elect_one()) tc_commit(&acc_full[buf]);
-        __syncwarp();
       }
+      // the item's last tensor-core chunk hands the A tile back (none: plain arrivals below)
+      int last_l = -1;
+      for (int l = it.l_begin; l < it.l_end; ++l)
+        if (nf.lbox[l].tc && nf.lbox[l].nchunks > 0) last_l = l;
+      const bool more = i + gridDim.x < nitems;  // another item follows: its A tile waits for this one's release
+      bool first = true;
+      for (int l = it.l_begin; l < it.l_end; ++l) {
+        const LevelBox lb = nf.lbox[l];
+        if (!lb.tc) continue;
+        const uint32_t idesc = make_idesc_bf16(TQ, lb.ncb * lb.rows * 8);
+        for (int c = 0; c < lb.nchunks; ++c, ++g) {
+          const int buf = g & 1;
+          const bool last_chunk = more && l == last_l && c == lb.nchunks - 1;
+          mbar_wait(&acc_empty[buf], ((g >> 1) & 1) ^ 1);  // the extraction has drained this accumulator
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + (uint32_t)buf * ACC_COLS;
+          for (int kb = 0; kb < KB; ++kb) {
+            // descriptors differ from their base only in the address field (bytes >> 4, no carry out of it below 256 KB)
+            const uint64_t a_hi = a_desc0 + (uint64_t)(kb * (A_BLOCK_BYTES >> 4));
+            const uint64_t a_mid = a_desc0 + (uint64_t)((KB + kb) * (A_BLOCK_BYTES >> 4));
+            // stage holding B_hi[kb]: hi*hi and mid*hi
+            if (first) mbar_wait(&a_full[kb], (uint32_t)(j & 1));  // first chunk: the A tile may still be arriving
+            mbar_wait(&b_full[cur], (fpar >> cur) & 1u);
+            fpar ^= 1u << cur;
+            tc_fence_after();
+            uint64_t bs = b_desc0 + (uint64_t)(cur * (sbytes >> 4));
+            if (elect_one()) {
+              tc_mma_f16_x4(tmem_d, a_hi, bs, idesc, kb != 0);
+              tc_mma_f16_x4(tmem_d, a_mid, bs, idesc, 1);
+              tc_commit(&b_empty[cur]);
+            }
+            __syncwarp();
+            if (++cur == nst) cur = 0;
+            // stage holding B_mid[kb]: hi*mid
+            mbar_wait(&b_full[cur], (fpar >> cur) & 1u);
+            fpar ^= 1u << cur;
+            tc_fence_after();
+            bs = b_desc0 + (uint64_t)(cur * (sbytes >> 4));
+            if (elect_one()) {
+              tc_mma_f16_x4(tmem_d, a_hi, bs, idesc, 1);
+              tc_commit(&b_empty[cur]);
+              if (last_chunk) tc_commit(&a_empty[kb]);  // the next item's A block may land here
+            }
+            __syncwarp();
+            if (++cur == nst) cur = 0;
+          }
+          first = false;
+          if (elect_one()) tc_commit(&acc_full[buf]);
+          __syncwarp();
+        }
+      }
+      if (last_l < 0) {  // no tensor-core chunk in this item: the A tile must still have landed before it is replaced
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&a_full[kb], (uint32_t)(j & 1));
+          if (more && elect_one()) mbar_arrive(&a_empty[kb]);
+          __syncwarp();
+        }
+      }
+      if (elect_one()) mbar_arrive(&info_empty[j & 1]);
+      __syncwarp();
     }
-    if (g == 0)  // no tensor-core level in this CTA: the A tile must still have landed before the CTA may exit
-      for (int kb = 0; kb < KB; ++kb) mbar_wait(&a_full[kb], 0);
-  } else if (half == 0) {
+  } else if (warp < 4) {
     // ===================== extraction warps 0-3: accumulators -> footprints, level by level =====================
     // F is double-buffered per level and handed to the tap warps through named barriers: 2 + buf "footprints of a
     // level complete" (extraction arrives, taps wait), 4 + buf "buffer free again" (taps arrive, extraction waits).
-    int g = 0;
-    for (int l = l_begin; l < l_end; ++l) {
-      const LevelBox lb = lbox[l];
-      const int fb = (l - l_begin) & 1;
-      float* Fl = F + fb * TQ * NCELL;
-      float* Fq = Fl + m * NCELL;
-      const bool haswin = (winmask >> l) & 1u;
-      if (l - l_begin >= 2) asm volatile("bar.sync %0, 256;" ::"r"(4 + fb) : "memory");  // the taps of level l - 2 are done with it
-      if (owner && qvalid && !haswin)
-        for (int e = 0; e < NCELL; ++e) Fq[e] = 0.0f;
-      if (lb.tc) {
-        const int ox = (l == 0 ? bx[0] : l == 1 ? bx[1] : l == 2 ? bx[2] : bx[3]) - lb.X0;  // window origin inside the box
-        const int oy = (l == 0 ? by[0] : l == 1 ? by[1] : l == 2 ? by[2] : by[3]) - lb.Y0;
-        float* rb = rowbuf + (warp * 16 + (lane & 15)) * 2 * ROWBUF_PITCH;  // two box rows per thread
-        for (int c = 0; c < lb.nchunks; ++c, ++g) {
-          const int buf = g & 1;
-          mbar_wait(&acc_full[buf], (g >> 1) & 1);
-          tc_fence_after();
-          const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * ACC_COLS;
+    const int m = 16 * quarter + (lane & 15);  // the query whose accumulator row this thread's TMEM lane holds
+    const bool owner = lane < 16;
+    int g = 0, lv = 0, j = 0;  // chunks, levels, items so far
+    for (long long i = blockIdx.x; i < nitems; i += gridDim.x, ++j) {
+      const Item it = decode_item(p, i, tiles_x, tiles_y);
+      const ItemInfo& nf = info[j & 1];
+      mbar_wait(&info_full[j & 1], (uint32_t)((j >> 1) & 1));
+      for (int l = it.l_begin; l < it.l_end; ++l, ++lv) {
+        const LevelBox lb = nf.lbox[l];
+        const QInfo qi = nf.qinfo[l][m];
+        const int fb = lv & 1;
+        float* Fl = F + fb * TQ * NCELL;
+        float* Fq = Fl + m * NCELL;
+        const bool qvalid = owner && (qi.flags & 1), haswin = owner && (qi.flags & 2);
+        if (lv >= 2) asm volatile("bar.sync %0, 256;" ::"r"(4 + fb) : "memory");  // the taps of level lv - 2 are done with it
+        if (qvalid && !haswin)
+          for (int e = 0; e < NCELL; ++e) Fq[e] = 0.0f;
+        if (lb.tc) {
+          const int ox = qi.bx - lb.X0, oy = qi.by - lb.Y0;  // window origin inside the box
+          float* rb = rowbuf + (warp * 16 + (lane & 15)) * 2 * ROWBUF_PITCH;  // two box rows per thread
+          for (int c = 0; c < lb.nchunks; ++c, ++g) {
+            const int buf = g & 1;
+            mbar_wait(&acc_full[buf], (g >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * ACC_COLS;
 #pragma unroll 1
-          for (int r = 0; r < lb.rows; r += 2) {  // two box rows per TMEM round trip
-            const int row = c * lb.rows + r;
-            if (row >= lb.BH) break;
-            const bool two = r + 1 < lb.rows && row + 1 < lb.BH;
-            float v[2][8 * MAX_CB];
-#pragma unroll
-            for (int cb = 0; cb < MAX_CB; ++cb)
-              if (cb < lb.ncb) {
-                tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + r * 8), v[0] + 8 * cb);
-                if (two) tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + (r + 1) * 8), v[1] + 8 * cb);
-              }
-            tmem_ld_wait();
-            // the rows go to this thread's row buffer (16-byte stores, static register indices); the <= 2r+2 cells
-            // of the thread's own window are then copied out at a dynamic shared-memory offset
-#pragma unroll
-            for (int rr = 0; rr < 2; ++rr)
+            for (int r = 0; r < lb.rows; r += 2) {  // two box rows per TMEM round trip
+              const int row = c * lb.rows + r;
+              if (row >= lb.BH) break;
+              const bool two = r + 1 < lb.rows && row + 1 < lb.BH;
+              float v[2][8 * MAX_CB];
 #pragma unroll
               for (int cb = 0; cb < MAX_CB; ++cb)
-                if (cb < lb.ncb && lane < 16 && (rr == 0 || two)) {
-                  float* d = rb + rr * ROWBUF_PITCH + 8 * cb;
-                  *reinterpret_cast<float4*>(d) = make_float4(v[rr][8 * cb], v[rr][8 * cb + 1], v[rr][8 * cb + 2], v[rr][8 * cb + 3]);
-                  *reinterpret_cast<float4*>(d + 4) = make_float4(v[rr][8 * cb + 4], v[rr][8 * cb + 5], v[rr][8 * cb + 6], v[rr][8 * cb + 7]);
+                if (cb < lb.ncb) {
+                  tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + r * 8), v[0] + 8 * cb);
+                  if (two) tmem_ld_32x8(taddr + (uint32_t)(cb * lb.rows * 8 + (r + 1) * 8), v[1] + 8 * cb);
                 }
+              tmem_ld_wait();
+              // the rows go to this thread's row buffer (16-byte stores, static register indices); the <= 2r+2 cells
+              // of the thread's own window are then copied out at a dynamic shared-memory offset
 #pragma unroll
-            for (int rr = 0; rr < 2; ++rr) {
-              const int wr = row + rr - oy;
-              if (haswin && (rr == 0 || two) && (unsigned)wr < (unsigned)FP) {
-                float* Fr = Fq + wr * FP;
-                const float* src = rb + rr * ROWBUF_PITCH + ox;
+              for (int rr = 0; rr < 2; ++rr)
 #pragma unroll
-                for (int wc = 0; wc < FP; ++wc) Fr[wc] = src[wc];
+                for (int cb = 0; cb < MAX_CB; ++cb)
+                  if (cb < lb.ncb && owner && (rr == 0 || two)) {
+                    float* d = rb + rr * ROWBUF_PITCH + 8 * cb;
+                    *reinterpret_cast<float4*>(d) = make_float4(v[rr][8 * cb], v[rr][8 * cb + 1], v[rr][8 * cb + 2], v[rr][8 * cb + 3]);
+                    *reinterpret_cast<float4*>(d + 4) = make_float4(v[rr][8 * cb + 4], v[rr][8 * cb + 5], v[rr][8 * cb + 6], v[rr][8 * cb + 7]);
+                  }
+#pragma unroll
+              for (int rr = 0; rr < 2; ++rr) {
+                const int wr = row + rr - oy;
+                if (haswin && (rr == 0 || two) && (unsigned)wr < (unsigned)FP) {
+                  float* Fr = Fq + wr * FP;
+                  const float* src = rb + rr * ROWBUF_PITCH + ox;
+#pragma unroll
+                  for (int wc = 0; wc < FP; ++wc) Fr[wc] = src[wc];
+                }
               }
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
           }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&acc_empty[buf]);
-        }
-      } else {
-        // scalar path: the windows of this patch do not fit one box at this level (rough flow)
-        const int t = threadIdx.x, qi = t >> 1, sub = t & 1;
-        const QInfo qi_info = qinfo[l * TQ + qi];
-        const bool n_ok = (qi_info.flags & 2) != 0;
-        const int qy = tyi * 8 + (qi >> 3), qx = txi * 8 + (qi & 7);
-        const long long qq = (long long)b * p.nq + (long long)qy * p.w_q + qx;
-        const int lh = l == 0 ? p.lh[0] : l == 1 ? p.lh[1] : l == 2 ? p.lh[2] : p.lh[3];
-        const int lw = l == 0 ? p.lw[0] : l == 1 ? p.lw[1] : l == 2 ? p.lw[2] : p.lw[3];
-        const float* f2l = l == 0 ? p.f2[0] : l == 1 ? p.f2[1] : l == 2 ? p.f2[2] : p.f2[3];
-        const float* f1q = p.f1 + (n_ok ? qq : 0) * p.D;
-        const float* f2b = f2l + (long long)b * lh * lw * p.D;
+        } else {
+          // scalar path: the windows of this patch do not fit one box at this level (rough flow)
+          const int t = threadIdx.x, qj = t >> 1, sub = t & 1;
+          const QInfo qs = nf.qinfo[l][qj];
+          const bool n_ok = (qs.flags & 2) != 0;
+          const long long qq = nf.qidx[qj];
+          const int lh = l == 0 ? p.lh[0] : l == 1 ? p.lh[1] : l == 2 ? p.lh[2] : p.lh[3];
+          const int lw = l == 0 ? p.lw[0] : l == 1 ? p.lw[1] : l == 2 ? p.lw[2] : p.lw[3];
+          const float* f2l = l == 0 ? p.f2[0] : l == 1 ? p.f2[1] : l == 2 ? p.f2[2] : p.f2[3];
+          const float* f1q = p.f1 + (n_ok ? qq : 0) * p.D;
+          const float* f2b = f2l + (long long)it.b * lh * lw * p.D;
 #pragma unroll 1
-        for (int i = 0; i < NCELL / 2; ++i) {
-          const int e = sub + 2 * i;
-          const int ry = e / FP, rx = e - ry * FP;
-          const int gy = qi_info.by + ry, gx = qi_info.bx + rx;
-          float s = 0.0f;
-          if (n_ok && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) {
-            const float4* cp = reinterpret_cast<const float4*>(f2b + ((long long)gy * lw + gx) * p.D);
-            const float4* ap = reinterpret_cast<const float4*>(f1q);
-            for (int k = 0; k < p.D / 4; ++k) {
-              const float4 vv = __ldg(cp + k), a = __ldg(ap + k);
-              s = fmaf(a.x, vv.x, s);
-              s = fmaf(a.y, vv.y, s);
-              s = fmaf(a.z, vv.z, s);
-              s = fmaf(a.w, vv.w, s);
+          for (int e = sub; e < NCELL; e += 2) {
+            const int ry = e / FP, rx = e - ry * FP;
+            const int gy = qs.by + ry, gx = qs.bx + rx;
+            float sacc = 0.0f;
+            if (n_ok && (unsigned)gy < (unsigned)lh && (unsigned)gx < (unsigned)lw) {
+              const float4* cp = reinterpret_cast<const float4*>(f2b + ((long long)gy * lw + gx) * p.D);
+              const float4* ap = reinterpret_cast<const float4*>(f1q);
+              for (int k = 0; k < p.D / 4; ++k) {
+                const float4 vv = __ldg(cp + k), a = __ldg(ap + k);
+                sacc = fmaf(a.x, vv.x, sacc);
+                sacc = fmaf(a.y, vv.y, sacc);
+                sacc = fmaf(a.z, vv.z, sacc);
+                sacc = fmaf(a.w, vv.w, sacc);
+              }
             }
+            Fl[qj * NCELL + e] = sacc * p.inv_sqrt_d;
           }
-          Fl[qi * NCELL + e] = s * p.inv_sqrt_d;
         }
+        __threadfence_block();
+        asm volatile("bar.arrive %0, 256;" ::"r"(2 + fb) : "memory");  // every footprint of the patch at this level is complete
       }
-      __threadfence_block();
-      asm volatile("bar.arrive %0, 256;" ::"r"(2 + fb) : "memory");  // every footprint of the patch at this level is complete
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&info_empty[j & 1]);
     }
   } else {
     // ===================== tap warps 4-7: warp 4 + k evaluates the 16 queries of lane quarter k =====================
     // (under the extraction of the next level and the MMAs of the one after)
     const int C = p.L * S * S;
-    for (int l = l_begin; l < l_end; ++l) {
-      const int fb = (l - l_begin) & 1;
-      asm volatile("bar.sync %0, 256;" ::"r"(2 + fb) : "memory");
-      column_taps_level<R>(F + fb * TQ * NCELL + 16 * quarter * NCELL, cx, cy, qvalid, q, l, p.out, C, lane);
-      if (l + 2 < l_end) asm volatile("bar.arrive %0, 256;" ::"r"(4 + fb) : "memory");
+    int lv = 0, j = 0;
+    for (long long i = blockIdx.x; i < nitems; i += gridDim.x, ++j) {
+      const Item it = decode_item(p, i, tiles_x, tiles_y);
+      const ItemInfo& nf = info[j & 1];
+      mbar_wait(&info_full[j & 1], (uint32_t)((j >> 1) & 1));
+      const int m = 16 * quarter + (lane & 15);
+      const float2 cc = nf.coord[m];
+      const bool qvalid = lane < 16 && nf.valid[m] != 0;
+      const long long q = nf.qidx[m];
+      for (int l = it.l_begin; l < it.l_end; ++l, ++lv) {
+        const int fb = lv & 1;
+        asm volatile("bar.sync %0, 256;" ::"r"(2 + fb) : "memory");
+        column_taps_level<R>(F + fb * TQ * NCELL + 16 * quarter * NCELL, cc.x, cc.y, qvalid, q, l, p.out, C, lane);
+        if (lv + 2 < my_levels) asm volatile("bar.arrive %0, 256;" ::"r"(4 + fb) : "memory");
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&info_empty[j & 1]);
     }
   }
 
@@ -611,8 +692,8 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   p.inv_sqrt_d = 1.0f / (float)sqrt((double)D);
   const int FP = 2 * radius + 2;
   const size_t smem = 1024 + (size_t)2 * (D / 64) * A_BLOCK_BYTES + (size_t)RING_BYTES +
-                      (size_t)2 * TQ * FP * FP * sizeof(float) + (size_t)4 * 16 * 2 * ROWBUF_PITCH * sizeof(float) + 256 + 320 +
-                      4 * sizeof(LevelBox) + 4 * TQ * sizeof(QInfo);
+                      (size_t)2 * TQ * FP * FP * sizeof(float) + (size_t)4 * 16 * 2 * ROWBUF_PITCH * sizeof(float) + 320 +
+                      2 * sizeof(ItemInfo);
   if (smem > (size_t)SMEM_LIMIT) return RAFTK_ERR_UNSUPPORTED;
   const long long nblk = (long long)B * ((rows_q + 7) / 8) * ((w + 7) / 8);
   if (nblk > 0x7fffffffLL) return RAFTK_ERR_SHAPE;
@@ -632,6 +713,8 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   auto kernel = radius == 4 ? altcorr_tc_kernel<4> : altcorr_tc_kernel<3>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  kernel<<<(unsigned)ncta, NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB[0], tmB[1], tmB[2], tmB[3], p);
+  // persistent: one CTA per SM at most, each walking the work items blockIdx.x, blockIdx.x + gridDim.x, ...
+  const long long grid = ncta < (long long)sm_count() ? ncta : (long long)sm_count();
+  kernel<<<(unsigned)grid, NUM_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB[0], tmB[1], tmB[2], tmB[3], p);
   return launch_status();
 }
