@@ -66,8 +66,8 @@ constexpr int MAX_STAGES = 8;
 constexpr int A_BLOCK_BYTES = TQ * 128;
 constexpr int ACC_COLS = MAX_CB * MAX_ROWS * 8;  // 192 accumulator columns per buffer
 constexpr int EPI_WARPS = 8;                    // warps 0-3: window extraction (TMEM lane quarter = warp); warps 4-7: taps of quarter warp - 4
-constexpr int PRODUCER_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1;
-constexpr int NUM_THREADS = (EPI_WARPS + 2) * 32;
+constexpr int PRODUCER_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1, AUX_WARP = EPI_WARPS + 2;
+constexpr int NUM_THREADS = (EPI_WARPS + 3) * 32;  // + B producer, MMA issuer, item-description / A-tile producer
 constexpr int SMEM_LIMIT = 232448;
 
 struct Params {
@@ -253,7 +253,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_empty[i], 4);  // one arrival per extraction warp
       mbar_init(&info_full[i], 1);
-      mbar_init(&info_empty[i], 9);
+      mbar_init(&info_empty[i], 10);  // B producer, MMA issuer, 4 extraction warps, 4 tap warps
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -267,14 +267,11 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const uint32_t tmem_base = *tmem_slot;
   const int quarter = warp & 3;
 
-  if (warp == PRODUCER_WARP) {
-    // ===================== producer: item descriptions, the A tile, the B ring =====================
-    // (the whole warp walks the loops, one elected lane issues: tc_ptx.cuh)
-    // B ring bookkeeping: every slot has its own full / empty barrier; `used`: the slot holds a stage whose release
-    // has not been awaited yet, `epar`: phase bit of its empty barrier.  Consecutive items almost always share the
-    // ring geometry; when it changes the ring is drained first.
-    int cur = 0, j = 0, sbytes = 0, nst = 1;
-    uint32_t used = 0, epar = 0;
+  if (warp == AUX_WARP) {
+    // ===================== item descriptions and the A tile, one item ahead of everybody else =====================
+    // (a warp of its own: the B producer below must not stop streaming while this one waits for global loads or for
+    // the previous item to release the A tile; the whole warp walks the loops, one elected lane issues: tc_ptx.cuh)
+    int j = 0;
     for (long long i = blockIdx.x; i < nitems; i += gridDim.x, ++j) {
       const Item it = decode_item(p, i, tiles_x, tiles_y);
       ItemInfo& nf = info[j & 1];
@@ -354,6 +351,18 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
         __syncwarp();
       }
+    }
+  } else if (warp == PRODUCER_WARP) {
+    // ===================== B producer: the ring of (chunk, k-block, hi | mid) slabs =====================
+    // Every slot has its own full / empty barrier; `used`: the slot holds a stage whose release has not been awaited
+    // yet, `epar`: phase bit of its empty barrier.  Consecutive items almost always share the ring geometry; when it
+    // changes the ring is drained first.
+    int cur = 0, j = 0, sbytes = 0, nst = 1;
+    uint32_t used = 0, epar = 0;
+    for (long long i = blockIdx.x; i < nitems; i += gridDim.x, ++j) {
+      const Item it = decode_item(p, i, tiles_x, tiles_y);
+      const ItemInfo& nf = info[j & 1];
+      mbar_wait(&info_full[j & 1], (uint32_t)((j >> 1) & 1));
       // ---- the B ring: one (chunk, k-block, hi | mid) slab per stage ----
       {
         const int sb = item_stage_bytes(nf, it);
@@ -393,6 +402,8 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               if (++cur == nst) cur = 0;
             }
       }
+      if (elect_one()) mbar_arrive(&info_empty[j & 1]);
+      __syncwarp();
     }
   } else if (warp == MMA_WARP) {
     // ===================== MMA issuer: the whole warp walks the loops, one elected lane issues =====================
