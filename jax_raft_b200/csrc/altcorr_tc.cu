@@ -3,9 +3,10 @@
 //   pool_l(f1 . f2^T)[q, Y, X] = f1[q] . pool_l(f2)[Y, X]
 // the taps of level l (model.py:448-470) are bilinear samples of dot products against fmap2 pooled l times.
 //
-// One CTA = one 8 x 8 patch of query pixels, all levels in turn (UMMA M = 64, cta_group::1).  Neighbouring windows
-// overlap, so per level the CTA computes the correlations of its 64 queries with every cell of the BOUNDING BOX of
-// their (2r+2)^2 windows — a (64 x box cells x D) GEMM — and each query then picks its own window out of the box:
+// One work item = one 8 x 8 patch of query pixels, all levels in turn (UMMA M = 64, cta_group::1); the CTAs are
+// persistent and walk the items.  Neighbouring windows overlap, so per level the CTA computes the correlations of its
+// 64 queries with every cell of the BOUNDING BOX of their (2r+2)^2 windows — a (64 x box cells x D) GEMM — and each
+// query then picks its own window out of the box:
 //
 //   operands   bf16 [hi | mid] splits of fmap1 (scaled by 1/sqrt(D)) and of every pooled fmap2 level, written once
 //              per pair by raftk_altcorr_split; products hi*hi + mid*hi + hi*mid in float32 (the scheme of the
@@ -33,14 +34,21 @@
 // that do not fit (rough flow: wider than 32 cells or taller than 6 chunks) take a scalar fp32 path inside the same
 // kernel (sequential fma chain over D, as altcorr.cu), slower and ~2e-5 away from the split product.
 //
-// Measured, 136 x 240, r = 4, D = 256, smooth +-8 px flow (profiles/altcorr_time.py): 128 us per iteration against
-// 560 us for the float32 FMA kernel (altcorr.cu).  510 CTAs = 3.45 waves.  History and phase elimination: DESIGN.md
-// §4.4.  The last 25 us came from the ISSUE path: with `if (lane == 0)` around the MMA / TMA loops the compiler wraps
-// every tcgen05.mma in a vote-and-broadcast loop (~23 instructions of the one issuing thread per ~60-cycle MMA); the
-// loops now run warp-uniformly and issue under elect.sync, four MMAs per asm statement (tc_ptx.cuh).  What would move
-// it further: M = 128 (a CTA pair over a 16 x 8 patch sharing one box: full tensor rate and 1/3 less box traffic; the
-// 128 KB A tile + 51 KB of footprints leave no room for it in one CTA), and persistent CTAs that fetch the next
-// patch's coordinates and A tile under the current patch's MMAs.
+//   items      warp 10 describes item j + 1 (coordinates, window origins, per-level boxes: two info slots) and
+//              fetches its A tile k-block by k-block as the last chunk of item j releases it (a_empty barriers), so
+//              the B producer (warp 8) never stops streaming and the MMAs of item j + 1 follow those of item j;
+//              B ring, accumulators, footprint buffers and barrier phases carry over item boundaries.  Whole waves
+//              of patches are one item each; the patches of a last, partial wave are (patch, level) items.
+//
+// Measured, 136 x 240, r = 4, D = 256, smooth +-8 px flow (profiles/altcorr_time.py): 114 us per iteration against
+// 560 us for the float32 FMA kernel (altcorr.cu).  History and phase elimination: DESIGN.md §4.4.  Two lessons:
+// (1) the ISSUE path — with `if (lane == 0)` around the MMA / TMA loops the compiler wraps every tcgen05.mma in a
+// vote-and-broadcast loop (~23 instructions of the one issuing thread per ~60-cycle MMA); the loops now run
+// warp-uniformly and issue under elect.sync, four MMAs per asm statement (tc_ptx.cuh): 171 -> 137 us; (2) per-item
+// fixed cost (set-up 5.7 us before the first accumulator, 4.6 us of tail after the last MMA, of ~32 us) — persistent
+// CTAs with the next item prepared one ahead: 128 -> 114 us.  What would move it further: M = 128 (a CTA pair over a
+// 16 x 8 patch sharing one box: full tensor rate and 1/3 less box traffic; the 128 KB A tile + 51 KB of footprints
+// leave no room for it in one CTA).
 
 #include <cuda.h>
 #include <cuda_bf16.h>
