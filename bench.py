@@ -573,6 +573,52 @@ def config4_rowshard(torch, dist, J, dev, rank, world, iters=ITERS):
         torch.cuda.synchronize(dev)
         gather.append(sync_max(torch, dist, world, dev, a.elapsed_time(b_)))
         pool.append(sync_max(torch, dist, world, dev, b_.elapsed_time(c)))
+    # the same exchange as ONE kernel over peer memory (sharding.PeerRowGather: gathered map + level-0 operand split),
+    # beside its two-step equivalent (NCCL all-gather, then raftk_altcorr_split of level 0)
+    peer_res = {}
+    try:
+        from jax_raft_b200 import _lib as _rl
+
+        lib = _rl.load()
+        pg = sharding.RowShardedCorr(J.AltCorrBlock(4, r), exchange="peer").peer_gather(B, h, w, D, dev)
+        pg.band.copy_(f2_rows)
+        ref_split = torch.empty((B, h, w, 2 * D), dtype=torch.bfloat16, device=dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        for _ in range(2):
+            full_p, split_p = pg.gather()
+        fused, two_step = [], []
+        reps = 10  # back-to-back calls per timing: one call alone is mostly launch latency
+        for _ in range(3):
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+            a, b_, c = ev(), ev(), ev()
+            a.record()
+            for _ in range(reps):
+                full_p, split_p = pg.gather()
+            b_.record()
+            for _ in range(reps):
+                full_n = sharding.all_gather_rows(f2_rows, h)
+                lib.raftk_altcorr_split(full_n.data_ptr(), ref_split.data_ptr(), B * h * w, D, 1.0, stream)
+            c.record()
+            torch.cuda.synchronize(dev)
+            fused.append(sync_max(torch, dist, world, dev, a.elapsed_time(b_) / reps))
+            two_step.append(sync_max(torch, dist, world, dev, b_.elapsed_time(c) / reps))
+        same = (bool(torch.equal(full_p, f2)) and bool(torch.equal(split_p.view(torch.int16), ref_split.view(torch.int16)))
+                and not pg.timed_out())
+        okp = torch.tensor([1.0 if same else 0.0], device=dev)
+        dist.all_reduce(okp, op=dist.ReduceOp.MIN)
+        remote = int(f2.numel() * 4) - int(f2_rows.numel() * 4)
+        peer_res = {
+            "kernel": "raftk_gather_rows_split (plain 16-byte loads from each rank's band in symmetric memory; writes fmap2 and its bf16 [hi|mid] split; ranks synchronise inside the kernel through flags over peer memory)",
+            "fused_gather_split_ms": min(fused), "fused_gather_split_ms_runs": fused,
+            "nccl_all_gather_plus_split_ms": min(two_step), "nccl_all_gather_plus_split_ms_runs": two_step,
+            "remote_bytes_read_per_rank": remote, "nvlink_read_gbs_per_rank": remote / (min(fused) * 1e-3) / 1e9,
+            "bit_equal_to_two_step": bool(okp.item() > 0),
+            "timing": "CUDA events around 10 back-to-back calls, per call, max over ranks, best of 3; the fused figure includes its synchronisation",
+        }
+        del full_p, split_p, full_n, ref_split
+    except Exception as exc:  # symmetric memory not available on this box: the NCCL exchange above stands
+        peer_res = {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
     lk = []
     for _ in range(iters):
         s, e = ev(), ev()
@@ -599,6 +645,7 @@ def config4_rowshard(torch, dist, J, dev, rank, world, iters=ITERS):
         "all_gather_fmap2_ms": gather_ms, "all_gather_fmap2_ms_runs": gather, "all_gather_bytes_total": total_bytes,
         "all_gather_bus_gbs": total_bytes * (world - 1) / world / (gather_ms * 1e-3) / 1e9,
         "nccl_bus_reference_gbs": NCCL_BUS_REFERENCE_GBS,
+        "peer_exchange": peer_res,
         "pool_fmap2_ms": min(pool), "altcorr_lookup_ms_per_iter": lookup_ms, "iters_timed": iters,
         "altcorr_tflops_per_rank": 2.0 * nq * 4 * (2 * r + 2) ** 2 * D / (lookup_ms * 1e-3) / 1e12,
         "band_matches_volume_path": bool(ok.item() > 0), "max_abs_err_per_rank": errs, "corr_scale": scale,

@@ -228,6 +228,32 @@ int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f2_levels, c
                             const void* const* f2_split, int num_levels, const float* coords, float* out,
                             int B, int nq, int h, int w, int D, int radius, void* stream);
 
+/* Query-row sharding (BASELINE.json config 4; no reference counterpart, the reference is single-device):
+ * the one exchange of the path — every rank needs all of fmap2 — fused with the level-0 operand split.
+ *   bands      HOST array of `world` DEVICE pointers: bands[g] = rank g's rows
+ *              [row_start[g], row_start[g+1]) of fmap2, (B, rows_g, w, D) float32, 16-byte aligned;
+ *              peer pointers (symmetric memory / IPC mappings) for g != this rank.  Read with plain
+ *              16-byte loads, each element once.
+ *   sync_flags NULL, or a HOST array of `world` DEVICE pointers to RAFTK_GATHER_SYNC_BYTES bytes each,
+ *              16-byte aligned, zeroed once before the first call, sync_flags[g] living on rank g and
+ *              peer-mapped like bands[g]; the same blocks on every call.
+ *   rank       this rank (0 <= rank < world); also where the round-robin walk over the bands starts
+ *   row_start  HOST array of world + 1 ints, row_start[0] = 0, row_start[world] = h, non-decreasing
+ *   full       device (local), (B, h, w, D) float32: the gathered map
+ *   split_bf16 device (local), (B, h, w, 2D) bf16 [hi | mid] (the f2_split[0] of raftk_altcorr_lookup_tc),
+ *              or NULL to gather only
+ * world <= 8, D % 4 == 0.  Synchronisation of the ranks — every band complete before it is read, no band
+ * overwritten until every rank has read it:
+ *   sync_flags == NULL  the caller's, around the launch;
+ *   sync_flags given    inside the kernel (flags over peer memory, see csrc/gather_split.cu): when the
+ *                       launch has completed on this rank's stream the results are in place AND every
+ *                       peer has finished reading this rank's band.  All ranks must make the same
+ *                       sequence of calls.  Waits give up after a few seconds and set word 18 of this
+ *                       rank's block (uint32, sticky) instead of hanging. */
+#define RAFTK_GATHER_SYNC_BYTES 256
+int raftk_gather_rows_split(const float* const* bands, void* const* sync_flags, int rank, const int* row_start,
+                            int world, float* full, void* split_bf16, int B, int h, int w, int D, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Kernel family 3 — convex 8x flow upsampling.
  * Replaces the up_mask branch of upsample_flow, model.py:85-98.

@@ -53,6 +53,10 @@ SIGNATURES = {
         [c_void_p, _FloatPtrArray, c_void_p, _FloatPtrArray, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
          c_int, c_void_p],
     ),
+    "raftk_gather_rows_split": (
+        c_int,
+        [_FloatPtrArray, _FloatPtrArray, c_int, ctypes.POINTER(c_int), c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
+    ),
     "raftk_bias_act_nhwc": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_int, c_void_p]),
     "raftk_instance_norm_scratch_bytes": (c_size_t, [c_int, c_int]),
     "raftk_instance_norm_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_size_t, c_void_p]),

@@ -375,7 +375,9 @@ class AltCorrBlock:
         return self.kernel == "tc" and self.num_levels <= 4 and self.radius in (3, 4) and d % 64 == 0 and d <= 256
 
     def build_pyramid(self, fmap1: torch.Tensor, fmap2: torch.Tensor,
-                      query_rows: Optional[Tuple[int, int]] = None):
+                      query_rows: Optional[Tuple[int, int]] = None, f2_split0: Optional[torch.Tensor] = None):
+        """``f2_split0``: the bf16 [hi | mid] split of ``fmap2`` (B, h, w, 2D) when the caller already has it
+        (sharding.PeerRowGather writes it while gathering); otherwise it is made here."""
         fmap1, fmap2 = _check_fmaps(fmap1, fmap2, self.num_levels, query_rows)
         b, h, w, d = fmap2.shape
         f2_levels = [fmap2] + [
@@ -393,10 +395,15 @@ class AltCorrBlock:
             # bf16 [hi | mid] operands of the tensor-core lookup, once per pair (1/sqrt(D) rides on fmap1)
             f1_split = torch.empty(tuple(fmap1.shape[:-1]) + (2 * d,), dtype=torch.bfloat16, device=fmap1.device)
             f2_split = [torch.empty(tuple(t.shape[:-1]) + (2 * d,), dtype=torch.bfloat16, device=t.device) for t in f2_levels]
-            for src, dst, scale in [(fmap1, f1_split, float(d) ** -0.5)] + [(s_, d_, 1.0) for s_, d_ in zip(f2_levels, f2_split)]:
+            todo = [(fmap1, f1_split, float(d) ** -0.5)] + [(s_, d_, 1.0) for s_, d_ in zip(f2_levels, f2_split)]
+            if f2_split0 is not None:
+                assert f2_split0.dtype == torch.bfloat16 and f2_split0.is_contiguous() and tuple(f2_split0.shape) == (b, h, w, 2 * d)
+                f2_split[0] = f2_split0
+                del todo[1]
+            for src, dst, scale in todo:
                 rc = lib.raftk_altcorr_split(src.data_ptr(), dst.data_ptr(), src.numel() // d, d, scale, stream)
                 _lib.check("raftk_altcorr_split", rc)
-            _lib.count_launch(1 + self.num_levels)
+            _lib.count_launch(len(todo))
         return (fmap1, f2_levels, f1_split, f2_split)
 
     def index_pyramid(self, corr_pyramid, centroids_coords: torch.Tensor) -> torch.Tensor:
