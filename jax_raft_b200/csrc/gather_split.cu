@@ -89,7 +89,8 @@ constexpr int kBlocksPerSM = 4;                  // 64 KB of loads in flight per
 // Work item = (row slot, segment of kSegment float4 of that image row); row slots enumerate (b, band, row in band)
 // with the band fastest.  The loads of an item are all issued before its first store; a software pipeline over items
 // (next item's loads before this item's stores) changed nothing — the remote side runs at what plain loads pull over
-// NVLink (~480 GB/s measured on 2 GPUs), not at a latency the loop exposes.
+// NVLink (~480 GB/s measured on 2 GPUs, ~530 GB/s per rank on 8), not at a latency the loop exposes; 32-byte loads
+// (LDG.256, three per thread) gave the same 36 us, so the request count is not what bounds it either.
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM) gather_split_kernel(const Params p, const SyncParams sp) {
   __shared__ int s_last;
   __shared__ const float* s_band[kMaxRanks];  // dynamically indexed: shared memory, not a local copy of the parameters
