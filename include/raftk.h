@@ -358,6 +358,13 @@ int raftk_flow_update(const float* delta_pre, int ld_delta, const float* bias, c
  * synchronised: set it before launching. */
 int raftk_set_pdl(int on);
 
+/* Which kernel raftk_altcorr_lookup_tc launches (no counterpart in the reference): 0 = by problem size
+ * (default, or RAFTK_ALTCORR_MODE in the environment), 1 = 8 x 8 query patches, UMMA M = 64, A tile in shared
+ * memory (csrc/altcorr_tc.cu), 2 = 16 x 8 patches, UMMA M = 128, A operand in tensor memory
+ * (csrc/altcorr_tc128.cu).  Same results contract either way (values agree to the split-product error,
+ * ~2e-5).  Returns the previous setting; other values only query it.  Process-wide, not synchronised. */
+int raftk_set_altcorr_mode(int mode);
+
 #ifdef __cplusplus
 }
 #endif

@@ -70,6 +70,7 @@ SIGNATURES = {
     "raftk_lookup_conv_weight_cols": (c_int, [c_int, c_int]),
     "raftk_corr_lookup_conv1x1": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_set_pdl": (c_int, [c_int]),
+    "raftk_set_altcorr_mode": (c_int, [c_int]),
     "raftk_mask_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "raftk_corr_lookup_update": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                          c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

@@ -53,8 +53,10 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <cstdlib>
 #include <cstring>
 
+#include "altcorr_tc128.cuh"
 #include "lookup_taps.cuh"
 #include "raftk_common.cuh"
 #include "tc_ptx.cuh"
@@ -642,6 +644,23 @@ static int encode_4d(EncodeTiledFn encode, CUtensorMap* tm, const void* base, in
 }  // namespace atc
 }  // namespace raftk
 
+namespace raftk {
+int& altcorr_mode_flag() {
+  static int flag = [] {
+    const char* e = getenv("RAFTK_ALTCORR_MODE");
+    return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 0;
+  }();
+  return flag;
+}
+}  // namespace raftk
+
+extern "C" int raftk_set_altcorr_mode(int mode) {
+  int& f = raftk::altcorr_mode_flag();
+  const int prev = f;
+  if (mode >= 0 && mode <= 2) f = mode;
+  return prev;
+}
+
 extern "C" int raftk_altcorr_split(const float* src, void* dst, long long rows, int D, float scale, void* stream) {
   using namespace raftk;
   if (rows < 0 || D <= 0) return RAFTK_ERR_SHAPE;
@@ -669,6 +688,19 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
   if ((long long)B * nq == 0) return RAFTK_OK;
   if (!fmap1 || !f2_levels || !f1_split || !f2_split || !coords || !out) return RAFTK_ERR_NULL;
   if (((uintptr_t)fmap1 & 15) || ((uintptr_t)f1_split & 15)) return RAFTK_ERR_ALIGN;
+  for (int l = 0; l < num_levels; ++l) {
+    if (!f2_levels[l] || !f2_split[l]) return RAFTK_ERR_NULL;
+    if (((uintptr_t)f2_levels[l] & 15) || ((uintptr_t)f2_split[l] & 15)) return RAFTK_ERR_ALIGN;
+  }
+  {
+    // which tensor-core kernel: the M = 128 / A-in-TMEM form (altcorr_tc128.cu) pays once its 16 x 8 patches fill the
+    // SMs (measured: 111 vs 115 us at 136 x 240, 70.5 vs 71 at 68 x 240, 49 vs 46 at 34 x 240); below that the 8 x 8
+    // patches of this file's kernel spread a small problem over more CTAs
+    const int mode = altcorr_mode_flag();
+    const long long patches128 = (long long)B * ((nq / w + 7) / 8) * ((w + 15) / 16);
+    if (mode == 2 || (mode == 0 && patches128 >= (long long)sm_count()))
+      return altcorr_tc128_launch(fmap1, f2_levels, f1_split, f2_split, num_levels, coords, out, B, nq, h, w, D, radius, stream);
+  }
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return RAFTK_ERR_UNSUPPORTED;
   Params p{};
