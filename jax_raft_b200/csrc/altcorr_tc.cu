@@ -46,9 +46,10 @@
 // vote-and-broadcast loop (~23 instructions of the one issuing thread per ~60-cycle MMA); the loops now run
 // warp-uniformly and issue under elect.sync, four MMAs per asm statement (tc_ptx.cuh): 171 -> 137 us; (2) per-item
 // fixed cost (set-up 5.7 us before the first accumulator, 4.6 us of tail after the last MMA, of ~32 us) — persistent
-// CTAs with the next item prepared one ahead: 128 -> 114 us.  What would move it further: M = 128 (a CTA pair over a
-// 16 x 8 patch sharing one box: full tensor rate and 1/3 less box traffic; the 128 KB A tile + 51 KB of footprints
-// leave no room for it in one CTA).
+// CTAs with the next item prepared one ahead: 128 -> 114 us.  A second kernel with UMMA M = 128 and the A operand in
+// tensor memory (altcorr_tc128.cu) is chosen for calls whose 16 x 8 patches fill the SMs (raftk_set_altcorr_mode);
+// the phase elimination behind that split — three quarters of this kernel's time is the stage pipeline between the
+// B producer and the MMA issuer, not the tensor pipe — is in DESIGN.md §4.4.
 
 #include <cuda.h>
 #include <cuda_bf16.h>
