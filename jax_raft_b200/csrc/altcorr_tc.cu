@@ -694,12 +694,12 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
     if (((uintptr_t)f2_levels[l] & 15) || ((uintptr_t)f2_split[l] & 15)) return RAFTK_ERR_ALIGN;
   }
   {
-    // which tensor-core kernel: the M = 128 / A-in-TMEM form (altcorr_tc128.cu) pays once its 16 x 8 patches fill the
-    // SMs (measured: 111 vs 115 us at 136 x 240, 70.5 vs 71 at 68 x 240, 49 vs 46 at 34 x 240); below that the 8 x 8
-    // patches of this file's kernel spread a small problem over more CTAs
+    // which tensor-core kernel: the M = 128 / A-in-TMEM form (altcorr_tc128.cu) wins once its 16 x 8 patches give the
+    // SMs enough to do (bands of a 136 x 240 image, M = 128 against M = 64: 136 rows 96 vs 114 us, 68 rows 59 vs 69,
+    // 34 rows 41 vs 45, 17 rows 34 vs 31); below that the 8 x 8 patches of this file's kernel spread the work wider
     const int mode = altcorr_mode_flag();
     const long long patches128 = (long long)B * ((nq / w + 7) / 8) * ((w + 15) / 16);
-    if (mode == 2 || (mode == 0 && patches128 >= (long long)sm_count()))
+    if (mode == 2 || (mode == 0 && 5 * patches128 >= 2 * (long long)sm_count()))
       return altcorr_tc128_launch(fmap1, f2_levels, f1_split, f2_split, num_levels, coords, out, B, nq, h, w, D, radius, stream);
   }
   EncodeTiledFn encode = get_encode_fn();

@@ -34,9 +34,11 @@ namespace atc128 {
 using namespace raftk::ptx;
 
 constexpr int TQ = 128, PW = 16, PH = 8;        // queries per item: 16 x 8
-constexpr int ROWS = 4;                         // box rows per chunk (the y extent of every level's TMA box)
+// box rows per chunk = the y extent of the TMA box, by box width in column blocks: as tall as N = 8 * ncb * rows <= 128
+// allows (N = 64, 128, 120, 128), so that the narrow boxes of the coarse levels need half as many chunks and stages
+__host__ __device__ constexpr int rows_for(int ncb) { return ncb >= 4 ? 4 : ncb == 3 ? 5 : 8; }
+constexpr int MAX_BOX_ROWS = 32;                // box height the tensor-core path takes
 constexpr int MAX_CB = 4;                       // column blocks of 8 cells: box width <= 32, N = 32 * ncb <= 128
-constexpr int MAX_CHUNKS = 8;                   // box height <= 32
 constexpr int RING_BYTES = 80 * 1024;           // B ring: stages of ncb * 4 KB
 constexpr int NINFO = 4;                        // item descriptions in flight (the describing warp runs NINFO - 1 items ahead)
 constexpr int NF = 2;                           // footprint buffers (levels in flight between extraction and taps)
@@ -177,7 +179,7 @@ __device__ __forceinline__ Item decode_item(const Params& p, long long i, int ti
 __device__ __forceinline__ int item_stage_bytes(const ItemInfo& nf, const Item& it) {
   int sb = 4 * 1024;
   for (int l = it.l_begin; l < it.l_end; ++l)
-    for (int bi = 0; bi < nf.nbox[l]; ++bi) sb = max(sb, nf.lbox[l][bi].ncb * ROWS * 1024);
+    for (int bi = 0; bi < nf.nbox[l]; ++bi) sb = max(sb, nf.lbox[l][bi].ncb * rows_for(nf.lbox[l][bi].ncb) * 1024);
   return sb;
 }
 
@@ -324,9 +326,9 @@ altcorr_tc128_kernel(const __grid_constant__ BMaps tmB, const Params p) {
           lb.Y0 = any_ ? mny_ : 0;
           lb.BW = any_ ? mxx_ - mnx_ + FP : 0;
           lb.BH = any_ ? mxy_ - mny_ + FP : 0;
-          lb.tc = (lb.BW <= 8 * MAX_CB && lb.BH <= ROWS * MAX_CHUNKS) ? 1 : 0;
+          lb.tc = (lb.BW <= 8 * MAX_CB && lb.BH <= MAX_BOX_ROWS) ? 1 : 0;
           lb.ncb = (lb.BW + 7) >> 3;
-          lb.nchunks = (lb.BH + ROWS - 1) / ROWS;
+          lb.nchunks = (lb.BH + rows_for(lb.ncb) - 1) / rows_for(lb.ncb);
           lb.pad = 0;
           return lb;
         };
@@ -426,7 +428,8 @@ altcorr_tc128_kernel(const __grid_constant__ BMaps tmB, const Params p) {
         const int b_ncb = lbp->ncb, b_nchunks = lbp->nchunks, b_X0 = lbp->X0, b_Y0 = lbp->Y0;
         if (b_nchunks == 0) continue;
         const CUtensorMap* tmBl = &tmB.m[l * MAX_CB + b_ncb - 1];
-        const int cb_bytes = ROWS * 1024;
+        const int b_rows = rows_for(b_ncb);
+        const int cb_bytes = b_rows * 1024;
         for (int c = 0; c < b_nchunks; ++c)
           for (int kb = 0; kb < KB; ++kb)
             for (int part = 0; part < 2; ++part) {
@@ -438,7 +441,7 @@ altcorr_tc128_kernel(const __grid_constant__ BMaps tmB, const Params p) {
               used |= bit;
               if (elect_one()) {
                 mbar_expect_tx(&b_full[cur], (uint32_t)(b_ncb * cb_bytes));
-                tma_load_4d(tmBl, &b_full[cur], smem_b + cur * sbytes, part * p.D + kb * 64, b_X0, b_Y0 + ROWS * c, it.b);
+                tma_load_4d(tmBl, &b_full[cur], smem_b + cur * sbytes, part * p.D + kb * 64, b_X0, b_Y0 + b_rows * c, it.b);
               }
               __syncwarp();
               if (++cur == nst) cur = 0;
@@ -475,7 +478,7 @@ altcorr_tc128_kernel(const __grid_constant__ BMaps tmB, const Params p) {
       for (int bi = 0; bi < nf.nbox[l]; ++bi) {
         const int b_ncb = nf.lbox[l][bi].ncb, b_nchunks = nf.lbox[l][bi].nchunks;
         if (b_nchunks == 0) continue;
-        const uint32_t idesc = make_idesc_bf16(TQ, b_ncb * ROWS * 8);
+        const uint32_t idesc = make_idesc_bf16(TQ, b_ncb * rows_for(b_ncb) * 8);
         for (int c = 0; c < b_nchunks; ++c, ++g) {
           const int buf = g & 1;
           const bool last_chunk = more && l == last_l && bi == last_bi && c == b_nchunks - 1;
@@ -562,7 +565,7 @@ altcorr_tc128_kernel(const __grid_constant__ BMaps tmB, const Params p) {
         if (nbox > 0) {
          for (int bi = 0; bi < nbox; ++bi) {
           const LevelBox* lbp = &nf.lbox[l][bi];
-          const int b_ncb = lbp->ncb, b_nchunks = lbp->nchunks, b_BH = lbp->BH;
+          const int b_ncb = lbp->ncb, b_nchunks = lbp->nchunks, b_BH = lbp->BH, b_rows = rows_for(b_ncb);
           // with two boxes a query extracts from the box of its own half of the patch only
           const bool inbox = haswin && (nbox == 1 || ((lane >> 3) & 1) == bi);
           const int ox = qi.bx - lbp->X0, oy = qi.by - lbp->Y0;  // window origin inside the box
@@ -573,10 +576,10 @@ altcorr_tc128_kernel(const __grid_constant__ BMaps tmB, const Params p) {
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)buf * ACC_COLS;
 #pragma unroll 1
-            for (int r = 0; r < ROWS; r += 2) {  // two box rows per TMEM round trip
-              const int row = c * ROWS + r;
+            for (int r = 0; r < b_rows; r += 2) {  // two box rows per TMEM round trip
+              const int row = c * b_rows + r;
               if (row >= b_BH) break;
-              const bool two = row + 1 < b_BH;
+              const bool two = r + 1 < b_rows && row + 1 < b_BH;
               float v[2][8 * MAX_CB];
 #pragma unroll
               for (int cb = 0; cb < MAX_CB; ++cb)
@@ -707,7 +710,7 @@ int altcorr_tc128_launch(const float* fmap1, const float* const* f2_levels, cons
     p.lh[l] = h >> ll;
     p.lw[l] = w >> ll;
     for (int ncb = 1; ncb <= MAX_CB; ++ncb) {
-      const int rc = encode_4d(encode, &tmB.m[l * MAX_CB + ncb - 1], f2_split[ll], 2 * D, w >> ll, h >> ll, B, 8 * ncb, ROWS);
+      const int rc = encode_4d(encode, &tmB.m[l * MAX_CB + ncb - 1], f2_split[ll], 2 * D, w >> ll, h >> ll, B, 8 * ncb, rows_for(ncb));
       if (rc != RAFTK_OK) return rc;
     }
   }

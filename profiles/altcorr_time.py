@@ -1,6 +1,6 @@
 """alt_corr lookup at 136x240 (BASELINE config 4 on one GPU), D = 256, r = 4, smooth +-8 px flow: the tensor-core
 kernel (raftk_altcorr_lookup_tc) beside the float32 FMA kernel (raftk_altcorr_lookup); graph of 4 launches, best of 5.
-    python profiles/altcorr_time.py [h w]"""
+    python profiles/altcorr_time.py [h w [rows]]      rows: only the first `rows` query rows (a rank's band of config 4)"""
 import os
 import sys
 
@@ -11,6 +11,7 @@ import jax_raft_b200 as J  # noqa: E402
 
 dev = torch.device("cuda", 0)
 h, w = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (136, 240)
+rows = int(sys.argv[3]) if len(sys.argv) > 3 else h
 d, r, L = 256, 4, 4
 g = torch.Generator(device=dev).manual_seed(0)
 f1 = torch.randn((1, h, w, d), device=dev, generator=g) * 1.45
@@ -18,11 +19,12 @@ f2 = torch.randn((1, h, w, d), device=dev, generator=g) * 1.45
 yy, xx = torch.meshgrid(torch.arange(h, device=dev), torch.arange(w, device=dev), indexing="ij")
 flow = torch.stack([8 * torch.sin(6.28 * (xx / w + 0.3 * yy / h)), 8 * torch.cos(6.28 * (yy / h - 0.2 * xx / w))], -1)[None].float()
 coords = (J.make_coords_grid(1, h, w, device=dev) + flow).contiguous()
-flops = 2.0 * h * w * L * (2 * r + 2) ** 2 * d
+flops = 2.0 * rows * w * L * (2 * r + 2) ** 2 * d
+coords = coords[:, :rows].contiguous()
 outs = {}
 for kernel in ("simt", "tc"):
     ab = J.AltCorrBlock(L, r, kernel=kernel)
-    pyr = ab.build_pyramid(f1, f2)
+    pyr = ab.build_pyramid(f1, f2, query_rows=(0, rows))
     outs[kernel] = ab.index_pyramid(pyr, coords)
     torch.cuda.synchronize()
     graph = torch.cuda.CUDAGraph()
@@ -44,7 +46,7 @@ for kernel in ("simt", "tc"):
     pyr = ab.build_pyramid(f1, f2)
     e1.record()
     torch.cuda.synchronize()
-    print(f"{h}x{w} {kernel:4s}: lookup {best * 1e3:8.1f} us/iter = {flops / best / 1e9:6.1f} TFLOP/s useful; build_pyramid (pool"
+    print(f"{rows}/{h}x{w} {kernel:4s}: lookup {best * 1e3:8.1f} us/iter = {flops / best / 1e9:6.1f} TFLOP/s useful; build_pyramid (pool"
           f"{' + split' if kernel == 'tc' else ''}) {e0.elapsed_time(e1) * 1e3:.1f} us", flush=True)
 scale = float(outs["simt"].abs().mean())
 print(f"max |tc - simt| = {float((outs['tc'] - outs['simt']).abs().max()):.3e} (mean |value| {scale:.3f})")
