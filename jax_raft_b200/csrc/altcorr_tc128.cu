@@ -1,20 +1,32 @@
 // The on-the-fly ("alt_corr") window lookup on the tensor cores at M = 128, with the A operand in TENSOR MEMORY.
 // Same result contract, operands and arithmetic as altcorr_tc.cu (read its header first); what differs:
 //
-//   item       one 16 x 8 patch of query pixels (two neighbouring 8 x 8 patches), all levels in turn.  UMMA M = 128
-//              runs the tensor pipe at its full rate (M = 64 costs the same cycles per instruction), the union box of
-//              the patch has ~30 % fewer cells per query than two 8 x 8 boxes, and accumulator row m = TMEM lane m, so
-//              all 32 lanes of every tcgen05.ld of the extraction carry a query (16 of 32 at M = 64).
+//   item       one 16 x 8 patch of query pixels (two neighbouring 8 x 8 patches), all levels in turn, UMMA M = 128.  The
+//              union box of the patch has ~35 % fewer cells per query than two 8 x 8 boxes (fewer B bytes and fewer
+//              stages per query: the stage pipeline, not the tensor pipe, paces these kernels — DESIGN.md §4.4), and
+//              accumulator row m = TMEM lane m, so all 32 lanes of every tcgen05.ld of the extraction carry a query
+//              (16 of 32 at M = 64).
 //   A          128 queries x 2D bf16 = 128 KB does not fit shared memory beside the footprints — it lives in TMEM:
 //              lane = query, 256 columns of packed bf16 pairs ([hi | mid], K = 2D <= 512), written by four loader warps
 //              (TMEM lane quarter = warp & 3) straight from global memory with tcgen05.st.32x32b — a thread owns its
 //              query's row — k-block by k-block as the last chunk of the previous item releases it.  The MMAs are
-//              tcgen05.mma [d_tmem], [a_tmem], b_desc (TS form; profiles/scratch/ts_mma_probe.cu pins the layout).
-//   D          two accumulators of 128 columns (columns 0-255; A: 256-511): chunks of 4 box rows x <= 32 cells.
-//   roles      warps 0-3 extraction, 4-7 taps (32 queries each), 8 B producer, 9 MMA issuer, 10 item descriptions,
-//              11-14 A loaders; 480 threads, <= 136 registers.
+//              tcgen05.mma [d_tmem], [a_tmem], b_desc (TS form; profiles/scratch/ts_mma_probe.cu pins the layout), so
+//              the MMAs read only B from shared memory.
+//   B          a stage of the ring is ONE TMA box {64 channels, 8 ncb cells, rows} from a tensor map per (level, box
+//              width ncb = 1 .. 4); rows = rows_for(ncb) is as tall as N = 8 ncb rows <= 128 allows (8, 8, 5, 4), so the
+//              narrow boxes of the coarse levels need half the chunks of a fixed height and every stage is 8-16 KB;
+//              accumulator column of box cell (r, x) = 8 ncb r + x.
+//   D          two accumulators of 128 columns (columns 0-255; A: 256-511).
+//   wide boxes when the union box of the patch is wider than 32 cells or taller than 32 rows, the left and right 8 x 8
+//              halves get a box each and are multiplied in turn (a query extracts from its own half's box; the other
+//              half's accumulator rows are ignored); only if a half does not fit either does the level take the scalar
+//              float32 path — exactly where altcorr_tc.cu does.
+//   roles      warps 0-3 extraction, 4-7 taps (32 queries each), 8 B producer, 9 MMA issuer, 10 item descriptions
+//              (coordinates + boxes, four in flight; the extraction threads recompute their own window origins),
+//              11-14 A loaders; 480 threads, 128 registers.
 //
-// Boxes wider than 32 cells or taller than 32 rows (rough flow) take the scalar float32 path, as in altcorr_tc.cu.
+// Measured, bands of a 136 x 240 image (profiles/altcorr_time.py 136 240 rows), against altcorr_tc.cu: 136 rows 96 vs
+// 114 us, 68 rows 59 vs 69, 34 rows 41 vs 45, 17 rows 34 vs 31 — raftk_altcorr_lookup_tc picks by problem size.
 
 #include <cuda.h>
 #include <cuda_bf16.h>
