@@ -1,5 +1,5 @@
 """SASS evidence that the tensor-core / TMA kernels are Blackwell-native: per kernel of lib/libraftk.so, the count of
-tcgen05 MMA (UTCHMMA / UTC*MMA), TMEM load (LDTM), TMA load/store (UTMALDG / UTMASTG), bulk copy (UBLKCP) and
+tcgen05 MMA (UTCHMMA / UTC*MMA), TMEM load / store (LDTM / STTM), TMA load/store (UTMALDG / UTMASTG), bulk copy (UBLKCP) and
 tcgen05 commit (UTCBAR) instructions.  Runs without a GPU:
     python profiles/sass_evidence.py > profiles/r2_sass_evidence.md"""
 import collections
@@ -10,7 +10,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "jax_raft_b200", "lib", "libraftk.so")
-MNEMONICS = ("UTCHMMA", "UTCQMMA", "UTCIMMA", "UTCOMMA", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP", "UTCBAR", "UTCATOMSWS", "HMMA", "FFMA")
+MNEMONICS = ("UTCHMMA", "UTCQMMA", "UTCIMMA", "UTCOMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UTCBAR", "UTCATOMSWS", "HMMA", "FFMA")
 sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
 demangle = lambda n: subprocess.run(["c++filt", n], capture_output=True, text=True).stdout.strip()  # noqa: E731
 counts, variants = collections.OrderedDict(), collections.Counter()
