@@ -699,7 +699,8 @@ extern "C" int raftk_altcorr_lookup_tc(const float* fmap1, const float* const* f
     // 34 rows 41 vs 45, 17 rows 34 vs 31); below that the 8 x 8 patches of this file's kernel spread the work wider
     const int mode = altcorr_mode_flag();
     const long long patches128 = (long long)B * ((nq / w + 7) / 8) * ((w + 15) / 16);
-    if (mode == 2 || (mode == 0 && 5 * patches128 >= 2 * (long long)sm_count()))
+    const bool fits128 = (long long)B * nq <= 0x7fffffffLL;  // that kernel keeps query indices in 32 bits
+    if (fits128 && (mode == 2 || (mode == 0 && 5 * patches128 >= 2 * (long long)sm_count())))
       return altcorr_tc128_launch(fmap1, f2_levels, f1_split, f2_split, num_levels, coords, out, B, nq, h, w, D, radius, stream);
   }
   EncodeTiledFn encode = get_encode_fn();
